@@ -1,0 +1,168 @@
+/*
+ * torchbooster_b200 -- C ABI of the B200-native batch-transform + metrics hot path.
+ *
+ * The reference (yliess86/TorchBooster) is pure Python and has no FFI of its own; each entry
+ * point below names the reference code it stands in for (paths relative to the reference
+ * checkout; "torchvision/..." = the third-party code the reference's examples call).
+ *
+ * Conventions (every function):
+ *   - returns 0 on success, a negative TB_E* code for argument errors, a positive cudaError_t for
+ *     CUDA errors; tb_last_error() gives a thread-local message for the last non-zero return;
+ *   - never throws, never synchronises the device, only enqueues on `stream`
+ *     (a cudaStream_t; NULL = legacy default stream);
+ *   - the caller owns every buffer and keeps it alive until the enqueued work has completed;
+ *   - works on the current CUDA device of the calling thread; no library-global mutable state;
+ *   - accumulating outputs (counters, confusion, running sums) are ADDED TO: the caller zeroes them.
+ */
+#ifndef TORCHBOOSTER_B200_H
+#define TORCHBOOSTER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TB_ABI_VERSION 1
+
+#define TB_OK        0
+#define TB_EINVAL  (-22)   /* bad argument (shape, alignment, enum) */
+#define TB_ENOTSUP (-95)   /* valid request this build does not cover */
+
+/* element types of outputs / logits */
+#define TB_F32  0
+#define TB_BF16 1
+#define TB_F16  2
+
+/* padding modes of torchvision F.pad (torchvision/transforms/_functional_pil.py:147-223) */
+#define TB_PAD_NONE      0  /* no padding declared; reads outside the image still give 0 */
+#define TB_PAD_CONSTANT  1  /* fill = 0 */
+#define TB_PAD_REFLECT   2  /* numpy "reflect": no edge repeat */
+#define TB_PAD_EDGE      3
+#define TB_PAD_SYMMETRIC 4
+
+/* lookup-table kinds for tb_build_lut */
+#define TB_LUT_TO_TENSOR  0  /* fl(x)/255                          ToTensor   (torchvision functional.py:127-178) */
+#define TB_LUT_NORMALIZE  1  /* (fl(x)/255 - mean) / std           Normalize  (_functional_tensor.py:905-928)     */
+#define TB_LUT_ONE_MINUS  2  /* 1 - fl(x)/255                      examples/img_gen/gan/gan.py:99, vae/vae.py:107 */
+#define TB_LUT_NORMALIZE_ONE_MINUS 3  /* 1 - (fl(x)/255 - mean)/std */
+
+/* flags */
+#define TB_FLAG_FORCE_GENERIC 1  /* tests: skip the staged fast path, use the one-gather-per-element kernel */
+
+typedef struct CUstream_st* tb_stream_t;   /* == cudaStream_t */
+
+#if defined(__GNUC__)
+#define TB_API __attribute__((visibility("default")))
+#else
+#define TB_API
+#endif
+
+TB_API int         tb_version(void);
+TB_API const char* tb_last_error(void);
+/* number of kernels this library has launched from the calling process (bench.py's gpu_launches) */
+TB_API int64_t     tb_launch_count(void);
+
+/*
+ * Per-channel 256-entry table of the pointwise part of the pipeline, built ON THE DEVICE with
+ * IEEE round-to-nearest sub/div in the reference's operation order (mean/std rounded to fp32
+ * first, no FMA contraction), then rounded RNE to `dst_dtype`.
+ * Replaces: T.ToTensor + T.Normalize (examples/img_cls/resnet/resnet.py:94,101;
+ * examples/img_stt/adain/adain.py:167-170) and the `1.0 - X` of examples/img_gen/gan/gan.py:99.
+ *   mean, std : HOST pointers, C floats each (ignored for kinds without normalise; may be NULL)
+ *   lut       : DEVICE, [C][256] elements of dst_dtype (TB_F32 or TB_BF16 or TB_F16)
+ */
+TB_API int tb_build_lut(int kind, const float* mean, const float* std, int C, int dst_dtype,
+                 void* lut, tb_stream_t stream);
+
+/*
+ * Fused pad -> crop -> horizontal flip -> table lookup -> cast, uint8 NHWC -> NCHW.
+ * Replaces, per batch instead of per sample: T.RandomCrop(size, padding, padding_mode) +
+ * T.RandomHorizontalFlip + T.ToTensor + T.Normalize + default collate
+ * (examples/img_cls/resnet/resnet.py:94-103; torchvision/transforms/transforms.py:634-722;
+ * torchbooster/config.py:371-379) and the fp32 host->device copy of torchbooster/config.py:174-175.
+ *
+ *   dst[b,c,y,x] = lut[c][ src[b, u, v, c] ],  xs = flip[b] ? out_w-1-x : x,
+ *   u = crop_top[b] + y - pad_y,  v = crop_left[b] + xs - pad_x,  folded by pad_mode; 0 outside.
+ *
+ *   src              : DEVICE uint8, element (b,h,w,c) at src + b*src_batch_stride + h*src_row_pitch + w*C + c
+ *   dst              : DEVICE contiguous [B][C][out_h][out_w] of dst_dtype (TB_F32 / TB_BF16 / TB_F16)
+ *   crop_top/left    : DEVICE int32[B] in padded coordinates (what F.crop receives); NULL = 0
+ *   flip             : DEVICE uint8[B]; NULL = no flip
+ *   lut              : DEVICE [C][256] of dst_dtype
+ * 1 <= C <= 4.  For reflect pad_y <= H-1, pad_x <= W-1; for symmetric pad <= size.
+ */
+TB_API int tb_transform_u8_nhwc_to_nchw(
+    const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride, int64_t src_row_pitch,
+    void* dst, int dst_dtype, int out_h, int out_w,
+    const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
+    int pad_y, int pad_x, int pad_mode,
+    const void* lut, int flags, tb_stream_t stream);
+
+/*
+ * Pillow's antialiased bilinear filter taps for one axis (host computation, float64 exactly as
+ * libImaging/Resample.c precompute_coeffs + normalize_coeffs_8bpc, 22-bit fixed point).
+ * Replaces the coefficient set-up inside T.Resize (examples/img_stt/adain/adain.py:170 ->
+ * torchvision/transforms/_functional_pil.py:242-253 -> PIL.Image.resize).
+ *   tb_resize_ksize : taps per output position
+ *   bounds : HOST int32 [out_size][2] = (first input index, tap count)
+ *   taps   : HOST int32 [out_size][ksize]
+ */
+TB_API int tb_resize_ksize(int in_size, int out_size);
+TB_API int tb_resize_taps(int in_size, int out_size, int32_t* bounds, int32_t* taps);
+
+/*
+ * Pillow-exact bilinear resize (horizontal pass -> uint8-rounded intermediate -> vertical pass)
+ * fused with crop / centre-crop (zero fill outside), flip, table lookup and cast.
+ * Replaces T.Resize + T.CenterCrop + T.ToTensor + T.Normalize
+ * (examples/img_stt/adain/adain.py:170; online/online.py:171-173; offline/offline.py:110).
+ *
+ *   R = resize(src[b]) of size [rs_h][rs_w][C]  (uint8; lives in shared memory only)
+ *   dst[b,c,y,x] = lut[c][ R[crop_top[b] + off_y + y, crop_left[b] + off_x + xs, c] ]  (0 outside R)
+ *
+ *   bounds_x,taps_x : DEVICE copies of tb_resize_taps(W, rs_w, ..) ; ks_x = tb_resize_ksize(W, rs_w)
+ *   bounds_y,taps_y : DEVICE copies of tb_resize_taps(H, rs_h, ..) ; ks_y likewise
+ *   off_y, off_x    : static offsets (centre crop: int(round((rs_h - out_h)/2.0)), may be negative)
+ * C in {1,3}: Pillow premultiplies alpha before resampling RGBA, which this path does not restate.
+ */
+TB_API int tb_resize_bilinear_u8_nhwc_to_nchw(
+    const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride, int64_t src_row_pitch,
+    int rs_h, int rs_w,
+    const int32_t* bounds_x, const int32_t* taps_x, int ks_x,
+    const int32_t* bounds_y, const int32_t* taps_y, int ks_y,
+    void* dst, int dst_dtype, int out_h, int out_w,
+    const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip, int off_y, int off_x,
+    const void* lut, int flags, tb_stream_t stream);
+
+/*
+ * One pass over a logits matrix: top-1 and top-k correct counts and confusion-matrix bins.
+ * Replaces torchbooster.metrics.accuracy (torchbooster/metrics.py:11-27: argmax == labels, sum)
+ * -- the count, before the division -- and adds the top-k / confusion accumulators the north
+ * star names (no reference counterpart; defined by the rank rule).
+ *
+ *   pred_n = first index of the row maximum, NaN counting as maximal (torch.argmax)
+ *   rank_n = #{j : l[n,j] > l[n,y_n]  or  (l[n,j] == l[n,y_n] and j < y_n)}
+ *   counters[0] += N ; [1] += #{rank_n < 1} ; [2] += #{rank_n < k} ; [3] += #{y_n outside [0,C)}
+ *   confusion[y_n*C + pred_n] += 1   (skipped for labels outside [0,C))
+ *
+ *   logits   : DEVICE [N][C], row n at logits + n*row_stride elements, dtype TB_F32/TB_BF16/TB_F16
+ *   labels   : DEVICE int64[N]
+ *   counters : DEVICE int64[4];  confusion : DEVICE int64[C*C] or NULL
+ */
+TB_API int tb_metrics_update(const void* logits, int logits_dtype, int64_t N, int C, int64_t row_stride,
+                      const int64_t* labels, int k,
+                      int64_t* counters, int64_t* confusion, tb_stream_t stream);
+
+/*
+ * Device-resident running mean: state[0] += sum(x[0..n)), state[1] += n   (float64).
+ * Replaces the two `.item()` syncs per step that feed torchbooster.metrics.RunningAverage
+ * (torchbooster/metrics.py:55-75; call sites examples/img_cls/resnet/resnet.py:66-67).
+ * The sum over x is taken in a fixed order (deterministic for a given n).
+ *   x : DEVICE, n elements of dtype TB_F32/TB_BF16/TB_F16 ;  state : DEVICE double[2]
+ */
+TB_API int tb_running_sum_update(const void* x, int dtype, int64_t n, double* state, tb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TORCHBOOSTER_B200_H */

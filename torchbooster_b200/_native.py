@@ -1,0 +1,107 @@
+"""ctypes binding of ``include/torchbooster_b200.h`` (the C-ABI boundary).
+
+There is no CPU fallback: if the shared library is missing or does not load, every entry point
+raises.  ctypes releases the GIL for the duration of each call.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from pathlib import Path
+
+_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libtorchbooster_b200.so"
+_lock = threading.Lock()
+_lib = None
+
+TB_OK, TB_EINVAL, TB_ENOTSUP = 0, -22, -95
+TB_F32, TB_BF16, TB_F16 = 0, 1, 2
+PAD_MODES = {"none": 0, "constant": 1, "reflect": 2, "edge": 3, "symmetric": 4}
+LUT_TO_TENSOR, LUT_NORMALIZE, LUT_ONE_MINUS, LUT_NORMALIZE_ONE_MINUS = 0, 1, 2, 3
+FLAG_FORCE_GENERIC = 1
+
+_i32, _i64, _vp = C.c_int, C.c_int64, C.c_void_p
+
+# name -> (restype, argtypes); mirrors include/torchbooster_b200.h one to one
+SIGNATURES = {
+    "tb_version": (_i32, []),
+    "tb_last_error": (C.c_char_p, []),
+    "tb_launch_count": (_i64, []),
+    "tb_build_lut": (_i32, [_i32, _vp, _vp, _i32, _i32, _vp, _vp]),
+    "tb_transform_u8_nhwc_to_nchw": (_i32, [_vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp, _i32, _i32, _i32,
+                                            _vp, _vp, _vp, _i32, _i32, _i32, _vp, _i32, _vp]),
+    "tb_resize_ksize": (_i32, [_i32, _i32]),
+    "tb_resize_taps": (_i32, [_i32, _i32, _vp, _vp]),
+    "tb_resize_bilinear_u8_nhwc_to_nchw": (_i32, [_vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _i32,
+                                                  _vp, _vp, _i32, _vp, _vp, _i32, _vp, _i32, _i32, _i32,
+                                                  _vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp]),
+    "tb_metrics_update": (_i32, [_vp, _i32, _i64, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
+    "tb_running_sum_update": (_i32, [_vp, _i32, _i64, _vp, _vp]),
+}
+
+
+class NativeLibraryMissing(ImportError):
+    pass
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def lib():
+    """The loaded library.  Raises ``NativeLibraryMissing`` -- never falls back."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            if not _LIB_PATH.exists():
+                raise NativeLibraryMissing(
+                    f"{_LIB_PATH} is missing: build it with `python -m torchbooster_b200.build` "
+                    "(needs nvcc).  torchbooster_b200 has no CPU or PyTorch fallback.")
+            try:
+                handle = C.CDLL(str(_LIB_PATH))
+            except OSError as e:  # pragma: no cover
+                raise NativeLibraryMissing(f"cannot load {_LIB_PATH}: {e}") from e
+            for name, (res, args) in SIGNATURES.items():
+                fn = getattr(handle, name)
+                fn.restype, fn.argtypes = res, args
+            _lib = handle
+    return _lib
+
+
+def last_error() -> str:
+    msg = lib().tb_last_error()
+    return msg.decode("utf-8", "replace") if msg else ""
+
+
+def check(rc: int, what: str = "") -> None:
+    """Translate a C-ABI return code: argument errors -> ValueError, the rest -> RuntimeError."""
+    if rc == TB_OK:
+        return
+    msg = last_error() or what
+    if rc == TB_EINVAL:
+        raise ValueError(msg)
+    if rc == TB_ENOTSUP:
+        raise NotImplementedError(msg)
+    raise RuntimeError(msg)
+
+
+def dtype_code(dtype) -> int:
+    import torch
+    try:
+        return {torch.float32: TB_F32, torch.bfloat16: TB_BF16, torch.float16: TB_F16}[dtype]
+    except KeyError:
+        raise ValueError(f"unsupported dtype {dtype}; use float32, bfloat16 or float16") from None
+
+
+def require_cuda(t, name: str):
+    if not t.is_cuda:
+        raise RuntimeError(
+            f"{name} must be a CUDA tensor: torchbooster_b200 runs this path on the GPU only "
+            "(there is no CPU fallback)")
+    return t
+
+
+def current_stream_ptr(device) -> int:
+    import torch
+    return torch.cuda.current_stream(device).cuda_stream

@@ -1,0 +1,302 @@
+// Pillow-exact antialiased bilinear resize fused with crop / flip / table lookup / cast (sm_100a).
+//
+// Replaces T.Resize + T.CenterCrop + T.ToTensor + T.Normalize of the reference's style-transfer
+// examples (examples/img_stt/adain/adain.py:170, online/online.py:171-173, offline/offline.py:110),
+// i.e. torchvision's PIL path -> PIL.Image.resize(BILINEAR) -> libImaging ImagingResample:
+// 22-bit fixed-point taps, horizontal pass first into a uint8-ROUNDED intermediate, then the
+// vertical pass.  Both roundings are reproduced, so the result is bit-identical to Pillow.
+//
+// One launch, no global intermediate: a CTA owns a tile of final output pixels; phase 1 runs the
+// horizontal pass for exactly the input rows / resized columns that tile needs into shared
+// memory, phase 2 runs the vertical pass out of shared memory, looks the byte up and stores.
+#include <math.h>
+#include <vector>
+
+#include "tb_common.cuh"
+
+// ----------------------------------------------------------------------------------------------
+// host: filter taps (libImaging/Resample.c precompute_coeffs + normalize_coeffs_8bpc, bilinear)
+// ----------------------------------------------------------------------------------------------
+static const int kPrecisionBits = 32 - 8 - 2;
+
+extern "C" int tb_resize_ksize(int in_size, int out_size) {
+    if (in_size < 1 || out_size < 1) return tb_fail(TB_EINVAL, "tb_resize_ksize: sizes must be >= 1");
+    double scale = (double)in_size / (double)out_size;
+    double filterscale = scale < 1.0 ? 1.0 : scale;
+    double support = 1.0 * filterscale;
+    return (int)ceil(support) * 2 + 1;
+}
+
+extern "C" int tb_resize_taps(int in_size, int out_size, int32_t* bounds, int32_t* taps) {
+    TB_REQUIRE(in_size >= 1 && out_size >= 1, "tb_resize_taps: sizes must be >= 1");
+    TB_REQUIRE(bounds && taps, "tb_resize_taps: NULL output");
+    const double scale = (double)in_size / (double)out_size;
+    const double filterscale = scale < 1.0 ? 1.0 : scale;
+    const double support = 1.0 * filterscale;
+    const int ksize = (int)ceil(support) * 2 + 1;
+    const double ss = 1.0 / filterscale;
+    std::vector<double> w(ksize);
+    for (int xx = 0; xx < out_size; ++xx) {
+        const double center = (xx + 0.5) * scale;
+        int xmin = (int)(center - support + 0.5);
+        if (xmin < 0) xmin = 0;
+        int xmax = (int)(center + support + 0.5);
+        if (xmax > in_size) xmax = in_size;
+        xmax -= xmin;
+        double ww = 0.0;
+        for (int x = 0; x < xmax; ++x) {
+            double a = (x + xmin - center + 0.5) * ss;
+            if (a < 0.0) a = -a;
+            const double v = a < 1.0 ? 1.0 - a : 0.0;
+            w[x] = v;
+            ww += v;
+        }
+        for (int x = 0; x < xmax; ++x)
+            if (ww != 0.0) w[x] /= ww;
+        for (int x = xmax; x < ksize; ++x) w[x] = 0.0;
+        for (int x = 0; x < ksize; ++x) {
+            const double v = w[x];
+            taps[(size_t)xx * ksize + x] =
+                v < 0 ? (int)(-0.5 + v * (1 << kPrecisionBits)) : (int)(0.5 + v * (1 << kPrecisionBits));
+        }
+        bounds[2 * xx] = xmin;
+        bounds[2 * xx + 1] = xmax;
+    }
+    return TB_OK;
+}
+
+// ----------------------------------------------------------------------------------------------
+// device
+// ----------------------------------------------------------------------------------------------
+namespace {
+
+struct RsParams {
+    const uint8_t* src;
+    int B, H, W;
+    int64_t bs, pitch;
+    int rs_h, rs_w;
+    const int32_t* bx; const int32_t* kx; int ksx;
+    const int32_t* by; const int32_t* ky; int ksy;
+    void* dst;
+    int out_h, out_w;
+    const int32_t* top; const int32_t* left; const uint8_t* flip;
+    int off_y, off_x;
+    const void* lut;
+    int TR, TC, tiles_x, tiles_y;
+    int row_bytes;     // bytes per intermediate row in shared memory (multiple of 4)
+    int words_ok;      // source rows may be read as aligned 32-bit words
+};
+
+__device__ __forceinline__ uint8_t tb_clip8(int acc) {
+    int v = acc >> kPrecisionBits;
+    v = v < 0 ? 0 : (v > 255 ? 255 : v);
+    return (uint8_t)v;
+}
+
+// C bytes at p (any alignment) packed little-endian into one word.
+template <int C>
+__device__ __forceinline__ uint32_t tb_load_px(const uint8_t* p, bool words_ok) {
+    if (C == 1) return *p;
+    if (words_ok) {
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>((uintptr_t)p & ~(uintptr_t)3);
+        const int sh = (int)((uintptr_t)p & 3);
+        uint32_t lo = __ldg(wp);
+        if (sh + C > 4) {
+            const uint32_t hi = __ldg(wp + 1);
+            lo = __funnelshift_r(lo, hi, sh * 8);
+        } else {
+            lo >>= sh * 8;
+        }
+        return lo;
+    }
+    uint32_t w = 0;
+#pragma unroll
+    for (int c = 0; c < C; ++c) w |= (uint32_t)p[c] << (8 * c);
+    return w;
+}
+
+template <typename T, int C>
+__global__ void __launch_bounds__(256) tb_resize_fused_kernel(RsParams p) {
+    extern __shared__ __align__(16) uint8_t inter[];   // [nin][row_bytes]
+    __shared__ T s_lut[C * 256];
+    for (int i = threadIdx.x; i < C * 256; i += blockDim.x) s_lut[i] = ((const T*)p.lut)[i];
+
+    int t = blockIdx.x;
+    const int tx = t % p.tiles_x; t /= p.tiles_x;
+    const int ty = t % p.tiles_y;
+    const int b = t / p.tiles_y;
+    const int y0 = ty * p.TR, x0 = tx * p.TC;
+    const int nr = min(p.TR, p.out_h - y0), nc = min(p.TC, p.out_w - x0);
+    const int oy = (p.top ? p.top[b] : 0) + p.off_y;
+    const int ox = (p.left ? p.left[b] : 0) + p.off_x;
+    const bool flip = p.flip ? (p.flip[b] != 0) : false;
+
+    // resized rows / columns this tile touches
+    const int ry0 = max(oy + y0, 0), ry1 = min(oy + y0 + nr, p.rs_h);
+    const int xs0 = flip ? p.out_w - x0 - nc : x0;
+    const int rx0 = max(ox + xs0, 0), rx1 = min(ox + xs0 + nc, p.rs_w);
+    const bool any = ry1 > ry0 && rx1 > rx0;
+    const bool vpass = p.rs_h != p.H, hpass = p.rs_w != p.W;
+
+    int iy0 = 0, nin = 0;
+    if (any) {
+        if (vpass) {
+            iy0 = p.by[2 * ry0];
+            nin = p.by[2 * (ry1 - 1)] + p.by[2 * (ry1 - 1) + 1] - iy0;
+        } else {
+            iy0 = ry0;
+            nin = ry1 - ry0;
+        }
+    }
+    const int ncols = any ? rx1 - rx0 : 0;
+    const uint8_t* simg = p.src + (int64_t)b * p.bs;
+
+    // ---- phase 1: horizontal pass (or copy) of input rows [iy0, iy0+nin), columns [rx0, rx1)
+    for (int i = threadIdx.x; i < nin * ncols; i += blockDim.x) {
+        const int r = i / ncols;
+        const int cx = i - r * ncols;
+        const int rx = rx0 + cx;
+        const uint8_t* row = simg + (int64_t)(iy0 + r) * p.pitch;
+        uint8_t* o = inter + (size_t)r * p.row_bytes + cx * C;
+        if (hpass) {
+            const int xmin = p.bx[2 * rx], n = p.bx[2 * rx + 1];
+            const int32_t* k = p.kx + (size_t)rx * p.ksx;
+            int acc[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) acc[c] = 1 << (kPrecisionBits - 1);
+            for (int j = 0; j < n; ++j) {
+                const uint32_t w = tb_load_px<C>(row + (size_t)(xmin + j) * C, p.words_ok != 0);
+                const int kk = __ldg(k + j);
+#pragma unroll
+                for (int c = 0; c < C; ++c) acc[c] += (int)((w >> (8 * c)) & 0xffu) * kk;
+            }
+#pragma unroll
+            for (int c = 0; c < C; ++c) o[c] = tb_clip8(acc[c]);
+        } else {
+            const uint32_t w = tb_load_px<C>(row + (size_t)rx * C, p.words_ok != 0);
+#pragma unroll
+            for (int c = 0; c < C; ++c) o[c] = (uint8_t)(w >> (8 * c));
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 2: vertical pass out of shared memory, table lookup, NCHW store
+    T* dimg = (T*)p.dst + (int64_t)b * C * p.out_h * p.out_w;
+    const int64_t plane = (int64_t)p.out_h * p.out_w;
+    for (int i = threadIdx.x; i < nr * nc; i += blockDim.x) {
+        const int yy = i / nc;
+        const int xx = i - yy * nc;
+        const int y = y0 + yy, x = x0 + xx;
+        const int ry = oy + y;
+        const int rx = ox + (flip ? p.out_w - 1 - x : x);
+        uint32_t e[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) e[c] = 0;
+        if (ry >= 0 && ry < p.rs_h && rx >= 0 && rx < p.rs_w) {
+            const uint8_t* col = inter + (size_t)(rx - rx0) * C;
+            if (vpass) {
+                const int ymin = p.by[2 * ry] - iy0, n = p.by[2 * ry + 1];
+                const int32_t* k = p.ky + (size_t)ry * p.ksy;
+                int acc[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) acc[c] = 1 << (kPrecisionBits - 1);
+                for (int j = 0; j < n; ++j) {
+                    const uint8_t* q = col + (size_t)(ymin + j) * p.row_bytes;
+                    const int kk = __ldg(k + j);
+#pragma unroll
+                    for (int c = 0; c < C; ++c) acc[c] += (int)q[c] * kk;
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) e[c] = tb_clip8(acc[c]);
+            } else {
+                const uint8_t* q = col + (size_t)(ry - iy0) * p.row_bytes;
+#pragma unroll
+                for (int c = 0; c < C; ++c) e[c] = q[c];
+            }
+        }
+        T* d = dimg + (int64_t)y * p.out_w + x;
+#pragma unroll
+        for (int c = 0; c < C; ++c) d[c * plane] = s_lut[c * 256 + e[c]];
+    }
+}
+
+template <typename T, int C>
+int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, cudaStream_t s) {
+    static bool attr_set[64] = {};
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    if (smem > 48 * 1024 && !attr_set[dev]) {
+        TB_CUDA(cudaFuncSetAttribute(tb_resize_fused_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     max_smem - 8192));
+        attr_set[dev] = true;
+    }
+    tb_resize_fused_kernel<T, C><<<(unsigned)blocks, 256, smem, s>>>(p);
+    TB_LAUNCH_CHECK("tb_resize_fused_kernel");
+    return TB_OK;
+}
+
+}  // namespace
+
+extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
+    const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride, int64_t src_row_pitch, int rs_h,
+    int rs_w, const int32_t* bounds_x, const int32_t* taps_x, int ks_x, const int32_t* bounds_y,
+    const int32_t* taps_y, int ks_y, void* dst, int dst_dtype, int out_h, int out_w, const int32_t* crop_top,
+    const int32_t* crop_left, const uint8_t* flip, int off_y, int off_x, const void* lut, int flags,
+    tb_stream_t stream) {
+    (void)flags;
+    TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_resize: bad source shape B=%d H=%d W=%d", B, H, W);
+    TB_REQUIRE(C == 1 || C == 3, "tb_resize: C=%d not supported (Pillow premultiplies alpha for RGBA); use C in {1,3}", C);
+    TB_REQUIRE(rs_h >= 1 && rs_w >= 1 && out_h >= 1 && out_w >= 1, "tb_resize: bad output sizes");
+    TB_REQUIRE(tb_dtype_size(dst_dtype) != 0, "tb_resize: unknown dst_dtype %d", dst_dtype);
+    TB_REQUIRE(src_row_pitch >= (int64_t)W * C && src_batch_stride >= 0, "tb_resize: bad source strides");
+    if (rs_w != W) {
+        TB_REQUIRE(bounds_x && taps_x, "tb_resize: horizontal taps missing");
+        TB_REQUIRE(ks_x == tb_resize_ksize(W, rs_w), "tb_resize: ks_x=%d does not match tb_resize_ksize(%d,%d)", ks_x, W, rs_w);
+    }
+    if (rs_h != H) {
+        TB_REQUIRE(bounds_y && taps_y, "tb_resize: vertical taps missing");
+        TB_REQUIRE(ks_y == tb_resize_ksize(H, rs_h), "tb_resize: ks_y=%d does not match tb_resize_ksize(%d,%d)", ks_y, H, rs_h);
+    }
+    if (B == 0) return TB_OK;
+    TB_REQUIRE(src && dst && lut, "tb_resize: NULL src/dst/lut");
+    TB_REQUIRE(((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_resize: dst misaligned for its dtype");
+
+    TbDevice dev;
+    int rc = tb_device(&dev);
+    if (rc) return rc;
+
+    RsParams p;
+    p.src = src; p.B = B; p.H = H; p.W = W; p.bs = src_batch_stride; p.pitch = src_row_pitch;
+    p.rs_h = rs_h; p.rs_w = rs_w;
+    p.bx = bounds_x; p.kx = taps_x; p.ksx = ks_x; p.by = bounds_y; p.ky = taps_y; p.ksy = ks_y;
+    p.dst = dst; p.out_h = out_h; p.out_w = out_w;
+    p.top = crop_top; p.left = crop_left; p.flip = flip; p.off_y = off_y; p.off_x = off_x; p.lut = lut;
+    p.words_ok = (((uintptr_t)src & 3) == 0 && (src_row_pitch & 3) == 0 && (src_batch_stride & 3) == 0) ? 1 : 0;
+
+    // Tile: TC output columns x TR output rows; the intermediate holds every input row the TR
+    // resized rows can touch: at most ceil(TR * scale_y) + ks_y rows.
+    const double scale_y = rs_h != H ? (double)H / rs_h : 1.0;
+    const int budget = 40 * 1024;
+    int TC = out_w < 256 ? out_w : 256;
+    int TR = 8;
+    auto rows_for = [&](int tr) { return rs_h != H ? (int)ceil(tr * scale_y) + ks_y + 1 : tr; };
+    auto rowb = [&](int tc) { return (tc * C + 3) & ~3; };
+    while (TR > 1 && (int64_t)rows_for(TR) * rowb(TC) > budget) TR >>= 1;
+    while (TC > 8 && (int64_t)rows_for(TR) * rowb(TC) > budget) TC = (TC + 1) / 2;
+    const int64_t smem = (int64_t)rows_for(TR) * rowb(TC);
+    TB_REQUIRE(smem <= dev.max_smem_optin - 8192, "tb_resize: a %dx%d tile needs %lld bytes of shared memory",
+               TR, TC, (long long)smem);
+    if (TR > out_h) TR = out_h;
+    p.TR = TR; p.TC = TC;
+    p.tiles_x = (out_w + TC - 1) / TC;
+    p.tiles_y = (out_h + TR - 1) / TR;
+    p.row_bytes = rowb(TC);
+    const int64_t blocks = (int64_t)p.tiles_x * p.tiles_y * B;
+    TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize: grid too large");
+    cudaStream_t s = (cudaStream_t)stream;
+    const bool f32 = dst_dtype == TB_F32;
+    if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, s)
+                           : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, s);
+    return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, s)
+               : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, s);
+}

@@ -1,0 +1,288 @@
+"""Batch-level replacement of the reference's per-sample torchvision pipelines.
+
+The reference's examples build ``torchvision.transforms`` chains that run per sample on PIL
+images inside DataLoader workers, collate to fp32 NCHW and copy to the GPU
+(``examples/img_cls/resnet/resnet.py:94-107``, ``examples/img_stt/adain/adain.py:167-171``,
+``torchbooster/config.py:371-379,174-175``).  ``BatchTransform`` takes the raw uint8 NHWC batch
+instead and produces the same tensor with one CUDA launch through the C ABI
+(``include/torchbooster_b200.h``).  PyTorch only owns the buffers.
+
+Random parameters are *inputs*: pass ``params=(top, left, flip)`` to reproduce any given draw, or
+let ``CropFlipParams`` replay torch's CPU generator so that the draws equal what
+``T.RandomCrop`` / ``T.RandomHorizontalFlip`` would have produced under ``torch.manual_seed``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+
+from . import _native as N
+
+IntPair = Union[int, Tuple[int, int]]
+
+
+def _pair(v) -> Tuple[int, int]:
+    if isinstance(v, (tuple, list)):
+        if len(v) == 1:
+            return int(v[0]), int(v[0])
+        return int(v[0]), int(v[1])
+    return int(v), int(v)
+
+
+@dataclass(frozen=True)
+class TransformSpec:
+    """What the pipeline does, in the reference's vocabulary.
+
+    Order: ``Resize`` -> ``CenterCrop`` -> ``RandomCrop(size, padding, padding_mode)`` ->
+    ``RandomHorizontalFlip(p)`` -> ``ToTensor`` -> ``Normalize(mean, std)`` -> ``1 - X`` -> cast.
+
+    resize        ``T.Resize`` argument: int (short side) or (h, w); Pillow antialiased bilinear.
+    center_crop   ``T.CenterCrop`` size (zero fill when larger than the image).
+    crop          ``T.RandomCrop`` size; offsets come from ``params`` (0 when absent).
+    padding       ``T.RandomCrop`` padding: int or (left/right, top/bottom).
+    padding_mode  "constant" (fill 0) | "reflect" | "edge" | "symmetric".
+    flip_p        ``T.RandomHorizontalFlip`` probability; ``None`` = transform not in the pipeline.
+    mean, std     ``T.Normalize``; ``None`` = ToTensor only.
+    one_minus     the ``1.0 - X`` of ``examples/img_gen/gan/gan.py:99``.
+    dtype         output dtype: float32 (the reference), bfloat16 or float16 (RNE of the fp32 value).
+    """
+    crop: Optional[IntPair] = None
+    padding: IntPair = 0
+    padding_mode: str = "constant"
+    flip_p: Optional[float] = None
+    resize: Optional[IntPair] = None
+    center_crop: Optional[IntPair] = None
+    mean: Optional[Sequence[float]] = None
+    std: Optional[Sequence[float]] = None
+    one_minus: bool = False
+    dtype: torch.dtype = torch.float32
+
+    def __post_init__(self):
+        if self.padding_mode not in ("constant", "reflect", "edge", "symmetric"):
+            # message of torchvision/transforms/_functional_pil.py:176-177
+            raise ValueError("Padding mode should be either constant, edge, reflect or symmetric")
+        if (self.mean is None) != (self.std is None):
+            raise ValueError("mean and std must be given together")
+        if self.resize is not None and _pair(self.padding) != (0, 0) and self.padding_mode != "constant":
+            raise NotImplementedError("resize combined with non-constant padding is not supported")
+        if self.center_crop is not None and _pair(self.padding) != (0, 0):
+            raise NotImplementedError("center_crop combined with padding is not supported")
+        N.dtype_code(self.dtype)
+
+
+def resized_output_size(h: int, w: int, size: IntPair) -> Tuple[int, int]:
+    """Output size of ``T.Resize(size)``: an int sets the short side, the long side becomes
+    ``int(size * long / short)`` (torchvision ``functional.py:353-384``)."""
+    if isinstance(size, (tuple, list)) and len(size) == 2:
+        return int(size[0]), int(size[1])
+    s = int(size[0]) if isinstance(size, (tuple, list)) else int(size)
+    short, long = (w, h) if w <= h else (h, w)
+    new_short, new_long = s, int(s * long / short)
+    return (new_long, new_short) if w <= h else (new_short, new_long)
+
+
+class CropFlipParams:
+    """Vectorised replay of the draws ``T.RandomCrop.get_params`` and ``T.RandomHorizontalFlip``
+    make from torch's global CPU generator after ``torch.manual_seed(seed)``
+    (``torchvision/transforms/transforms.py:634-655,712-722``; ``torchbooster/utils.py:59-61``
+    seeds that generator).
+
+    torch's CPU generator is mt19937 seeded like ``numpy.random.RandomState(seed)``; per sample
+    it spends one 32-bit word per ``randint`` (``word % range``) and one per ``rand``
+    (``(word & (2**24 - 1)) * 2**-24``), in the order top, left, flip.  Nothing is drawn for the
+    crop when the padded image already has the crop size.
+    """
+
+    def __init__(self, seed: int) -> None:
+        self._rs = np.random.RandomState(int(seed) & 0xFFFFFFFF)
+
+    def draw(self, batch: int, h: int, w: int, crop: Optional[Tuple[int, int]], padding: Tuple[int, int] = (0, 0),
+             flip_p: Optional[float] = None):
+        """``h, w``: unpadded source size.  Returns numpy ``(top int32[B], left int32[B], flip uint8[B])``."""
+        px, py = padding
+        ph, pw = h + 2 * py, w + 2 * px
+        need_crop = crop is not None and not (ph == crop[0] and pw == crop[1])
+        if crop is not None and (ph < crop[0] or pw < crop[1]):
+            raise ValueError(f"Required crop size {tuple(crop)} is larger than input image size {(ph, pw)}")
+        per = (2 if need_crop else 0) + (1 if flip_p is not None else 0)
+        top = np.zeros(batch, np.int32)
+        left = np.zeros(batch, np.int32)
+        flip = np.zeros(batch, np.uint8)
+        if per == 0 or batch == 0:
+            return top, left, flip
+        words = self._rs.randint(0, 2 ** 32, size=(batch, per), dtype=np.uint64)
+        col = 0
+        if need_crop:
+            top = (words[:, 0] % np.uint64(ph - crop[0] + 1)).astype(np.int32)
+            left = (words[:, 1] % np.uint64(pw - crop[1] + 1)).astype(np.int32)
+            col = 2
+        if flip_p is not None:
+            u = (words[:, col] & np.uint64((1 << 24) - 1)).astype(np.float32) * np.float32(2.0 ** -24)
+            flip = (u < np.float32(flip_p)).astype(np.uint8)
+        return top, left, flip
+
+
+class BatchTransform:
+    """``uint8 [B,H,W,C]`` -> ``[B,C,h,w]`` on the GPU, bit-identical to the reference pipeline.
+
+    ``batch`` may be a CUDA tensor (any batch / row stride, pixels dense) or a host tensor
+    (ideally pinned), which is copied to the device on the current stream first.
+    """
+
+    def __init__(self, spec: TransformSpec, device: Union[str, torch.device, None] = None, seed: Optional[int] = None):
+        self.spec = spec
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        if self.device.type != "cuda":
+            raise RuntimeError("BatchTransform runs on a CUDA device only (no CPU fallback)")
+        self._luts = {}
+        self._taps = {}
+        self._rng = CropFlipParams(seed) if seed is not None else None
+        self._param_host = None
+        self.flags = 0
+
+    # -- tables ----------------------------------------------------------------------------
+    def lut(self, channels: int) -> torch.Tensor:
+        """Per-channel 256-entry table of ToTensor/Normalize/1-X/cast, built on the device."""
+        t = self._luts.get(channels)
+        if t is not None:
+            return t
+        sp = self.spec
+        if sp.mean is not None:
+            mean = [float(m) for m in sp.mean]
+            std = [float(s) for s in sp.std]
+            if len(mean) == 1:
+                mean = mean * channels
+            if len(std) == 1:
+                std = std * channels
+            if len(mean) != channels or len(std) != channels:
+                raise ValueError(f"mean/std have {len(mean)}/{len(std)} entries for {channels} channels")
+            kind = N.LUT_NORMALIZE_ONE_MINUS if sp.one_minus else N.LUT_NORMALIZE
+            m_arr = (C.c_float * channels)(*mean)
+            s_arr = (C.c_float * channels)(*std)
+        else:
+            kind = N.LUT_ONE_MINUS if sp.one_minus else N.LUT_TO_TENSOR
+            m_arr = s_arr = None
+        t = torch.empty((channels, 256), dtype=sp.dtype, device=self.device)
+        with torch.cuda.device(self.device):
+            N.check(N.lib().tb_build_lut(kind, m_arr, s_arr, channels, N.dtype_code(sp.dtype), t.data_ptr(),
+                                         N.current_stream_ptr(self.device)))
+        self._luts[channels] = t
+        return t
+
+    def _resize_taps(self, in_size: int, out_size: int):
+        key = (in_size, out_size)
+        hit = self._taps.get(key)
+        if hit is not None:
+            return hit
+        L = N.lib()
+        ks = L.tb_resize_ksize(in_size, out_size)
+        if ks < 0:
+            N.check(ks)
+        bounds = np.empty((out_size, 2), np.int32)
+        taps = np.empty((out_size, ks), np.int32)
+        N.check(L.tb_resize_taps(in_size, out_size, bounds.ctypes.data, taps.ctypes.data))
+        hit = (ks, torch.from_numpy(bounds).to(self.device), torch.from_numpy(taps).to(self.device))
+        self._taps[key] = hit
+        return hit
+
+    # -- parameters ------------------------------------------------------------------------
+    def geometry(self, h: int, w: int):
+        """Static geometry for a source of ``h x w``: resized size, static offsets, output size,
+        padding and whether random offsets apply."""
+        sp = self.spec
+        rs_h, rs_w = (resized_output_size(h, w, sp.resize) if sp.resize is not None else (h, w))
+        cur_h, cur_w, off_y, off_x = rs_h, rs_w, 0, 0
+        if sp.center_crop is not None:
+            ch, cw = _pair(sp.center_crop)
+            # torchvision functional.py:556-594: zero-pad when larger, then int(round(./2.0))
+            pad_l = (cw - cur_w) // 2 if cw > cur_w else 0
+            pad_t = (ch - cur_h) // 2 if ch > cur_h else 0
+            pad_r = (cw - cur_w + 1) // 2 if cw > cur_w else 0
+            pad_b = (ch - cur_h + 1) // 2 if ch > cur_h else 0
+            ph, pw = cur_h + pad_t + pad_b, cur_w + pad_l + pad_r
+            top = int(round((ph - ch) / 2.0))
+            left = int(round((pw - cw) / 2.0))
+            off_y, off_x = top - pad_t, left - pad_l
+            cur_h, cur_w = ch, cw
+        px, py = _pair(sp.padding)
+        crop = _pair(sp.crop) if sp.crop is not None else None
+        out_h, out_w = crop if crop is not None else (cur_h + 2 * py, cur_w + 2 * px)
+        return dict(rs=(rs_h, rs_w), off=(off_y, off_x), cur=(cur_h, cur_w), pad=(px, py), crop=crop,
+                    out=(out_h, out_w))
+
+    def draw_params(self, batch: int, h: int, w: int):
+        """Next ``(top, left, flip)`` from the replayed torch generator (needs ``seed=``)."""
+        if self._rng is None:
+            raise RuntimeError("BatchTransform was built without a seed; pass params= explicitly")
+        g = self.geometry(h, w)
+        return self._rng.draw(batch, g["cur"][0], g["cur"][1], g["crop"], g["pad"], self.spec.flip_p)
+
+    def _params_to_device(self, params, batch: int):
+        top, left, flip = params
+        if all(isinstance(t, torch.Tensor) and t.is_cuda for t in (top, left, flip) if t is not None):
+            conv = lambda t, dt: None if t is None else t.to(device=self.device, dtype=dt).contiguous()
+            return conv(top, torch.int32), conv(left, torch.int32), conv(flip, torch.uint8)
+        # one pinned staging buffer, one async copy: [top i32 x B][left i32 x B][flip u8 x B]
+        host = torch.empty(9 * batch, dtype=torch.uint8, pin_memory=True)
+        hv = host.numpy()
+        hv[:4 * batch].view(np.int32)[:] = 0 if top is None else np.asarray(top, dtype=np.int32)
+        hv[4 * batch:8 * batch].view(np.int32)[:] = 0 if left is None else np.asarray(left, dtype=np.int32)
+        hv[8 * batch:] = 0 if flip is None else np.asarray(flip, dtype=np.uint8)
+        dev = host.to(self.device, non_blocking=True)
+        self._param_host = host  # keep the pinned source alive until the copy has run
+        return dev[:4 * batch].view(torch.int32), dev[4 * batch:8 * batch].view(torch.int32), dev[8 * batch:]
+
+    # -- the call --------------------------------------------------------------------------
+    def __call__(self, batch: torch.Tensor, params=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if batch.dtype != torch.uint8 or batch.dim() != 4:
+            raise TypeError(f"batch must be uint8 [B,H,W,C]; got {batch.dtype} {tuple(batch.shape)}")
+        sp = self.spec
+        if not batch.is_cuda:
+            batch = batch.to(self.device, non_blocking=True)
+        elif batch.device != self.device:
+            raise ValueError(f"batch is on {batch.device}, transform on {self.device}")
+        B, H, W, Cn = batch.shape
+        if batch.stride(3) != 1 or batch.stride(2) != Cn:
+            batch = batch.contiguous()
+        g = self.geometry(H, W)
+        out_h, out_w = g["out"]
+        if params is None and self._rng is not None and (g["crop"] is not None or sp.flip_p is not None):
+            params = self.draw_params(B, H, W)
+        top = left = flip = None
+        if params is not None:
+            top, left, flip = self._params_to_device(params, B)
+        if out is None:
+            out = torch.empty((B, Cn, out_h, out_w), dtype=sp.dtype, device=self.device)
+        else:
+            if tuple(out.shape) != (B, Cn, out_h, out_w) or out.dtype != sp.dtype or not out.is_contiguous() \
+                    or out.device != self.device:
+                raise ValueError("out must be a contiguous tensor of shape "
+                                 f"{(B, Cn, out_h, out_w)}, dtype {sp.dtype} on {self.device}")
+        lut = self.lut(Cn)
+        px, py = g["pad"]
+        ptr = lambda t: None if t is None else t.data_ptr()
+        L = N.lib()
+        with torch.cuda.device(self.device):
+            stream = N.current_stream_ptr(self.device)
+            if sp.resize is None and g["off"] == (0, 0) and sp.center_crop is None:
+                mode = N.PAD_MODES[sp.padding_mode] if (px or py) else N.PAD_MODES["none"]
+                rc = L.tb_transform_u8_nhwc_to_nchw(
+                    batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1),
+                    out.data_ptr(), N.dtype_code(sp.dtype), out_h, out_w,
+                    ptr(top), ptr(left), ptr(flip), py, px, mode, lut.data_ptr(), self.flags, stream)
+            else:
+                rs_h, rs_w = g["rs"]
+                ksx, bx, kx = self._resize_taps(W, rs_w) if rs_w != W else (0, None, None)
+                ksy, by, ky = self._resize_taps(H, rs_h) if rs_h != H else (0, None, None)
+                off_y, off_x = g["off"]
+                rc = L.tb_resize_bilinear_u8_nhwc_to_nchw(
+                    batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1), rs_h, rs_w,
+                    ptr(bx), ptr(kx), ksx, ptr(by), ptr(ky), ksy,
+                    out.data_ptr(), N.dtype_code(sp.dtype), out_h, out_w,
+                    ptr(top), ptr(left), ptr(flip), off_y - py, off_x - px, lut.data_ptr(), self.flags, stream)
+        N.check(rc)
+        return out
