@@ -28,6 +28,7 @@ extern "C" {
 #define TB_OK        0
 #define TB_EINVAL  (-22)   /* bad argument (shape, alignment, enum) */
 #define TB_ENOTSUP (-95)   /* valid request this build does not cover */
+#define TB_ENOENT   (-2)   /* LMDB: file or key not found */
 
 /* element types of outputs / logits */
 #define TB_F32  0
@@ -161,6 +162,24 @@ TB_API int tb_metrics_update(const void* logits, int logits_dtype, int64_t N, in
  *   x : DEVICE, n elements of dtype TB_F32/TB_BF16/TB_F16 ;  state : DEVICE double[2]
  */
 TB_API int tb_running_sum_update(const void* x, int dtype, int64_t n, double* state, tb_stream_t stream);
+
+/*
+ * Read-only LMDB reader (host side; liblmdb 0.9 data format, memcmp key order, main DB only).
+ * Replaces py-lmdb under torchbooster.lmdb.LMDBReader (torchbooster/lmdb.py:48-83:
+ * lmdb.open(path, readonly=True, lock=False, readahead=False) + txn.get(key)).
+ *   tb_lmdb_open   : path = LMDB directory (holding data.mdb) or the data file; TB_ENOENT if missing
+ *   tb_lmdb_get    : *data points into the read-only map (valid until close); TB_ENOENT if absent
+ *   tb_lmdb_gather : batched `reader[idx]` (key = decimal idx, torchbooster/lmdb.py:96-97) of n
+ *                    records of exactly record_bytes each into dst + i*record_bytes (host memory,
+ *                    ideally pinned) on `threads` host threads
+ */
+typedef struct tb_lmdb tb_lmdb;
+TB_API int     tb_lmdb_open(const char* path, tb_lmdb** out);
+TB_API int     tb_lmdb_close(tb_lmdb* db);
+TB_API int64_t tb_lmdb_entries(const tb_lmdb* db);
+TB_API int     tb_lmdb_get(const tb_lmdb* db, const void* key, int64_t klen, const void** data, int64_t* len);
+TB_API int     tb_lmdb_gather(const tb_lmdb* db, const int64_t* indices, int64_t n, int64_t record_bytes,
+                              void* dst, int threads);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,147 @@
+"""Parity of the CUDA metrics path: counts and confusion bins are bit-exact against the
+reference-pinned oracle; the accuracy quotient is the reference's float32 value exactly."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import metrics_oracle as MO
+from torchbooster_b200 import metrics as M
+
+pytestmark = pytest.mark.gpu
+
+
+def bf16_from_bits(bits):
+    return torch.from_numpy(np.ascontiguousarray(bits)).view(torch.bfloat16)
+
+
+def test_reference_golden(golden):
+    g = golden("metrics_reference.npz")
+    kat = torch.from_numpy(g["kat_logits"]).cuda()
+    for lab in range(4):
+        labels = torch.full((kat.shape[0],), lab, dtype=torch.int64, device="cuda")
+        acc = M.accuracy(kat, labels)
+        assert acc.dtype == torch.float32 and acc.dim() == 0 and acc.is_cuda
+        assert acc.cpu().numpy() == g[f"kat_accuracy_label{lab}"]
+    cm = M.confusion_matrix(kat, torch.zeros(kat.shape[0], dtype=torch.int64, device="cuda"))
+    assert cm[0].cpu().tolist() == np.bincount(g["kat_argmax"], minlength=4).tolist()
+    a = M.accuracy(torch.from_numpy(g["a_logits"]).cuda(), torch.from_numpy(g["a_labels"]).cuda())
+    assert a.cpu().numpy() == g["a_accuracy"]
+    b = M.accuracy(bf16_from_bits(g["b_logits_bf16_bits"]).cuda(), torch.from_numpy(g["b_labels"]).cuda())
+    assert b.cpu().numpy() == g["b_accuracy"]
+    c = M.Accuracy()(torch.from_numpy(g["c_logits"]).cuda(), torch.from_numpy(g["c_labels"]).cuda())
+    assert c.cpu().numpy() == g["c_accuracy"] == 5.0
+    d = M.accuracy(torch.from_numpy(g["d_logits"]).cuda(), torch.from_numpy(g["d_labels"]).cuda(), dim=0)
+    assert d.cpu().numpy() == g["d_accuracy_dim0"]
+
+
+def check_state(logits, labels, k, C):
+    st = M.MetricState(C, k=k, device="cuda")
+    st.update(logits.cuda(), labels.cuda())
+    res = st.compute()
+    rank = MO.label_rank(logits.float(), labels)
+    valid = ((labels >= 0) & (labels < C)).numpy()
+    assert res["n"] == logits.shape[0]
+    assert res["correct_1"] == int(((rank < 1) & valid).sum())
+    assert res[f"correct_{k}"] == int(((rank < k) & valid).sum())
+    assert res["invalid_labels"] == int((~valid).sum())
+    assert np.array_equal(res["confusion"].cpu().numpy(), MO.confusion(logits.float(), labels, C))
+    return res
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("N,C", [(1, 1000), (1000, 1000), (513, 10), (64, 7), (33, 1), (100, 1003), (257, 4099)])
+def test_counts_and_confusion(dtype, N, C):
+    gen = torch.Generator().manual_seed(N * 31 + C)
+    logits = torch.randn(N, C, generator=gen).to(dtype)      # 16-bit values tie often: stresses the rank rule
+    labels = torch.randint(0, C, (N,), generator=gen)
+    check_state(logits, labels, 5, C)
+
+
+def test_ties_nan_inf_signed_zero_and_invalid_labels():
+    nan, inf = float("nan"), float("inf")
+    neg_nan = nan   # replaced below by a negative NaN with a payload, bit for bit
+    rows = torch.tensor([[2., 2, 2, 2, 2], [nan, 5, 1, nan, 0], [1, nan, 0, 0, 0], [-0.0, 0.0, -1, -2, -3],
+                         [0.0, -0.0, -1, -2, -3], [-inf] * 5, [inf, nan, inf, 1, 0], [1, 2, 3, 4, 5],
+                         [neg_nan, 9, 9, 9, 9], [3, neg_nan, nan, 3, 3]])
+    bits = rows.view(torch.int32)
+    bits[8, 0] = int(np.array([0xFFC00001], np.uint32).view(np.int32)[0])
+    bits[9, 1] = int(np.array([0xFF800123], np.uint32).view(np.int32)[0])
+    bits[9, 2] = 0x7F800001
+    rows = torch.cat([rows, rows, rows])
+    labels = torch.cat([torch.arange(10) % 5, (torch.arange(10) + 2) % 5, torch.tensor([5, -1, 0, 1, 2, 3, 4, 99, 0, 1])])
+    for dtype in (torch.float32, torch.bfloat16, torch.float16):
+        check_state(rows.to(dtype), labels, 2, 5)
+
+
+def test_unaligned_rows_and_strided_view():
+    gen = torch.Generator().manual_seed(4)
+    base = torch.randn(50, 40, generator=gen)
+    for dtype in (torch.float32, torch.bfloat16):
+        big = base.to(dtype).cuda()
+        view = big[:, 3:36]                      # row stride 40, 33 classes, rows start off 16-byte boundaries
+        labels = torch.randint(0, 33, (50,), generator=gen)
+        st = M.MetricState(33, k=3, device="cuda")
+        st.update(view, labels.cuda())
+        res = st.compute()
+        rank = MO.label_rank(view.float().cpu(), labels)
+        assert res["correct_1"] == int((rank < 1).sum()) and res["correct_3"] == int((rank < 3).sum())
+        assert np.array_equal(res["confusion"].cpu().numpy(), MO.confusion(view.float().cpu(), labels, 33))
+
+
+def test_accumulation_over_batches_and_loss():
+    gen = torch.Generator().manual_seed(8)
+    st = M.MetricState(10, k=3, device="cuda")
+    dra = M.DeviceRunningAverage("cuda")
+    all_l, all_y, losses = [], [], []
+    for _ in range(5):
+        l = torch.randn(97, 10, generator=gen); y = torch.randint(0, 10, (97,), generator=gen)
+        loss = torch.rand((), generator=gen)
+        st.update(l.cuda(), y.cuda()); st.update_loss(loss.cuda()); dra.update(loss.cuda())
+        all_l.append(l); all_y.append(y); losses.append(float(loss))
+    res = st.compute()
+    L, Y = torch.cat(all_l), torch.cat(all_y)
+    assert res["n"] == 485 and res["correct_1"] == MO.topk_correct(L, Y, 1) and res["correct_3"] == MO.topk_correct(L, Y, 3)
+    assert np.array_equal(res["confusion"].cpu().numpy(), MO.confusion(L, Y, 10))
+    assert abs(res["loss"] - float(np.mean(np.array(losses, np.float64)))) < 1e-12
+    assert dra.current == 5 and abs(dra.value - res["loss"]) < 1e-15
+    per_sample = torch.rand(1000, generator=gen)
+    st.reset(); st.update_loss(per_sample.cuda())
+    assert abs(st.compute()["loss"] - float(per_sample.double().mean())) < 1e-12
+
+
+def test_topk_matches_torch_topk_without_ties():
+    gen = torch.Generator().manual_seed(1)
+    logits = torch.randn(4096, 1000, generator=gen)
+    labels = torch.randint(0, 1000, (4096,), generator=gen)
+    want = (logits.topk(5, -1).indices == labels[:, None]).any(-1).float().mean()
+    got = M.top_k_accuracy(logits.cuda(), labels.cuda(), k=5)
+    assert got.cpu() == want
+
+
+def test_full_size_c5_properties():
+    """BASELINE config 5 scale (1M x 1000 would be 4 GB; per-rank share 125k x 1000 here): the
+    confusion matrix row sums equal the label histogram, its trace equals correct_1, and
+    permuting the samples leaves every accumulator unchanged."""
+    N, C = 125_000, 1000
+    gen = torch.Generator(device="cuda").manual_seed(1234)
+    logits = torch.randn(N, C, device="cuda", generator=gen)
+    labels = torch.randint(0, C, (N,), device="cuda", generator=gen)
+    labels[::3] = logits[::3].argmax(-1)
+    st = M.MetricState(C, k=5, device="cuda")
+    st.update(logits, labels)
+    res = st.compute()
+    cm = res["confusion"]
+    assert res["n"] == N and int(cm.sum()) == N
+    assert torch.equal(cm.sum(1), torch.bincount(labels, minlength=C))
+    assert int(cm.diagonal().sum()) == res["correct_1"] == int((logits.argmax(-1) == labels).sum())
+    assert res["correct_5"] >= res["correct_1"]
+    perm = torch.randperm(N, device="cuda", generator=gen)
+    st2 = M.MetricState(C, k=5, device="cuda")
+    st2.update(logits[perm], labels[perm])
+    assert torch.equal(st2.buffer, st.buffer)
+    assert float(M.accuracy(logits, labels)) == float(torch.tensor(res["correct_1"]) / N)
+
+
+def test_cpu_tensors_are_rejected():
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        M.accuracy(torch.randn(4, 3), torch.zeros(4, dtype=torch.int64))

@@ -1,0 +1,85 @@
+"""Parity of the CUDA resize path against Pillow (through torchvision's PIL backend): bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import transform_oracle as TO
+from torchbooster_b200.transforms import BatchTransform, TransformSpec
+
+pytestmark = pytest.mark.gpu
+IMAGENET = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+
+
+def same(a, b):
+    a, b = a.cpu().contiguous(), b.cpu().contiguous()
+    view = {torch.float32: torch.int32, torch.bfloat16: torch.int16, torch.float16: torch.int16}[a.dtype]
+    return a.dtype == b.dtype and a.shape == b.shape and torch.equal(a.view(view), b.view(view))
+
+
+def test_golden_c4(golden):
+    g = golden("transform_torchvision.npz")
+    bt = BatchTransform(TransformSpec(resize=32, center_crop=32, mean=IMAGENET[0], std=IMAGENET[1]), device="cuda")
+    assert same(bt(torch.from_numpy(g["c4_in"]).cuda()), torch.from_numpy(g["c4_out"]))
+
+
+def test_golden_pillow_resize(golden):
+    """Raw resize results: table = identity-like ToTensor, compare bytes via x/255 table inverse."""
+    g = golden("resize_pillow.npz")
+    for i in range(int(g["n_cases"])):
+        src, want = g[f"r{i}_in"], g[f"r{i}_out"]
+        if src.ndim == 2:
+            src, want = src[:, :, None], want[:, :, None]
+        bt = BatchTransform(TransformSpec(resize=want.shape[:2]), device="cuda")
+        out = bt(torch.from_numpy(src[None]).cuda())
+        ref = torch.from_numpy(want).permute(2, 0, 1)[None].float().div(255)
+        assert same(out, ref), f"case {i}"
+
+
+CASES = [
+    # B, H, W, C, resize, center_crop, dtype
+    (2, 512, 512, 3, 256, 256, torch.float32),       # C4
+    (2, 375, 500, 3, 256, 256, torch.float32),       # adain.py on a COCO-shaped image
+    (1, 480, 640, 3, 512, 512, torch.bfloat16),      # upscale
+    (2, 300, 200, 3, (384, 256), None, torch.float32),
+    (2, 64, 48, 1, 32, None, torch.float32),
+    (1, 50, 50, 3, 20, 32, torch.float32),           # centre crop larger than the image: zero fill
+    (1, 41, 57, 3, (41, 30), None, torch.float32),   # horizontal pass only
+    (1, 41, 57, 3, (19, 57), None, torch.float32),   # vertical pass only
+    (1, 1000, 900, 3, 64, 64, torch.float32),        # large reduction: 31-tap filters
+    (1, 37, 61, 3, None, 24, torch.float16),         # centre crop only
+]
+
+
+@pytest.mark.parametrize("B,H,W,C,resize,cc,dtype", CASES)
+def test_resize_grid_vs_oracle(B, H, W, C, resize, cc, dtype):
+    rng = np.random.default_rng(H * 7 + W)
+    batch = rng.integers(0, 256, (B, H, W, C), dtype=np.uint8)
+    mean, std = (IMAGENET if C == 3 else ((.5,), (.5,)))
+    want = TO.transform_batch(batch, resize=resize, center_crop=cc, mean=mean, std=std, dtype=dtype)
+    bt = BatchTransform(TransformSpec(resize=resize, center_crop=cc, mean=mean, std=std, dtype=dtype), device="cuda")
+    assert same(bt(torch.from_numpy(batch).cuda()), want)
+
+
+def test_resize_then_random_crop_flip():
+    rng = np.random.default_rng(77)
+    B = 3
+    batch = rng.integers(0, 256, (B, 90, 120, 3), dtype=np.uint8)
+    top = np.array([0, 4, 8], np.int32); left = np.array([21, 0, 7], np.int32); flip = np.array([1, 1, 0], np.uint8)
+    want = TO.transform_batch(batch, resize=48, crop_top=top, crop_left=left, out_size=(40, 43), flip=flip,
+                              mean=IMAGENET[0], std=IMAGENET[1])
+    bt = BatchTransform(TransformSpec(resize=48, crop=(40, 43), flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1]),
+                        device="cuda")
+    assert same(bt(torch.from_numpy(batch).cuda(), params=(top, left, flip)), want)
+
+
+def test_resize_linearity_property_full_size():
+    """Full C4 size (32 x 512x512): a constant image resizes to the same constant, and resizing
+    is monotone: img_a <= img_b pointwise implies out_a <= out_b (non-negative taps)."""
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    a = torch.randint(0, 200, (32, 512, 512, 3), dtype=torch.uint8, device="cuda", generator=gen)
+    b = a + torch.randint(0, 56, a.shape, dtype=torch.uint8, device="cuda", generator=gen)
+    bt = BatchTransform(TransformSpec(resize=256, center_crop=256), device="cuda")
+    oa, ob = bt(a), bt(b)
+    assert bool((oa <= ob).all())
+    c = torch.full((2, 512, 512, 3), 77, dtype=torch.uint8, device="cuda")
+    assert bool((bt(c) == torch.tensor(77.0).div(255)).all())

@@ -1,0 +1,118 @@
+"""LMDBReader drop-in over this package's own reader/writer (py-lmdb is absent: the contract is
+the behaviour cited from torchbooster/lmdb.py; parity against a py-lmdb-written file is UNPINNED)."""
+import os
+
+import numpy as np
+import pytest
+
+from torchbooster_b200.dataset import BaseDataset, Split
+from torchbooster_b200.lmdb import LMDBReader, write_image_lmdb, write_lmdb
+
+
+@pytest.fixture(scope="module")
+def image_db(tmp_path_factory):
+    d = tmp_path_factory.mktemp("db")
+    rng = np.random.default_rng(0)
+    imgs = rng.integers(0, 256, (200, 32, 32, 3), dtype=np.uint8)     # 3072-byte values: overflow pages
+    write_image_lmdb(str(d / "cifar"), imgs, labels=np.arange(200) % 10)
+    return str(d / "cifar"), imgs
+
+
+def test_reader_contract(image_db):
+    path, imgs = image_db
+    r = LMDBReader(path)
+    assert (r.path, r.map_size, r.max_readers, r.env, r.length) == (path, 1024 ** 4, 126, None, None)
+    assert len(r) == 200 and r.env is None          # __len__ opens and closes (fork safety, lmdb.py:85-90)
+    assert r[0] == imgs[0].tobytes() and r.env is not None     # lazy open on first get
+    assert r.get(b"199") == imgs[199].tobytes()
+    assert [len(v) for v in list(r)[:3]] == [3072] * 3
+    with pytest.raises(KeyError, match="does not contain key"):
+        r.get(b"200")
+    r.close()
+    assert r.env is None
+    with LMDBReader(path) as ctx:
+        assert ctx.get(b"label/13") == b"3"
+    assert ctx.env is None
+
+
+def test_missing_database_raises_ioerror(tmp_path):
+    with pytest.raises(IOError, match="Could not open lmdb dataset"):
+        LMDBReader(str(tmp_path / "absent")).open()
+    (tmp_path / "junk").mkdir()
+    (tmp_path / "junk" / "data.mdb").write_bytes(b"\0" * 8192)
+    with pytest.raises(IOError):
+        LMDBReader(str(tmp_path / "junk")).open()
+
+
+def test_length_defaults_to_zero_without_length_key(tmp_path):
+    write_lmdb(str(tmp_path / "nolen"), [(b"0", b"abc")])
+    r = LMDBReader(str(tmp_path / "nolen"))
+    r.open()
+    assert r.length == 0 and r[0] == b"abc"
+
+
+def test_small_values_deep_tree_and_key_order(tmp_path):
+    items = [(f"{i}".encode(), f"value-{i}".encode() * (1 + i % 5)) for i in range(120_000)]
+    items += [(b"length", b"120000"), (b"\x00\xff", b"lo"), (b"\xff\xfe", b"hi"), (b"k" * 511, b"longkey")]
+    write_lmdb(str(tmp_path / "deep"), items)
+    r = LMDBReader(str(tmp_path / "deep"))
+    assert len(r) == 120_000
+    for i in (0, 1, 9, 10, 99_999, 119_999, 54_321):
+        assert r[i] == f"value-{i}".encode() * (1 + i % 5)
+    assert r.get(b"\x00\xff") == b"lo" and r.get(b"\xff\xfe") == b"hi" and r.get(b"k" * 511) == b"longkey"
+    for missing in (b"120000", b"", b"-1", b"k" * 510, b"\xff\xff"):
+        with pytest.raises(KeyError):
+            r.get(missing)
+
+
+def test_empty_database(tmp_path):
+    write_lmdb(str(tmp_path / "empty"), [])
+    r = LMDBReader(str(tmp_path / "empty"))
+    assert len(r) == 0
+    with pytest.raises(KeyError):
+        r.get(b"0")
+
+
+def test_get_batch_gathers_records(image_db):
+    path, imgs = image_db
+    r = LMDBReader(path)
+    idx = [5, 0, 199, 5, 42]
+    out = r.get_batch(idx, 3072, threads=3)
+    assert out.shape == (5, 3072) and np.array_equal(out.numpy().reshape(5, 32, 32, 3), imgs[idx])
+    with pytest.raises(KeyError):
+        r.get_batch([1, 200], 3072)
+    with pytest.raises(ValueError, match="not 100 bytes"):
+        r.get_batch([1], 100)
+    assert r.get_batch([], 3072).shape == (0, 3072)
+
+
+def test_reader_survives_fork(image_db):
+    path, imgs = image_db
+    r = LMDBReader(path)
+    assert r[3] == imgs[3].tobytes()
+    pid = os.fork()
+    if pid == 0:
+        ok = r[4] == imgs[4].tobytes()      # child reopens its own map
+        os._exit(0 if ok else 1)
+    assert os.waitpid(pid, 0)[1] == 0
+    assert r[5] == imgs[5].tobytes()
+
+
+def test_base_dataset_contract(image_db):
+    path, imgs = image_db
+    ds = BaseDataset(path)
+    assert (ds.path, ds.transform, ds.map_size, ds.max_readers) == (path, None, 1024 * 4, 126)
+    assert isinstance(ds.lmdb_reader, LMDBReader) and len(ds) == 200
+    with pytest.raises(NotImplementedError, match="__getitem__"):
+        ds[0]
+    with pytest.raises(NotImplementedError, match="prepare"):
+        BaseDataset.prepare()
+    assert Split("validation") is Split.VALID
+
+    class Cifar(BaseDataset):
+        def __getitem__(self, idx):
+            img = np.frombuffer(self.lmdb_reader[idx], np.uint8).reshape(32, 32, 3)
+            return img, int(self.lmdb_reader.get(f"label/{idx}".encode()))
+
+    x, y = Cifar(path)[17]
+    assert np.array_equal(x, imgs[17]) and y == 7

@@ -13,7 +13,7 @@ _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libtorchbooster_b200.so"
 _lock = threading.Lock()
 _lib = None
 
-TB_OK, TB_EINVAL, TB_ENOTSUP = 0, -22, -95
+TB_OK, TB_EINVAL, TB_ENOTSUP, TB_ENOENT = 0, -22, -95, -2
 TB_F32, TB_BF16, TB_F16 = 0, 1, 2
 PAD_MODES = {"none": 0, "constant": 1, "reflect": 2, "edge": 3, "symmetric": 4}
 LUT_TO_TENSOR, LUT_NORMALIZE, LUT_ONE_MINUS, LUT_NORMALIZE_ONE_MINUS = 0, 1, 2, 3
@@ -36,6 +36,11 @@ SIGNATURES = {
                                                   _vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp]),
     "tb_metrics_update": (_i32, [_vp, _i32, _i64, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
     "tb_running_sum_update": (_i32, [_vp, _i32, _i64, _vp, _vp]),
+    "tb_lmdb_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),
+    "tb_lmdb_close": (_i32, [_vp]),
+    "tb_lmdb_entries": (_i64, [_vp]),
+    "tb_lmdb_get": (_i32, [_vp, C.c_char_p, _i64, C.POINTER(_vp), C.POINTER(_i64)]),
+    "tb_lmdb_gather": (_i32, [_vp, _vp, _i64, _i64, _vp, _i32]),
 }
 
 

@@ -46,6 +46,7 @@ int tb_device(TbDevice* out);
 // ---------------------------------------------------------------------------------------------
 // device-side helpers
 // ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
 __device__ __forceinline__ uint32_t tb_smem_addr(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
@@ -89,3 +90,4 @@ __device__ __forceinline__ void tb_st_cs_v4(void* p, uint4 v) {
     asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                  : "memory");
 }
+#endif  // __CUDACC__
