@@ -49,7 +49,9 @@ extern "C" {
 #define TB_LUT_NORMALIZE_ONE_MINUS 3  /* 1 - (fl(x)/255 - mean)/std */
 
 /* flags */
-#define TB_FLAG_FORCE_GENERIC 1  /* tests: skip the staged fast path, use the one-gather-per-element kernel */
+#define TB_FLAG_FORCE_GENERIC 1  /* tests: skip the streaming path, use the one-gather-per-pixel kernel */
+#define TB_FLAG_FORCE_STREAM  2  /* tests: take the streaming path even where the gather kernel is the better launch */
+#define TB_FLAG_NO_PDL        4  /* launch without programmatic stream serialization */
 
 typedef struct CUstream_st* tb_stream_t;   /* == cudaStream_t */
 

@@ -28,7 +28,7 @@ def same(a: torch.Tensor, b: torch.Tensor) -> bool:
 def run_both_paths(spec, batch, params):
     """Staged fast path (when eligible) and the gather path must both equal the oracle."""
     outs = []
-    for flags in (0, N.FLAG_FORCE_GENERIC):
+    for flags in (0, N.FLAG_FORCE_GENERIC, N.FLAG_FORCE_STREAM, N.FLAG_FORCE_STREAM | N.FLAG_NO_PDL):
         bt = BatchTransform(spec, device="cuda")
         bt.flags = flags
         outs.append(bt(torch.from_numpy(batch).cuda(), params=params))

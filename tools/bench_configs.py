@@ -1,0 +1,117 @@
+#!/usr/bin/env python
+"""Kernel-level timing of every BASELINE.json config (C1..C5) through the C ABI: CUDA events,
+inputs rotated over more than L2 of distinct buffers, algorithmic bytes from SURVEY.md 8(d).
+One JSON line per case on stdout.  Development tool; the headline line comes from bench.py."""
+import argparse
+import json
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+from torchbooster_b200 import _native as N                      # noqa: E402
+from torchbooster_b200.metrics import MetricState                # noqa: E402
+from torchbooster_b200.transforms import BatchTransform, CropFlipParams, TransformSpec  # noqa: E402
+
+IMAGENET = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+CIFAR = ((0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010))
+PEAK = 6428.4
+try:
+    PEAK = float(json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["hbm_gbs"])
+except Exception:
+    pass
+L2 = 126 << 20
+
+
+def time_loop(fn, iters, warm=5):
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def transform_case(name, B, H, W, spec_kw, alg_bytes, iters, flags=0, params=True):
+    dev = torch.device("cuda", 0)
+    spec = TransformSpec(**spec_kw)
+    bt = BatchTransform(spec, device=dev)
+    bt.flags = flags
+    nbuf = min(24, max(3, -(-4 * L2 // (B * H * W * 3))))
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    srcs = [torch.randint(0, 256, (B, H, W, 3), dtype=torch.uint8, device=dev, generator=gen) for _ in range(nbuf)]
+    g = bt.geometry(H, W)
+    prm = None
+    if params:
+        px, py = g["pad"]
+        t, l, f = CropFlipParams(42).draw(B, g["cur"][0], g["cur"][1], g["crop"], g["pad"], spec.flip_p)
+        prm = tuple(torch.from_numpy(a).to(dev) for a in (t, l, f))
+    out = [torch.empty((B, 3) + g["out"], dtype=spec.dtype, device=dev) for _ in range(2)]
+    ms = time_loop(lambda i: bt(srcs[i % nbuf], params=prm, out=out[i & 1]), iters)
+    gbs = alg_bytes * B / (ms * 1e-3) / 1e9
+    print(json.dumps({"case": name, "B": B, "ms": ms, "images_per_s": B / (ms * 1e-3), "alg_GBps": gbs,
+                      "frac_measured": gbs / PEAK, "frac_nominal": gbs / 8000, "nbuf": nbuf, "flags": flags}), flush=True)
+
+
+def metrics_case(name, n, c, dtype, iters):
+    dev = torch.device("cuda", 0)
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    es = 4 if dtype == torch.float32 else 2
+    nbuf = min(8, max(2, -(-4 * L2 // (n * c * es))))
+    logits = [torch.randn(n, c, device=dev, generator=gen).to(dtype) for _ in range(nbuf)]
+    labels = [torch.randint(0, c, (n,), device=dev, generator=gen) for _ in range(nbuf)]
+    st = MetricState(c, k=5, device=dev)
+    ms = time_loop(lambda i: st.update(logits[i % nbuf], labels[i % nbuf]), iters)
+    gbs = n * (c * es + 8) / (ms * 1e-3) / 1e9
+    print(json.dumps({"case": name, "N": n, "C": c, "ms": ms, "samples_per_s": n / (ms * 1e-3), "alg_GBps": gbs,
+                      "frac_measured": gbs / PEAK, "frac_nominal": gbs / 8000, "nbuf": nbuf}), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="")
+    ap.add_argument("--quick", action="store_true")
+    a = ap.parse_args()
+    want = lambda n: not a.only or any(n.startswith(x) for x in a.only.split(","))
+    c2 = dict(crop=224, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
+    if want("c2"):
+        knob = lambda warps=0, rows=0, extra=0: extra | (warps << 16) | (rows << 24)
+        cases = [("c2_default", 0), ("c2_no_pdl", N.FLAG_NO_PDL), ("c2_w11_r8", knob(11, 8)), ("c2_w22_r4", knob(22, 4)),
+                 ("c2_w10_r8", knob(10, 8)), ("c2_w8_r12", knob(8, 12)), ("c2_w14_r6", knob(14, 6)), ("c2_generic", 1)]
+        if a.quick:
+            cases = cases[:3]
+        for label, flags in cases:
+            transform_case(label, 512, 256, 256, c2, 224 * 224 * 9, 200, flags)
+        transform_case("c2_default_B2048", 2048, 256, 256, c2, 224 * 224 * 9, 60, 0)
+        transform_case("c2_fp32_out", 512, 256, 256, dict(c2, dtype=torch.float32), 224 * 224 * 15, 200)
+        transform_case("c2_fp32_out_w10_r4", 512, 256, 256, dict(c2, dtype=torch.float32), 224 * 224 * 15, 200, knob(10, 4))
+    if want("c1"):
+        c1 = dict(crop=32, padding=4, padding_mode="reflect", flip_p=.5, mean=CIFAR[0], std=CIFAR[1])
+        for bsz in (256, 2048):
+            transform_case(f"c1_cifar_b{bsz}", bsz, 32, 32, c1, 15360, 300)
+            transform_case(f"c1_cifar_b{bsz}_stream", bsz, 32, 32, c1, 15360, 300, flags=N.FLAG_FORCE_STREAM)
+            transform_case(f"c1_cifar_b{bsz}_generic", bsz, 32, 32, c1, 15360, 300, flags=1)
+    if want("c3"):
+        c3 = dict(flip_p=.5, mean=[.5] * 3, std=[.5] * 3)
+        transform_case("c3_gen_b1024", 1024, 64, 64, c3, 61440, 300)
+        transform_case("c3_gen_b1024_generic", 1024, 64, 64, c3, 61440, 300, flags=1)
+    if want("c4"):
+        c4 = dict(resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1])
+        transform_case("c4_stt_b32", 32, 512, 512, c4, 1572864, 200, params=False)
+        transform_case("c4_stt_b256", 256, 512, 512, c4, 1572864, 50, params=False)
+    if want("c5"):
+        metrics_case("c5_fp32_125k", 125_000, 1000, torch.float32, 50)
+        metrics_case("c5_bf16_125k", 125_000, 1000, torch.bfloat16, 50)
+        metrics_case("c5_fp32_1000", 1000, 1000, torch.float32, 300)
+        metrics_case("c5_fp32_512", 512, 1000, torch.float32, 300)
+
+
+if __name__ == "__main__":
+    main()

@@ -17,7 +17,7 @@ TB_OK, TB_EINVAL, TB_ENOTSUP, TB_ENOENT = 0, -22, -95, -2
 TB_F32, TB_BF16, TB_F16 = 0, 1, 2
 PAD_MODES = {"none": 0, "constant": 1, "reflect": 2, "edge": 3, "symmetric": 4}
 LUT_TO_TENSOR, LUT_NORMALIZE, LUT_ONE_MINUS, LUT_NORMALIZE_ONE_MINUS = 0, 1, 2, 3
-FLAG_FORCE_GENERIC = 1
+FLAG_FORCE_GENERIC, FLAG_FORCE_STREAM, FLAG_NO_PDL = 1, 2, 4
 
 _i32, _i64, _vp = C.c_int, C.c_int64, C.c_void_p
 
@@ -110,3 +110,16 @@ def require_cuda(t, name: str):
 def current_stream_ptr(device) -> int:
     import torch
     return torch.cuda.current_stream(device).cuda_stream
+
+
+def cuda_device(device=None, allow_cpu: bool = False):
+    """Normalise to an indexed CUDA device (``cuda`` -> ``cuda:<current>``)."""
+    import torch
+    if device is None:
+        return torch.device("cuda", torch.cuda.current_device())
+    device = torch.device(device)
+    if device.type == "cuda":
+        return device if device.index is not None else torch.device("cuda", torch.cuda.current_device())
+    if allow_cpu and device.type == "cpu":
+        return device
+    raise RuntimeError(f"{device} is not a CUDA device: torchbooster_b200 runs on the GPU only (no CPU fallback)")

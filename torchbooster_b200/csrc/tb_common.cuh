@@ -86,6 +86,17 @@ __device__ __forceinline__ void tb_bulk_g2s(void* smem_dst, const void* gsrc, ui
                  : "memory");
 }
 
+// Generic-proxy reads of a shared-memory stage are ordered before the async-proxy (bulk copy)
+// writes that refill it.
+__device__ __forceinline__ void tb_fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// Programmatic dependent launch.  `wait` blocks until every kernel this launch depends on has
+// completed and its writes are visible (a no-op for a normal launch); it must precede the first
+// global-memory access.  `launch_dependents` lets the next PDL launch in the stream begin its
+// own pre-wait preamble.
+__device__ __forceinline__ void tb_grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void tb_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void tb_st_cs_v4(void* p, uint4 v) {
     asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                  : "memory");

@@ -65,13 +65,68 @@ struct Elem<TB_F16> {
     }
 };
 
+// ---- per-row accumulator ---------------------------------------------------------------------
+// The sweep keeps per lane: `cnt` (how many elements outrank the label), and the key and position
+// of the best vector seen (first one wins); the exact argmax index is resolved once per row by
+// re-reading that one vector.
+//
+// Rank counting runs on the float pipe.  For a label logit ly that is not NaN,
+//   j <  y counts when x_j >= ly  <=>  x_j > pred(ly)   (pred = next float below; NaN x_j counts)
+//   j >= y counts when x_j >  ly                         (NaN x_j counts)
+// so one "greater than or unordered" compare against a per-vector threshold does both; the one
+// vector that straddles y selects per element.  A NaN label logit takes the key-based route.
+__device__ __forceinline__ int tb_gtu(float x, float thr) {   // -1 when x > thr or unordered, else 0
+    int r;
+    asm("set.gtu.s32.f32 %0, %1, %2;" : "=r"(r) : "f"(x), "f"(thr));
+    return r;
+}
+__device__ __forceinline__ float tb_max_nan(float a, float b) {   // NaN-propagating max
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+
 struct RowAcc {
-    int best, bidx, cnt;
-    int ky, y;
+    int bestk, bj0, bn;     // key of the best vector, its first element index and length
+    int cnt;                // minus the number of elements that outrank the label
+    int y, ky;
+    float lo, hi;           // thresholds for j < y and j >= y
+    bool ynan;
+
+    __device__ __forceinline__ void init(float ly, int label) {
+        y = label;
+        ky = tb_key(ly);
+        ynan = ly != ly;
+        const float c = ly + 0.0f;
+        const uint32_t b = __float_as_uint(c);
+        hi = c;
+        if (b == 0xff800000u) lo = __uint_as_float(0x7fffffffu);            // >= -inf: everything counts
+        else if (b == 0u) lo = __uint_as_float(0x80000001u);                // below zero: -denorm_min
+        else lo = __uint_as_float((b & 0x80000000u) ? b + 1u : b - 1u);
+        bestk = INT_MIN; bj0 = INT_MAX; bn = 0; cnt = 0;
+    }
+    // scalar element (row head / tail, NaN-label rows)
     __device__ __forceinline__ void one(float x, int j) {
         const int k = tb_key(x);
-        cnt += (k > ky - (j < y ? 1 : 0)) ? 1 : 0;   // j<y: ties count; j>=y: strictly greater
-        if (k > best) { best = k; bidx = j; }
+        cnt -= (k > ky - (j < y ? 1 : 0)) ? 1 : 0;
+        if (k > bestk) { bestk = k; bj0 = j; bn = 1; }
+    }
+    template <int VE>
+    __device__ __forceinline__ void vec(const float* f, int j0) {
+        float m = tb_max_nan(f[0], f[1]);
+#pragma unroll
+        for (int e = 2; e < VE; ++e) m = tb_max_nan(m, f[e]);
+        const int k = tb_key(m);
+        if (k > bestk) { bestk = k; bj0 = j0; bn = VE; }
+        const int d = y - j0;
+        if ((unsigned)d < (unsigned)VE) {
+#pragma unroll
+            for (int e = 0; e < VE; ++e) cnt += tb_gtu(f[e], e < d ? lo : hi);
+        } else {
+            const float thr = d > 0 ? lo : hi;
+#pragma unroll
+            for (int e = 0; e < VE; ++e) cnt += tb_gtu(f[e], thr);
+        }
     }
 };
 
@@ -83,9 +138,12 @@ __global__ void __launch_bounds__(kMxThreads) tb_metrics_kernel(const void* __re
     using E = Elem<DT>;
     constexpr int VE = E::VE;
     constexpr int ES = 16 / VE;
+    constexpr int UN = 32 / VE;      // 16-byte loads per lane per batch: 8 for fp32, 4 for 16-bit types
     __shared__ unsigned int s_cnt[3];
     if (threadIdx.x < 3) s_cnt[threadIdx.x] = 0;
     __syncthreads();
+    tb_launch_dependents();
+    tb_grid_dependency_wait();      // first global access below (programmatic dependent launch)
 
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = (int64_t)blockIdx.x * kMxWarps + (threadIdx.x >> 5);
@@ -97,45 +155,46 @@ __global__ void __launch_bounds__(kMxThreads) tb_metrics_kernel(const void* __re
         if (y64 < 0 || y64 >= C) { inv += 1; continue; }
         const typename E::type* row = (const typename E::type*)logits + n * row_stride;
         RowAcc a;
-        a.y = (int)y64;
-        a.ky = tb_key(E::get(row, a.y));
-        a.best = INT_MIN; a.bidx = INT_MAX; a.cnt = 0;
+        a.init(E::get(row, (int)y64), (int)y64);
 
         const int mis = (int)(((uintptr_t)row & 15) / ES);          // elements past the previous 16-byte boundary
         const int jf = mis ? min(VE - mis, C) : 0;                  // head elements before the first aligned vector
         const int nfull = (C - jf) / VE;
         const int jt = jf + nfull * VE;                             // first tail element
-
-        if (lane < jf) a.one(E::get(row, lane), lane);
-
         const uint4* vp = reinterpret_cast<const uint4*>(row + jf);
-        int v = lane;
-        for (; v + 96 < nfull; v += 128) {
-            uint4 r[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) r[i] = __ldcs(vp + v + 32 * i);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                float f[VE];
-                E::unpack(r[i], f);
-                const int j0 = jf + (v + 32 * i) * VE;
-#pragma unroll
-                for (int e = 0; e < VE; ++e) a.one(f[e], j0 + e);
-            }
-        }
-        for (; v < nfull; v += 32) {
-            const uint4 r = __ldcs(vp + v);
-            float f[VE];
-            E::unpack(r, f);
-            const int j0 = jf + v * VE;
-#pragma unroll
-            for (int e = 0; e < VE; ++e) a.one(f[e], j0 + e);
-        }
-        if (jt + lane < C) a.one(E::get(row, jt + lane), jt + lane);   // tail: fewer than VE <= 32 elements
 
-        const int mx = __reduce_max_sync(0xffffffffu, a.best);
-        const int pred = __reduce_min_sync(0xffffffffu, a.best == mx ? a.bidx : INT_MAX);
-        const int rank = __reduce_add_sync(0xffffffffu, a.cnt);
+        if (a.ynan) {
+            // rare: the label's own logit is NaN -- everything through the key route
+            for (int j = lane; j < C; j += 32) a.one(E::get(row, j), j);
+        } else {
+            if (lane < jf) a.one(E::get(row, lane), lane);
+            // UN vectors per lane in flight at once (a 1000-class fp32 row is 250 vectors: one batch)
+            for (int v = lane; v < nfull; v += 32 * UN) {
+                uint4 r[UN];
+#pragma unroll
+                for (int i = 0; i < UN; ++i)
+                    if (v + 32 * i < nfull) r[i] = __ldcs(vp + v + 32 * i);
+#pragma unroll
+                for (int i = 0; i < UN; ++i) {
+                    if (v + 32 * i < nfull) {
+                        float f[VE];
+                        E::unpack(r[i], f);
+                        a.template vec<VE>(f, jf + (v + 32 * i) * VE);
+                    }
+                }
+            }
+            if (jt + lane < C) a.one(E::get(row, jt + lane), jt + lane);   // tail: fewer than VE <= 32 elements
+        }
+
+        const int mx = __reduce_max_sync(0xffffffffu, a.bestk);
+        int cand = INT_MAX;
+        if (a.bestk == mx) {
+            // first element of this lane's best vector that attains the maximum
+            for (int e = a.bn - 1; e >= 0; --e)
+                if (tb_key(E::get(row, a.bj0 + e)) == mx) cand = a.bj0 + e;
+        }
+        const int pred = __reduce_min_sync(0xffffffffu, cand);
+        const int rank = -__reduce_add_sync(0xffffffffu, a.cnt);
         if (lane == 0) {
             c1 += (rank < 1) ? 1u : 0u;
             ck += (rank < k) ? 1u : 0u;
@@ -198,15 +257,23 @@ extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N
     const int64_t cap = (int64_t)dev.sm_count * 8;   // 8 x 256 threads = full occupancy
     if (blocks > cap) blocks = cap;
     TB_REQUIRE(N / (blocks * kMxWarps) < ((int64_t)1 << 28), "tb_metrics_update: N too large for one launch");
-    cudaStream_t s = (cudaStream_t)stream;
     auto* cnt = reinterpret_cast<unsigned long long*>(counters);
     auto* cm = reinterpret_cast<unsigned long long*>(confusion);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3(kMxThreads);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
     if (logits_dtype == TB_F32)
-        tb_metrics_kernel<TB_F32><<<(unsigned)blocks, kMxThreads, 0, s>>>(logits, N, C, row_stride, labels, k, cnt, cm);
+        TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<TB_F32>, logits, N, C, row_stride, labels, k, cnt, cm));
     else if (logits_dtype == TB_BF16)
-        tb_metrics_kernel<TB_BF16><<<(unsigned)blocks, kMxThreads, 0, s>>>(logits, N, C, row_stride, labels, k, cnt, cm);
+        TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<TB_BF16>, logits, N, C, row_stride, labels, k, cnt, cm));
     else
-        tb_metrics_kernel<TB_F16><<<(unsigned)blocks, kMxThreads, 0, s>>>(logits, N, C, row_stride, labels, k, cnt, cm);
+        TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<TB_F16>, logits, N, C, row_stride, labels, k, cnt, cm));
     TB_LAUNCH_CHECK("tb_metrics_kernel");
     return TB_OK;
 }

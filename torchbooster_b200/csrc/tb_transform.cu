@@ -6,13 +6,14 @@
 //
 // Two kernels, same index map (DESIGN.md "transform"):
 //   * tb_xf_generic_kernel : one gather per output pixel, any C in [1,4], any geometry / padding.
-//   * tb_xf_staged_kernel  : the HBM-bound path for C == 3.  Persistent CTAs (one per SM); a
-//     producer warp streams the crop rows of a tile into a shared-memory ring with 1-D bulk
-//     async copies (TMA engine, cp.async.bulk -> SASS UBLKCP) signalled on mbarriers; consumer
-//     warps de-interleave / flip out of shared memory, look every byte up in a bank-conflict-free
-//     (32x lane-replicated) table and write 16-byte streaming stores to the three planes.
-//     Tiles whose crop window leaves the image (padding) take the gather route inside the same
-//     launch, so any parameter values are safe.
+//   * tb_xf_stream_kernel  : the HBM-bound path for C == 3.  One persistent CTA per SM.  Every
+//     warp streams its own tiles (a few crop rows of one image): it issues 1-D bulk async copies
+//     (TMA engine, cp.async.bulk -> SASS UBLKCP) of the rows into its private two-stage
+//     shared-memory ring, waits on its own mbarrier, de-interleaves / flips out of shared
+//     memory, looks every byte up in a lane-replicated table and writes 16-byte streaming stores
+//     to the three planes.  Warps never wait for each other, so they drift apart and cover each
+//     other's latencies.  Tiles whose crop window leaves the image (padding) take the gather
+//     route inside the same launch, so any parameter values are safe.
 // The arithmetic is a table lookup on purpose: see tb_lut.cu.
 #include "tb_common.cuh"
 
@@ -56,6 +57,7 @@ __device__ __forceinline__ int tb_fold(int i, int n, int mode, bool& inside) {
 template <typename T>
 __global__ void __launch_bounds__(256) tb_xf_generic_kernel(XfParams p, int blocks_per_image) {
     __shared__ T s_lut[4 * 256];
+    tb_grid_dependency_wait();
     const T* __restrict__ glut = (const T*)p.lut;
     for (int i = threadIdx.x; i < p.C * 256; i += blockDim.x) s_lut[i] = glut[i];
     __syncthreads();
@@ -82,192 +84,263 @@ __global__ void __launch_bounds__(256) tb_xf_generic_kernel(XfParams p, int bloc
 }
 
 // ------------------------------------------------------------------------------------------
-// staged: C == 3, persistent, bulk-copy ring + replicated table
+// streaming: C == 3, persistent, per-warp bulk-copy rings + lane-replicated table
 // ------------------------------------------------------------------------------------------
-constexpr int kXfThreads = 512;                 // warp 0 = producer, warps 1..15 = consumers
-constexpr int kXfConsumers = kXfThreads - 32;
-constexpr int kXfStages = 4;
-constexpr int kXfMaxRows = 256;
-constexpr int kXfStageBudget = 24 * 1024;       // target bytes per ring stage
-constexpr int kXfLutWords = 3 * 256 * 32;       // [c][entry][lane] 32-bit words = 96 KB
+// Shared-window map (byte addresses as seen by ld.shared).  A table row is 256 bytes (64 words)
+// per byte value, so the byte to look up drops into address bits 8-15 with ONE PRMT, and lane l
+// always reads word l (or 32 + l) of its row, i.e. its own bank: no bank conflicts whatever the
+// 32 byte values are.
+//   16-bit outputs (bf16 / fp16):
+//     [s0, 0x20000)       plain table copy (3 KiB), per-warp rings, mbarriers
+//     [0x20000, 0x30000)  rows: words 0-31 = {c0 | c1 << 16} per lane, words 32-63 = {c2 | c2 << 16}
+//   32-bit outputs (fp32):
+//     [s0, 0x10000)       plain table copy, per-warp rings, mbarriers
+//     [0x10000, 0x20000)  rows: words 0-31 = c0, words 32-63 = c1
+//     [0x20000, 0x30000)  rows: words 0-31 = c2
+constexpr uint32_t kXfSmemEnd = 0x30000u;
 
-struct XfStagedGeom {
-    int rows;          // output rows per tile
-    int rowbuf;        // bytes per staged row (multiple of 16)
-    int contiguous;    // crop rows are whole source rows back to back: one bulk copy per tile
-    int tiles_per_image;
-    int total_tiles;
-    int gpr;           // 16-byte output groups per row
-    uint32_t gpr_magic;
-};
+__device__ __forceinline__ uint32_t tb_lds32(uint32_t addr) {
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+__device__ __forceinline__ void tb_lds64(uint32_t addr, uint32_t& lo, uint32_t& hi) {
+    asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(addr));
+}
 
 template <typename T>
-struct XfPack;  // PX pixels of one channel -> one 16-byte store
+struct Xf;   // per output width: pixels per 16-byte store, table layout, packing
 template <>
-struct XfPack<float> {
+struct Xf<float> {
     static constexpr int PX = 4;
-    __device__ static __forceinline__ uint4 pack(const uint32_t* v) { return make_uint4(v[0], v[1], v[2], v[3]); }
+    static constexpr uint32_t kLow = 0x10000u;    // end of the ring region
+    static constexpr uint32_t kTab = 0x10000u;    // first table
     __device__ static __forceinline__ uint32_t widen(float f) { return __float_as_uint(f); }
-    __device__ static __forceinline__ float narrow(uint32_t w) { return __uint_as_float(w); }
+    // 16 x 16-byte stores per row: words 0-31 one channel, words 32-63 the next
+    __device__ static __forceinline__ void fill(uint32_t* tab, const uint32_t* plain, int tid, int nthreads) {
+        uint4* t4 = reinterpret_cast<uint4*>(tab);
+        for (int i = tid; i < 2 * 256 * 16; i += nthreads) {
+            const int t = i >> 12, e = (i >> 4) & 255, c = t * 2 + ((i >> 3) & 1);
+            if (c < 3) {
+                const uint32_t v = plain[c * 256 + e];
+                t4[i] = make_uint4(v, v, v, v);
+            }
+        }
+    }
+    __device__ static __forceinline__ uint32_t base(int c, int lane) {
+        return kTab + (c == 2 ? 0x10000u : 0u) + (c == 1 ? 128u : 0u) + lane * 4;
+    }
+    __device__ static __forceinline__ uint4 pack(const uint32_t* v, int) { return make_uint4(v[0], v[1], v[2], v[3]); }
+    __device__ static __forceinline__ float one(uint32_t w, int) { return __uint_as_float(w); }
 };
 template <>
-struct XfPack<uint16_t> {   // bf16 and fp16: the table already holds the rounded 16-bit pattern
+struct Xf<uint16_t> {   // bf16 and fp16: the table already holds the rounded 16-bit pattern
     static constexpr int PX = 8;
-    __device__ static __forceinline__ uint4 pack(const uint32_t* v) {
-        return make_uint4(__byte_perm(v[0], v[1], 0x5410), __byte_perm(v[2], v[3], 0x5410),
-                          __byte_perm(v[4], v[5], 0x5410), __byte_perm(v[6], v[7], 0x5410));
-    }
+    static constexpr uint32_t kLow = 0x20000u;
+    static constexpr uint32_t kTab = 0x20000u;
     __device__ static __forceinline__ uint32_t widen(uint16_t h) { return h; }
-    __device__ static __forceinline__ uint16_t narrow(uint32_t w) { return (uint16_t)w; }
+    __device__ static __forceinline__ void fill(uint32_t* tab, const uint32_t* plain, int tid, int nthreads) {
+        uint4* t4 = reinterpret_cast<uint4*>(tab);
+        for (int i = tid; i < 256 * 16; i += nthreads) {
+            const int e = i >> 4;
+            const uint32_t v = (i & 8) ? plain[512 + e] * 0x10001u : (plain[e] | (plain[256 + e] << 16));
+            t4[i] = make_uint4(v, v, v, v);
+        }
+    }
+    __device__ static __forceinline__ uint32_t base(int c, int lane) { return kTab + (c == 2 ? 128u : 0u) + lane * 4; }
+    __device__ static __forceinline__ uint4 pack(const uint32_t* v, int c) {
+        const uint32_t sel = c == 1 ? 0x7632u : 0x5410u;   // channel 1 lives in the high halves
+        return make_uint4(__byte_perm(v[0], v[1], sel), __byte_perm(v[2], v[3], sel), __byte_perm(v[4], v[5], sel),
+                          __byte_perm(v[6], v[7], sel));
+    }
+    __device__ static __forceinline__ uint16_t one(uint32_t w, int c) { return (uint16_t)(c == 1 ? w >> 16 : w); }
+};
+
+struct XfGeom {
+    int rows;                 // output rows per warp tile (<= 32: one bulk copy per lane)
+    int rowbuf;               // bytes per staged row (multiple of 16)
+    int contiguous;           // crop rows are whole source rows back to back: one bulk copy per tile
+    int tiles_per_image, total_tiles;
+    int gpr;                  // 16-byte output groups ("units") per row
+    uint32_t gpr_magic;
+    int step_r, step_g;       // 32 units further = (step_r rows, step_g groups) further
+    int tile_db, tile_dt;     // stride of the tile walk (all warps of the grid) as (images, tiles)
+    int stage_bytes;
+    uint32_t dyn_bytes;
 };
 
 template <typename T>
-__global__ void __launch_bounds__(kXfThreads, 1) tb_xf_staged_kernel(XfParams p, XfStagedGeom g) {
-    constexpr int PX = XfPack<T>::PX;
+__global__ void __launch_bounds__(768, 1) tb_xf_stream_kernel(XfParams p, XfGeom g) {
+    using X = Xf<T>;
+    constexpr int PX = X::PX;
     constexpr int NB = 3 * PX;            // source bytes per unit
     constexpr int NW = NB / 4;            // aligned words once shifted
     extern __shared__ __align__(128) uint8_t smem[];
-    uint32_t* lut32 = reinterpret_cast<uint32_t*>(smem);
-    uint8_t* ring = smem + kXfLutWords * 4;
-    uint64_t* full = reinterpret_cast<uint64_t*>(ring + (size_t)kXfStages * g.rows * g.rowbuf);
-    uint64_t* empty = full + kXfStages;
-    __shared__ T s_plain[3 * 256];
-
+    const uint32_t s0 = tb_smem_addr(smem);
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
+    const int nwarps = (int)blockDim.x >> 5;
+    const uint32_t plain_addr = (s0 + 15u) & ~15u;
+    const uint32_t ring0 = (plain_addr + 3072u + 127u) & ~127u;
+    const uint32_t bars_addr = ring0 + (uint32_t)(nwarps * 2 * g.stage_bytes);
+    // the launch must have provided the window this map assumes
+    if (bars_addr + (uint32_t)nwarps * 16u > X::kLow || s0 + g.dyn_bytes < kXfSmemEnd) asm volatile("trap;");
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + (bars_addr - s0)) + warp * 2;
+    uint32_t* plain = reinterpret_cast<uint32_t*>(smem + (plain_addr - s0));
+    uint32_t* tab = reinterpret_cast<uint32_t*>(smem + (X::kTab - s0));
+    const uint32_t my_ring = ring0 + (uint32_t)(warp * 2 * g.stage_bytes);
+    uint8_t* my_ring_ptr = smem + (my_ring - s0);
 
-    if (tid == 0) {
-        for (int s = 0; s < kXfStages; ++s) {
-            tb_mbar_init(&full[s], 1);
-            tb_mbar_init(&empty[s], kXfConsumers / 32);
-        }
+    if (lane == 0) {
+        tb_mbar_init(&full[0], 1);
+        tb_mbar_init(&full[1], 1);
         tb_mbar_fence_init();
     }
-    for (int i = tid; i < 3 * 256; i += kXfThreads) s_plain[i] = ((const T*)p.lut)[i];
-    __syncthreads();
+    __syncwarp();
+    // everything above touches no global memory: with programmatic dependent launch it overlaps
+    // the tail of the previous kernel in the stream
+    tb_launch_dependents();
+    tb_grid_dependency_wait();
 
-    const int stage_bytes = g.rows * g.rowbuf;
-
-    if (warp == 0) {
-        // ===== producer: one bulk copy per tile row, issued by lane r =====
-        int it = 0;
-        for (int t = blockIdx.x; t < g.total_tiles; t += gridDim.x, ++it) {
-            const int s = it % kXfStages;
-            const uint32_t ph = (it / kXfStages) & 1;
-            const int b = t / g.tiles_per_image;
-            const int y0 = (t - b * g.tiles_per_image) * g.rows;
+    // two cursors over this warp's tiles t = gw, gw + stride, ...: the load cursor runs two tiles
+    // ahead of the compute cursor
+    const int gw = blockIdx.x * nwarps + warp;
+    int tp = gw, bp = gw / g.tiles_per_image, tip = gw - bp * g.tiles_per_image;
+    int tc = tp, bc = bp, tic = tip;
+    const int tstride = g.tile_db * g.tiles_per_image + g.tile_dt;
+    auto advance = [&](int& t, int& b, int& ti) {
+        t += tstride;
+        b += g.tile_db;
+        ti += g.tile_dt;
+        if (ti >= g.tiles_per_image) { ti -= g.tiles_per_image; ++b; }
+    };
+    auto issue = [&](int stage) {
+        // bulk copies of tile (bp, tip) into `stage`; nothing is armed for tiles that leave the image
+        if (tp < g.total_tiles) {
+            const int y0 = tip * g.rows;
             const int nrows = min(g.rows, p.out_h - y0);
-            const int top = (p.top ? p.top[b] : 0) - p.pad_y;
-            const int left = (p.left ? p.left[b] : 0) - p.pad_x;
+            const int top = (p.top ? p.top[bp] : 0) - p.pad_y;
+            const int left = (p.left ? p.left[bp] : 0) - p.pad_x;
             const bool inside = top >= 0 && top + p.out_h <= p.H && left >= 0 && left + p.out_w <= p.W;
-            tb_mbar_wait(&empty[s], ph ^ 1);
-            if (!inside) {
-                if (lane == 0) tb_mbar_arrive(&full[s]);
-                continue;
-            }
-            const int boff = left * 3;
-            const uint8_t* gsrc = p.src + (int64_t)b * p.bs + (int64_t)(top + y0) * p.pitch + (boff & ~15);
-            uint8_t* sdst = ring + (size_t)s * stage_bytes;
-            if (g.contiguous) {
-                if (lane == 0) {
-                    const uint32_t len = (uint32_t)nrows * (uint32_t)g.rowbuf;
-                    tb_mbar_arrive_expect_tx(&full[s], len);
-                    tb_bulk_g2s(sdst, gsrc, len, &full[s]);
+            if (inside) {
+                const int boff = left * 3;
+                const uint8_t* gsrc = p.src + (int64_t)bp * p.bs + (int64_t)(top + y0) * p.pitch + (boff & ~15);
+                uint8_t* sdst = my_ring_ptr + stage * g.stage_bytes;
+                if (g.contiguous) {
+                    if (lane == 0) {
+                        const uint32_t len = (uint32_t)nrows * (uint32_t)g.rowbuf;
+                        tb_mbar_arrive_expect_tx(&full[stage], len);
+                        tb_bulk_g2s(sdst, gsrc, len, &full[stage]);
+                    }
+                } else {
+                    // 16-byte aligned superset of the crop row
+                    const uint32_t len = (uint32_t)(((boff & 15) + p.out_w * 3 + 15) & ~15);
+                    if (lane == 0) tb_mbar_arrive_expect_tx(&full[stage], len * (uint32_t)nrows);
+                    __syncwarp();
+                    if (lane < nrows)
+                        tb_bulk_g2s(sdst + (size_t)lane * g.rowbuf, gsrc + (int64_t)lane * p.pitch, len, &full[stage]);
                 }
-            } else {
-                const uint32_t len = (uint32_t)(((boff & 15) + p.out_w * 3 + 15) & ~15);
-                if (lane == 0) tb_mbar_arrive_expect_tx(&full[s], len * (uint32_t)nrows);
-                __syncwarp();
-                for (int r = lane; r < nrows; r += 32)
-                    tb_bulk_g2s(sdst + (size_t)r * g.rowbuf, gsrc + (int64_t)r * p.pitch, len, &full[s]);
             }
         }
-        return;
-    }
+        advance(tp, bp, tip);
+    };
+    // first two tiles are in flight while the table is built
+    issue(0);
+    issue(1);
 
-    // ===== consumers =====
-    const int ctid = tid - 32;
-    // replicate the table: lut32[(c*256+e)*32 + lane] = entry, every lane reads its own bank
-    for (int i = ctid; i < kXfLutWords; i += kXfConsumers) lut32[i] = XfPack<T>::widen(s_plain[i >> 5]);
-    asm volatile("bar.sync 1, %0;" ::"n"(kXfConsumers) : "memory");
-    const uint32_t* lutl = lut32 + lane;
+    for (int i = tid; i < 768; i += blockDim.x) plain[i] = X::widen(((const T*)p.lut)[i]);
+    __syncthreads();
+    X::fill(tab, plain, tid, blockDim.x);
+    __syncthreads();
 
-    int it = 0;
-    for (int t = blockIdx.x; t < g.total_tiles; t += gridDim.x, ++it) {
-        const int s = it % kXfStages;
-        const uint32_t ph = (it / kXfStages) & 1;
-        const int b = t / g.tiles_per_image;
-        const int y0 = (t - b * g.tiles_per_image) * g.rows;
+    const uint32_t base0 = X::base(0, lane), base1 = X::base(1, lane), base2 = X::base(2, lane);
+    const int64_t plane = (int64_t)p.out_h * p.out_w;
+    const int ur0 = (int)__umulhi((uint32_t)lane, g.gpr_magic);   // (row, group) of this lane's first unit
+    const int ug0 = lane - ur0 * g.gpr;
+
+    uint32_t phases = 0;     // bit s = parity to wait for on stage s
+    for (int it = 0; tc < g.total_tiles; ++it) {
+        const int stage = it & 1;
+        const int y0 = tic * g.rows;
         const int nrows = min(g.rows, p.out_h - y0);
-        const int top = (p.top ? p.top[b] : 0) - p.pad_y;
-        const int left = (p.left ? p.left[b] : 0) - p.pad_x;
-        const bool flip = p.flip ? (p.flip[b] != 0) : false;
+        const int top = (p.top ? p.top[bc] : 0) - p.pad_y;
+        const int left = (p.left ? p.left[bc] : 0) - p.pad_x;
+        const bool flip = p.flip ? (p.flip[bc] != 0) : false;
         const bool inside = top >= 0 && top + p.out_h <= p.H && left >= 0 && left + p.out_w <= p.W;
-        T* __restrict__ dimg = (T*)p.dst + (int64_t)b * 3 * p.out_h * p.out_w;
-        const int64_t plane = (int64_t)p.out_h * p.out_w;
-
-        tb_mbar_wait(&full[s], ph);
+        T* __restrict__ dimg = (T*)p.dst + (int64_t)bc * 3 * plane;
 
         if (inside) {
-            const uint8_t* stage = ring + (size_t)s * stage_bytes;
-            const int a = (left * 3) & 15;
+            tb_mbar_wait(&full[stage], (phases >> stage) & 1u);
+            phases ^= 1u << stage;
+            const uint32_t sbase = my_ring + (uint32_t)(stage * g.stage_bytes);
             const int units = nrows * g.gpr;
-            for (int u = ctid; u < units; u += kXfConsumers) {
-                const int r = (int)__umulhi((uint32_t)u, g.gpr_magic);
-                const int gq = u - r * g.gpr;
-                // first source byte of this unit inside the staged row
-                const int start = a + 3 * (flip ? (p.out_w - PX - gq * PX) : gq * PX);
-                const uint32_t* wp = reinterpret_cast<const uint32_t*>(stage + (size_t)r * g.rowbuf + (start & ~3));
+            // first source byte of group 0 and the signed byte step from one group to the next
+            const int start0 = ((left * 3) & 15) + (flip ? 3 * (p.out_w - PX) : 0);
+            const int gstep = flip ? -3 * PX : 3 * PX;
+            int r = ur0, gq = ug0;
+            T* d = dimg + (int64_t)y0 * p.out_w + (int64_t)lane * PX;   // a tile is contiguous per plane
+            for (int u = lane; u < units; u += 32, d += 32 * PX) {
+                // NB source bytes from `start`: 8-byte loads of the aligned window (lanes 24 bytes
+                // apart never share a bank within a half-warp), then a word select + funnel shift.
+                const int start = start0 + gq * gstep;
+                const uint32_t wa = sbase + (uint32_t)(r * g.rowbuf + (start & ~7));
+                const bool hi4 = (start & 4) != 0;
                 const int sh = (start & 3) * 8;
-                uint32_t raw[NW + 1];
+                constexpr int NDW = (NW + 3) / 2;     // 8-byte words covering (start & 7) + NB bytes
+                uint32_t w[2 * NDW];
 #pragma unroll
-                for (int i = 0; i <= NW; ++i) raw[i] = wp[i];
+                for (int i = 0; i < NDW; ++i) tb_lds64(wa + 8 * i, w[2 * i], w[2 * i + 1]);
                 uint32_t q[NW];
 #pragma unroll
-                for (int i = 0; i < NW; ++i) q[i] = __funnelshift_r(raw[i], raw[i + 1], sh);
-                T* drow = dimg + (int64_t)(y0 + r) * p.out_w + gq * PX;
+                for (int i = 0; i < NW; ++i)
+                    q[i] = __funnelshift_r(hi4 ? w[i + 1] : w[i], hi4 ? w[i + 2] : w[i + 1], sh);
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
+                    const uint32_t base = c == 0 ? base0 : (c == 1 ? base1 : base2);
                     uint32_t v[PX];
-                    if (flip) {
+                    if (flip) {     // the flip only changes which source pixel feeds output slot j
 #pragma unroll
                         for (int j = 0; j < PX; ++j) {
                             const int bi = 3 * (PX - 1 - j) + c;
-                            const uint32_t e = (q[bi >> 2] >> (8 * (bi & 3))) & 0xFFu;
-                            v[j] = lutl[(c * 256 + e) * 32];
+                            v[j] = tb_lds32(__byte_perm(base, q[bi >> 2], 0x3240 | ((bi & 3) << 4)));
                         }
                     } else {
 #pragma unroll
                         for (int j = 0; j < PX; ++j) {
                             const int bi = 3 * j + c;
-                            const uint32_t e = (q[bi >> 2] >> (8 * (bi & 3))) & 0xFFu;
-                            v[j] = lutl[(c * 256 + e) * 32];
+                            v[j] = tb_lds32(__byte_perm(base, q[bi >> 2], 0x3240 | ((bi & 3) << 4)));
                         }
                     }
-                    tb_st_cs_v4(drow + c * plane, XfPack<T>::pack(v));
+                    tb_st_cs_v4(d + c * plane, X::pack(v, c));
                 }
+                r += g.step_r;
+                gq += g.step_g;
+                if (gq >= g.gpr) { gq -= g.gpr; ++r; }
             }
         } else {
             // crop window touches padding: gather route for this tile
             const int npix = nrows * p.out_w;
-            for (int i = ctid; i < npix; i += kXfConsumers) {
+            for (int i = lane; i < npix; i += 32) {
                 const int r = i / p.out_w;
                 const int x = i - r * p.out_w;
                 const int xs = flip ? p.out_w - 1 - x : x;
                 bool in = true;
                 const int uu = tb_fold(top + y0 + r, p.H, p.pad_mode, in);
                 const int vv = tb_fold(left + xs, p.W, p.pad_mode, in);
-                const uint8_t* sp = p.src + (int64_t)b * p.bs + (int64_t)uu * p.pitch + (int64_t)vv * 3;
-                T* d = dimg + (int64_t)(y0 + r) * p.out_w + x;
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    const uint32_t e = in ? (uint32_t)sp[c] : 0u;
-                    d[c * plane] = XfPack<T>::narrow(lutl[(c * 256 + e) * 32]);
-                }
+                const uint8_t* sp = p.src + (int64_t)bc * p.bs + (int64_t)uu * p.pitch + (int64_t)vv * 3;
+                T* dd = dimg + (int64_t)(y0 + r) * p.out_w + x;
+                const uint32_t e0 = in ? sp[0] : 0u, e1 = in ? sp[1] : 0u, e2 = in ? sp[2] : 0u;
+                dd[0] = X::one(tb_lds32(base0 + (e0 << 8)), 0);
+                dd[plane] = X::one(tb_lds32(base1 + (e1 << 8)), 1);
+                dd[2 * plane] = X::one(tb_lds32(base2 + (e2 << 8)), 2);
             }
         }
+        // this stage is drained by the whole warp: refill it with the tile two steps ahead
         __syncwarp();
-        if (lane == 0) tb_mbar_arrive(&empty[s]);
+        tb_fence_proxy_async();
+        issue(stage);
+        advance(tc, bc, tic);
     }
 }
 
@@ -283,52 +356,86 @@ int launch_generic(const XfParams& p, cudaStream_t s) {
 }
 
 template <typename T>
-int launch_staged(const XfParams& p, const TbDevice& dev, cudaStream_t s, bool* taken) {
-    constexpr int PX = XfPack<T>::PX;
+int launch_stream(const XfParams& p, const TbDevice& dev, cudaStream_t s, int force_rows, int force_warps, bool pdl,
+                  bool* taken) {
+    using X = Xf<T>;
+    constexpr int PX = X::PX;
     *taken = false;
-    XfStagedGeom g;
+    if (dev.max_smem_optin < (int)kXfSmemEnd + 2048) return TB_OK;
+    XfGeom g;
     // Whole-row crops of a dense source land as one copy per tile; otherwise one copy per row
     // covering the 16-byte aligned superset of the crop row.
     g.contiguous = (p.W == p.out_w && p.pitch == (int64_t)p.W * 3) ? 1 : 0;
     g.rowbuf = g.contiguous ? (int)p.pitch : ((p.out_w * 3 + 15 + 15) & ~15);
     g.gpr = p.out_w / PX;
-    const int fixed = kXfLutWords * 4 + 2 * kXfStages * 8 + 4096 /* static table copy + slack */;
-    const int avail = dev.max_smem_optin - fixed;
-    if (avail < kXfStages * g.rowbuf) return TB_OK;
-    int max_rows = avail / (kXfStages * g.rowbuf);
-    const int budget_rows = kXfStageBudget / g.rowbuf > 1 ? kXfStageBudget / g.rowbuf : 1;
-    if (max_rows > budget_rows) max_rows = budget_rows;
-    if (max_rows > kXfMaxRows) max_rows = kXfMaxRows;
-    if (max_rows > p.out_h) max_rows = p.out_h;
-    // Rows per tile: fewest consumer "rounds" per image (a round = every consumer thread takes one
-    // 16-byte unit), then fewest tiles.
-    int rows = 1;
-    int64_t best_rounds = -1;
-    for (int r = max_rows; r >= 1; --r) {
-        const int full_tiles = p.out_h / r, tail = p.out_h - full_tiles * r;
-        const int64_t rounds = (int64_t)full_tiles * ((r * g.gpr + kXfConsumers - 1) / kXfConsumers) +
-                               (tail ? (tail * g.gpr + kXfConsumers - 1) / kXfConsumers : 0);
-        if (best_rounds < 0 || rounds < best_rounds) { best_rounds = rounds; rows = r; }
+    // dynamic shared memory starts within the first 2 KiB of the window (1 KiB is reserved by the
+    // system and this kernel has no static shared memory); the kernel traps if that ever changes
+    const int avail = (int)X::kLow - 2048 - 3072 - 256;
+    // Rows per warp tile R and warps per CTA W.  Issue slots per image do not depend on W, so:
+    // fewest slots per image (a fixed cost per tile plus one unit per 32-lane round), with a mild
+    // preference for more resident warps.
+    int best_rows = 0, best_warps = 0;
+    double best = -1.0;
+    for (int warps = 6; warps <= 24; ++warps) {
+        if (force_warps && warps != force_warps) continue;
+        const int budget = (avail - 16 * warps) / warps;
+        int max_rows = budget / (2 * g.rowbuf);
+        if (max_rows > 32) max_rows = 32;
+        if (max_rows > p.out_h) max_rows = p.out_h;
+        for (int rows = 1; rows <= max_rows; ++rows) {
+            if (force_rows && rows != force_rows) continue;
+            const int full = p.out_h / rows, tail = p.out_h - full * rows;
+            auto tile_cost = [&](int r) { return ((r * g.gpr + 31) / 32) * 110.0 + 90.0; };
+            double cost = full * tile_cost(rows) + (tail ? tile_cost(tail) : 0.0);
+            cost *= 1.0 + 6.0 / warps;
+            if (best < 0 || cost < best) { best = cost; best_rows = rows; best_warps = warps; }
+        }
     }
-    g.rows = rows;
-    g.tiles_per_image = (p.out_h + rows - 1) / rows;
+    if (best < 0) return TB_OK;     // a single row does not fit a warp's ring: gather path
+    g.rows = best_rows;
+    const int warps = best_warps;
+    g.stage_bytes = g.rows * g.rowbuf;
+    g.tiles_per_image = (p.out_h + g.rows - 1) / g.rows;
     const int64_t total = (int64_t)g.tiles_per_image * p.B;
-    if (total >= (int64_t)1 << 31) return TB_OK;
+    if (total >= (int64_t)1 << 30) return TB_OK;
     g.total_tiles = (int)total;
     g.gpr_magic = (uint32_t)(((uint64_t)1 << 32) / (uint32_t)g.gpr) + 1u;
-    if ((int64_t)rows * g.gpr >= 60000) return TB_OK;  // keeps the magic division exact
-    const size_t smem = (size_t)kXfLutWords * 4 + (size_t)kXfStages * rows * g.rowbuf + 2 * kXfStages * 8;
+    g.step_r = 32 / g.gpr;
+    g.step_g = 32 % g.gpr;
+    int64_t grid = (total + warps - 1) / warps;
+    if (grid > dev.sm_count) grid = dev.sm_count;
+    const int64_t stride = grid * warps;
+    g.tile_db = (int)(stride / g.tiles_per_image);
+    g.tile_dt = (int)(stride % g.tiles_per_image);
+    g.dyn_bytes = kXfSmemEnd;
     static bool attr_set[64] = {};
     if (!attr_set[dev.device]) {
-        TB_CUDA(cudaFuncSetAttribute(tb_xf_staged_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     dev.max_smem_optin - 4096 + 2 * kXfStages * 8));
+        TB_CUDA(cudaFuncSetAttribute(tb_xf_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     dev.max_smem_optin));
         attr_set[dev.device] = true;
     }
-    const int grid = (int)(total < dev.sm_count ? total : dev.sm_count);
-    tb_xf_staged_kernel<T><<<grid, kXfThreads, smem, s>>>(p, g);
-    TB_LAUNCH_CHECK("tb_xf_staged_kernel");
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)warps * 32);
+    cfg.dynamicSmemBytes = g.dyn_bytes;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    TB_CUDA(cudaLaunchKernelEx(&cfg, tb_xf_stream_kernel<T>, p, g));
+    TB_LAUNCH_CHECK("tb_xf_stream_kernel");
     *taken = true;
     return TB_OK;
+}
+
+// Chance that a uniformly drawn crop window lies inside the unpadded image along one axis.
+double inside_fraction(int n, int pad, int out) {
+    const int positions = n + 2 * pad - out + 1;      // RandomCrop draws from [0, positions)
+    const int inside = n - out + 1;
+    if (positions <= 0 || inside <= 0) return 0.0;
+    return (double)inside / positions;
 }
 
 }  // namespace
@@ -366,12 +473,22 @@ extern "C" int tb_transform_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, in
     if (rc) return rc;
 
     const int px = 16 / tb_dtype_size(dst_dtype);
-    const bool fast_ok = !(flags & TB_FLAG_FORCE_GENERIC) && C == 3 && (out_w % px) == 0 &&
-                         ((uintptr_t)dst % 16) == 0 && ((uintptr_t)src % 16) == 0 && (src_row_pitch % 16) == 0 &&
-                         (src_batch_stride % 16) == 0;
-    if (fast_ok) {
+    bool stream_ok = !(flags & TB_FLAG_FORCE_GENERIC) && C == 3 && (out_w % px) == 0 &&
+                     ((uintptr_t)dst % 16) == 0 && ((uintptr_t)src % 16) == 0 && (src_row_pitch % 16) == 0 &&
+                     (src_batch_stride % 16) == 0;
+    // With padding most random windows leave the image (CIFAR: 32 from 32 + 2*4 -> 1 in 81 stays
+    // inside) and would take the gather route anyway; the plain gather kernel is then the better
+    // launch.  TB_FLAG_FORCE_STREAM overrides (tests).
+    if (stream_ok && !(flags & TB_FLAG_FORCE_STREAM) && (crop_top || crop_left) &&
+        inside_fraction(H, pad_y, out_h) * inside_fraction(W, pad_x, out_w) < 0.5)
+        stream_ok = false;
+    if (stream_ok) {
         bool taken = false;
-        rc = (dst_dtype == TB_F32) ? launch_staged<float>(p, dev, s, &taken) : launch_staged<uint16_t>(p, dev, s, &taken);
+        // development knobs: bits 16-23 warps per CTA, bits 24-31 rows per warp tile
+        const int fw = (flags >> 16) & 0xff, fr = (flags >> 24) & 0xff;
+        const bool pdl = !(flags & TB_FLAG_NO_PDL);
+        rc = dst_dtype == TB_F32 ? launch_stream<float>(p, dev, s, fr, fw, pdl, &taken)
+                                 : launch_stream<uint16_t>(p, dev, s, fr, fw, pdl, &taken);
         if (rc) return rc;
         if (taken) return TB_OK;
     }

@@ -113,7 +113,7 @@ class DeviceRunningAverage:
     """
 
     def __init__(self, device=None) -> None:
-        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.device = N.cuda_device(device)
         self.state = torch.zeros(2, dtype=torch.float64, device=self.device)
 
     def update(self, value: Tensor) -> None:
@@ -153,7 +153,7 @@ class MetricState:
         if num_classes < 1 or k < 1:
             raise ValueError("num_classes and k must be >= 1")
         self.num_classes, self.k, self.with_confusion = int(num_classes), int(k), bool(confusion)
-        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.device = N.cuda_device(device, allow_cpu=True)   # CPU state: reduction tests only; update() needs CUDA
         n = self.HEADER + (self.num_classes ** 2 if confusion else 0)
         self.buffer = torch.zeros(n, dtype=torch.int64, device=self.device)
         self.loss = torch.zeros(2, dtype=torch.float64, device=self.device)

@@ -17,9 +17,8 @@ class DeviceStager:
     def __init__(self, device, depth: int = 2) -> None:
         if depth < 2:
             raise ValueError("depth must be >= 2 (one buffer in use, one in flight)")
-        self.device = torch.device(device)
-        if self.device.type != "cuda":
-            raise RuntimeError("DeviceStager stages onto a CUDA device")
+        from ._native import cuda_device
+        self.device = cuda_device(device)
         self.depth = depth
         self.copy_stream = torch.cuda.Stream(self.device)
         self._buffers = [dict() for _ in range(depth)]

@@ -135,9 +135,7 @@ class BatchTransform:
 
     def __init__(self, spec: TransformSpec, device: Union[str, torch.device, None] = None, seed: Optional[int] = None):
         self.spec = spec
-        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
-        if self.device.type != "cuda":
-            raise RuntimeError("BatchTransform runs on a CUDA device only (no CPU fallback)")
+        self.device = N.cuda_device(device)
         self._luts = {}
         self._taps = {}
         self._rng = CropFlipParams(seed) if seed is not None else None
