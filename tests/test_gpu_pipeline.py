@@ -1,0 +1,63 @@
+"""The whole path on one GPU: LMDB records -> pinned gather -> staged H2D -> transform -> scoring,
+checked against the oracle (torchvision per sample + reference-pinned metric definitions)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import metrics_oracle as MO
+from oracle import params_oracle as PO
+from oracle import transform_oracle as TO
+from torchbooster_b200.lmdb import LMDBReader, write_image_lmdb
+from torchbooster_b200.metrics import MetricState
+from torchbooster_b200.staging import DeviceStager
+from torchbooster_b200.transforms import BatchTransform, TransformSpec
+
+pytestmark = pytest.mark.gpu
+CIFAR = ((0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010))
+
+
+def test_lmdb_to_metrics_end_to_end(tmp_path):
+    rng = np.random.default_rng(31)
+    n, B = 96, 32
+    imgs = rng.integers(0, 256, (n, 32, 32, 3), dtype=np.uint8)
+    write_image_lmdb(str(tmp_path / "db"), imgs, labels=np.arange(n) % 10)
+    reader = LMDBReader(str(tmp_path / "db"))
+    assert len(reader) == n
+    spec = TransformSpec(crop=32, padding=4, padding_mode="reflect", flip_p=.5, mean=CIFAR[0], std=CIFAR[1])
+    bt = BatchTransform(spec, device="cuda", seed=42)
+    top, left, flip = PO.draw_crop_flip(42, n, 32, 32, 32, 32, 4)       # torchvision's draws for the same seed
+    order = np.arange(n)
+    state = MetricState(10, k=3, device="cuda")
+    gen = torch.Generator().manual_seed(5)
+    head = torch.randn(3 * 32 * 32, 10, generator=gen)                  # a stand-in "model"
+    all_logits, all_labels = [], []
+    for s in range(0, n, B):
+        idx = order[s:s + B]
+        raw = reader.get_batch(idx, 32 * 32 * 3).view(-1, 32, 32, 3)
+        x = bt(raw)
+        want = TO.transform_batch(imgs[idx], crop_top=top[s:s + B], crop_left=left[s:s + B], out_size=(32, 32),
+                                  flip=flip[s:s + B], padding=4, padding_mode="reflect", mean=CIFAR[0], std=CIFAR[1])
+        assert torch.equal(x.cpu(), want)
+        logits = x.flatten(1) @ head.cuda()
+        labels = torch.from_numpy(idx % 10).cuda()
+        state.update(logits, labels)
+        all_logits.append(logits.cpu()); all_labels.append(labels.cpu())
+    res = state.compute()
+    L, Y = torch.cat(all_logits), torch.cat(all_labels)
+    assert res["n"] == n and res["correct_1"] == MO.topk_correct(L, Y, 1) and res["correct_3"] == MO.topk_correct(L, Y, 3)
+    assert np.array_equal(res["confusion"].cpu().numpy(), MO.confusion(L, Y, 10))
+
+
+def test_device_stager_keeps_order_and_content():
+    rng = np.random.default_rng(1)
+    hosts = [torch.from_numpy(rng.integers(0, 256, (8, 16, 16, 3), dtype=np.uint8)).pin_memory() for _ in range(7)]
+    stager = DeviceStager("cuda", depth=2)
+    seen = []
+    for (dev,), tag in stager.run(((h,), i) for i, h in enumerate(hosts)):
+        assert dev.is_cuda
+        seen.append((tag, dev.clone()))
+    torch.cuda.synchronize()
+    assert [t for t, _ in seen] == list(range(7))
+    for (t, d), h in zip(seen, hosts):
+        assert torch.equal(d.cpu(), h)
+    assert list(stager.run(iter(()))) == []

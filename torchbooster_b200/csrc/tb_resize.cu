@@ -220,15 +220,154 @@ __global__ void __launch_bounds__(256) tb_resize_fused_kernel(RsParams p) {
     }
 }
 
+
+// ----------------------------------------------------------------------------------------------
+// fast path: both passes active with at most kRsKS taps (scale factors up to 2, and any upscale),
+// source rows readable as aligned 32-bit words.  Same tiling; per thread the horizontal taps of
+// its column live in registers for the whole tile, the source bytes of a tap window are fetched
+// as words and funnel-shifted once, and the vertical taps of the tile's rows sit in shared memory.
+// ----------------------------------------------------------------------------------------------
+constexpr int kRsKS = 5;
+
 template <typename T, int C>
-int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, cudaStream_t s) {
+__global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
+    constexpr int NBYTES = kRsKS * C;                 // bytes of one tap window
+    constexpr int NQ = (NBYTES + 3) / 4;              // aligned words after the shift
+    extern __shared__ __align__(16) uint8_t inter[];  // [nin][row_bytes]
+    __shared__ T s_lut[C * 256];
+    __shared__ int s_ky[32][kRsKS];
+    __shared__ int s_ymin[32];
+    tb_grid_dependency_wait();
+    for (int i = threadIdx.x; i < C * 256; i += 256) s_lut[i] = ((const T*)p.lut)[i];
+
+    int t = blockIdx.x;
+    const int tx = t % p.tiles_x; t /= p.tiles_x;
+    const int ty = t % p.tiles_y;
+    const int b = t / p.tiles_y;
+    const int y0 = ty * p.TR, x0 = tx * p.TC;
+    const int nr = min(p.TR, p.out_h - y0), nc = min(p.TC, p.out_w - x0);
+    const int oy = (p.top ? p.top[b] : 0) + p.off_y;
+    const int ox = (p.left ? p.left[b] : 0) + p.off_x;
+    const bool flip = p.flip ? (p.flip[b] != 0) : false;
+    const int ry0 = max(oy + y0, 0), ry1 = min(oy + y0 + nr, p.rs_h);
+    const int xs0 = flip ? p.out_w - x0 - nc : x0;
+    const int rx0 = max(ox + xs0, 0), rx1 = min(ox + xs0 + nc, p.rs_w);
+    const bool any = ry1 > ry0 && rx1 > rx0;
+    int iy0 = 0, nin = 0;
+    if (any) {
+        iy0 = p.by[2 * ry0];
+        nin = p.by[2 * (ry1 - 1)] + p.by[2 * (ry1 - 1) + 1] - iy0;
+    }
+    const int ncols = any ? rx1 - rx0 : 0;
+    // vertical taps of the resized rows this tile touches (zero beyond each row's tap count)
+    for (int i = threadIdx.x; i < (ry1 - ry0) * kRsKS; i += 256) {
+        const int rr = i / kRsKS, j = i - rr * kRsKS;
+        const int ry = ry0 + rr;
+        s_ky[rr][j] = (j < p.ksy && j < p.by[2 * ry + 1]) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+        if (j == 0) s_ymin[rr] = p.by[2 * ry] - iy0;
+    }
+
+    // ---- phase 1: horizontal pass; thread <-> column, looping over the input rows
+    const uint8_t* simg = p.src + (int64_t)b * p.bs;
+    const int pitch_w = (int)(p.pitch >> 2);
+    for (int c0 = 0; c0 < ncols; c0 += 256) {
+        const int nch = min(256, ncols - c0);
+        const int ngrp = max(1, 256 / nch);
+        const int grp = threadIdx.x / nch;
+        if (grp < ngrp) {
+            const int cx = c0 + threadIdx.x - grp * nch;
+            const int rx = rx0 + cx;
+            const int xmin = p.bx[2 * rx], n = p.bx[2 * rx + 1];
+            int k[kRsKS];
+#pragma unroll
+            for (int j = 0; j < kRsKS; ++j) k[j] = (j < p.ksx && j < n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+            const int boff = xmin * C;
+            const int a = boff & 3;
+            const int nw = (a + n * C + 3) >> 2;                 // words that hold this window
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(simg + (boff - a)) + (size_t)(iy0 + grp) * pitch_w;
+            uint8_t* o = inter + (size_t)grp * p.row_bytes + cx * C;
+            for (int r = grp; r < nin; r += ngrp, wp += (size_t)ngrp * pitch_w, o += (size_t)ngrp * p.row_bytes) {
+                uint32_t w[NQ + 1];
+#pragma unroll
+                for (int i = 0; i <= NQ; ++i) w[i] = i < nw ? __ldg(wp + i) : 0u;
+                uint32_t q[NQ];
+#pragma unroll
+                for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[i], w[i + 1], a * 8);
+                int acc[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) acc[c] = 1 << (kPrecisionBits - 1);
+#pragma unroll
+                for (int j = 0; j < kRsKS; ++j) {
+#pragma unroll
+                    for (int c = 0; c < C; ++c) {
+                        const int bi = j * C + c;
+                        acc[c] += (int)((q[bi >> 2] >> (8 * (bi & 3))) & 0xffu) * k[j];
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) o[c] = tb_clip8(acc[c]);
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 2: vertical pass out of shared memory; thread <-> output column, looping over rows
+    T* dimg = (T*)p.dst + (int64_t)b * C * p.out_h * p.out_w;
+    const int64_t plane = (int64_t)p.out_h * p.out_w;
+    for (int c0 = 0; c0 < nc; c0 += 256) {
+        const int nch = min(256, nc - c0);
+        const int ngrp = max(1, 256 / nch);
+        const int grp = threadIdx.x / nch;
+        if (grp >= ngrp) continue;
+        const int xx = c0 + threadIdx.x - grp * nch;
+        const int x = x0 + xx;
+        const int rx = ox + (flip ? p.out_w - 1 - x : x);
+        const bool colin = rx >= 0 && rx < p.rs_w;
+        const uint8_t* col = inter + (size_t)(colin ? rx - rx0 : 0) * C;
+        for (int yy = grp; yy < nr; yy += ngrp) {
+            const int y = y0 + yy;
+            const int ry = oy + y;
+            uint32_t e[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) e[c] = 0;
+            if (colin && ry >= 0 && ry < p.rs_h) {
+                const int rr = ry - ry0;
+                const uint8_t* q = col + (size_t)s_ymin[rr] * p.row_bytes;
+                int acc[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) acc[c] = 1 << (kPrecisionBits - 1);
+#pragma unroll
+                for (int j = 0; j < kRsKS; ++j) {
+                    const int kk = s_ky[rr][j];
+                    // taps past the row's count are zero; keep their reads inside the tile
+                    const uint8_t* qq = q + (size_t)min(j, nin - 1 - s_ymin[rr]) * p.row_bytes;
+#pragma unroll
+                    for (int c = 0; c < C; ++c) acc[c] += (int)qq[c] * kk;
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) e[c] = tb_clip8(acc[c]);
+            }
+            T* d = dimg + (int64_t)y * p.out_w + x;
+#pragma unroll
+            for (int c = 0; c < C; ++c) d[c * plane] = s_lut[c * 256 + e[c]];
+        }
+    }
+}
+
+template <typename T, int C>
+int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, bool fast, cudaStream_t s) {
     static bool attr_set[64] = {};
     int dev = 0;
     TB_CUDA(cudaGetDevice(&dev));
-    if (smem > 48 * 1024 && !attr_set[dev]) {
+    if (smem > 40 * 1024 && !attr_set[dev]) {
         TB_CUDA(cudaFuncSetAttribute(tb_resize_fused_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      max_smem - 8192));
         attr_set[dev] = true;
+    }
+    if (fast && smem <= 40 * 1024) {
+        tb_resize_fast_kernel<T, C><<<(unsigned)blocks, 256, smem, s>>>(p);
+        TB_LAUNCH_CHECK("tb_resize_fast_kernel");
+        return TB_OK;
     }
     tb_resize_fused_kernel<T, C><<<(unsigned)blocks, 256, smem, s>>>(p);
     TB_LAUNCH_CHECK("tb_resize_fused_kernel");
@@ -243,7 +382,6 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     const int32_t* taps_y, int ks_y, void* dst, int dst_dtype, int out_h, int out_w, const int32_t* crop_top,
     const int32_t* crop_left, const uint8_t* flip, int off_y, int off_x, const void* lut, int flags,
     tb_stream_t stream) {
-    (void)flags;
     TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_resize: bad source shape B=%d H=%d W=%d", B, H, W);
     TB_REQUIRE(C == 1 || C == 3, "tb_resize: C=%d not supported (Pillow premultiplies alpha for RGBA); use C in {1,3}", C);
     TB_REQUIRE(rs_h >= 1 && rs_w >= 1 && out_h >= 1 && out_w >= 1, "tb_resize: bad output sizes");
@@ -277,8 +415,11 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     // resized rows can touch: at most ceil(TR * scale_y) + ks_y rows.
     const double scale_y = rs_h != H ? (double)H / rs_h : 1.0;
     const int budget = 40 * 1024;
+    const bool fast = !(flags & TB_FLAG_FORCE_GENERIC) && p.words_ok && rs_w != W && rs_h != H && ks_x <= kRsKS &&
+                      ks_y <= kRsKS;
     int TC = out_w < 256 ? out_w : 256;
-    int TR = 8;
+    // taller tiles recompute fewer halo rows; keep at least ~4 CTAs per SM in the grid
+    int TR = ((int64_t)B * ((out_h + 15) / 16) * ((out_w + TC - 1) / TC) >= 4 * (int64_t)dev.sm_count) ? 16 : 8;
     auto rows_for = [&](int tr) { return rs_h != H ? (int)ceil(tr * scale_y) + ks_y + 1 : tr; };
     auto rowb = [&](int tc) { return (tc * C + 3) & ~3; };
     while (TR > 1 && (int64_t)rows_for(TR) * rowb(TC) > budget) TR >>= 1;
@@ -295,8 +436,8 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize: grid too large");
     cudaStream_t s = (cudaStream_t)stream;
     const bool f32 = dst_dtype == TB_F32;
-    if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, s)
-                           : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, s);
-    return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, s)
-               : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, s);
+    if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, fast, s)
+                           : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, fast, s);
+    return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, fast, s)
+               : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, fast, s);
 }
