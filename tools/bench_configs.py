@@ -24,6 +24,7 @@ try:
 except Exception:
     pass
 L2 = 126 << 20
+CASE = ""          # --case: run only cases whose name contains this
 
 
 def time_loop(fn, iters, warm=5):
@@ -40,6 +41,8 @@ def time_loop(fn, iters, warm=5):
 
 
 def transform_case(name, B, H, W, spec_kw, alg_bytes, iters, flags=0, params=True):
+    if CASE and CASE not in name:
+        return
     dev = torch.device("cuda", 0)
     spec = TransformSpec(**spec_kw)
     bt = BatchTransform(spec, device=dev)
@@ -61,6 +64,8 @@ def transform_case(name, B, H, W, spec_kw, alg_bytes, iters, flags=0, params=Tru
 
 
 def metrics_case(name, n, c, dtype, iters):
+    if CASE and CASE not in name:
+        return
     dev = torch.device("cuda", 0)
     gen = torch.Generator(device=dev).manual_seed(1234)
     es = 4 if dtype == torch.float32 else 2
@@ -74,11 +79,27 @@ def metrics_case(name, n, c, dtype, iters):
                       "frac_measured": gbs / PEAK, "frac_nominal": gbs / 8000, "nbuf": nbuf}), flush=True)
 
 
+def calibrate():
+    """Library reference points on the same buffers: a read-only reduction and a copy."""
+    dev = torch.device("cuda", 0)
+    bufs = [torch.randn(125_000, 1000, device=dev) for _ in range(2)]
+    dst = torch.empty_like(bufs[0])
+    nbytes = bufs[0].numel() * 4
+    for name, fn, moved in (("calib_torch_sum_500MB", lambda i: bufs[i & 1].sum(), nbytes),
+                            ("calib_torch_amax_rows_500MB", lambda i: bufs[i & 1].amax(dim=1), nbytes),
+                            ("calib_torch_copy_500MB", lambda i: dst.copy_(bufs[i & 1]), 2 * nbytes)):
+        ms = time_loop(fn, 50)
+        print(json.dumps({"case": name, "ms": ms, "GBps": moved / (ms * 1e-3) / 1e9, "frac_measured": moved / (ms * 1e-3) / 1e9 / PEAK}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--case", default="")
     a = ap.parse_args()
+    global CASE
+    CASE = a.case
     want = lambda n: not a.only or any(n.startswith(x) for x in a.only.split(","))
     c2 = dict(crop=224, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
     if want("c2"):
@@ -106,6 +127,8 @@ def main():
         c4 = dict(resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1])
         transform_case("c4_stt_b32", 32, 512, 512, c4, 1572864, 200, params=False)
         transform_case("c4_stt_b256", 256, 512, 512, c4, 1572864, 50, params=False)
+    if want("calib"):
+        calibrate()
     if want("c5"):
         metrics_case("c5_fp32_125k", 125_000, 1000, torch.float32, 50)
         metrics_case("c5_bf16_125k", 125_000, 1000, torch.bfloat16, 50)

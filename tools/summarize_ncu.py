@@ -83,7 +83,13 @@ def main():
             if "tb_xf_stream" in name:
                 traffic["c2"] = sum(v) / len(v)
     if (src / "prof_mx.ncu-rep").exists():
-        summarize_report(src / "prof_mx.ncu-rep", OUT / f"{tag}_ncu_metrics_resize.txt", "metrics (C5) and resize (C4) kernels")
+        t = summarize_report(src / "prof_mx.ncu-rep", OUT / f"{tag}_ncu_metrics.txt", "metrics kernel, C5 workload (125 000 x 1000 fp32)")
+        for name, v in t.items():
+            traffic["c5"] = sum(v) / len(v)
+    if (src / "prof_rs.ncu-rep").exists():
+        t = summarize_report(src / "prof_rs.ncu-rep", OUT / f"{tag}_ncu_resize.txt", "resize kernel, C4 workload (batch 256)")
+        for name, v in t.items():
+            traffic["c4_b256"] = sum(v) / len(v)
     if traffic:
         (OUT / "traffic.json").write_text(json.dumps(traffic, indent=1) + "\n")
     for f in ("bench_full.json", "bench_ref.json", "configs.jsonl"):

@@ -28,6 +28,7 @@ template <>
 struct Elem<TB_F32> {
     static constexpr int VE = 4;
     using type = float;
+    __device__ static __forceinline__ float to_float(float v) { return v; }
     __device__ static __forceinline__ float get(const void* p, int64_t i) { return ((const float*)p)[i]; }
     __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
         f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y); f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
@@ -37,9 +38,8 @@ template <>
 struct Elem<TB_BF16> {
     static constexpr int VE = 8;
     using type = uint16_t;
-    __device__ static __forceinline__ float get(const void* p, int64_t i) {
-        return __uint_as_float((uint32_t)((const uint16_t*)p)[i] << 16);
-    }
+    __device__ static __forceinline__ float to_float(uint16_t v) { return __uint_as_float((uint32_t)v << 16); }
+    __device__ static __forceinline__ float get(const void* p, int64_t i) { return to_float(((const uint16_t*)p)[i]); }
     __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -53,7 +53,8 @@ template <>
 struct Elem<TB_F16> {
     static constexpr int VE = 8;
     using type = uint16_t;
-    __device__ static __forceinline__ float get(const void* p, int64_t i) { return __half2float(((const __half*)p)[i]); }
+    __device__ static __forceinline__ float to_float(uint16_t v) { return __half2float(__ushort_as_half(v)); }
+    __device__ static __forceinline__ float get(const void* p, int64_t i) { return to_float(((const uint16_t*)p)[i]); }
     __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -66,15 +67,17 @@ struct Elem<TB_F16> {
 };
 
 // ---- per-row accumulator ---------------------------------------------------------------------
-// The sweep keeps per lane: `cnt` (how many elements outrank the label), and the key and position
-// of the best vector seen (first one wins); the exact argmax index is resolved once per row by
-// re-reading that one vector.
+// The sweep keeps per lane: `cnt` (how many elements outrank the label, scaled by kScale) and the
+// value, key and position of the best 16-byte vector seen (first one wins); the exact argmax
+// index is resolved once per row by re-reading that one vector.
 //
-// Rank counting runs on the float pipe.  For a label logit ly that is not NaN,
-//   j <  y counts when x_j >= ly  <=>  x_j > pred(ly)   (pred = next float below; NaN x_j counts)
+// Rank counting needs no integer keys.  For a label logit ly that is not NaN,
+//   j <  y counts when x_j >= ly  <=>  x_j > pred(ly)   (pred = next value below; NaN x_j counts)
 //   j >= y counts when x_j >  ly                         (NaN x_j counts)
 // so one "greater than or unordered" compare against a per-vector threshold does both; the one
-// vector that straddles y selects per element.  A NaN label logit takes the key-based route.
+// vector that straddles y selects per element.  16-bit logits are compared two at a time
+// (set.gtu.{bf16x2,f16x2}) and the eight half-word masks of a vector are folded into one word
+// whose popcount is 4x the number of hits.  A NaN label logit takes the key-based route.
 __device__ __forceinline__ int tb_gtu(float x, float thr) {   // -1 when x > thr or unordered, else 0
     int r;
     asm("set.gtu.s32.f32 %0, %1, %2;" : "=r"(r) : "f"(x), "f"(thr));
@@ -85,52 +88,182 @@ __device__ __forceinline__ float tb_max_nan(float a, float b) {   // NaN-propaga
     asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
     return r;
 }
+__device__ __forceinline__ uint32_t tb_bitsel(uint32_t a, uint32_t b, uint32_t k) { return (a & k) | (b & ~k); }
 
+template <int DT>
+struct Packed {   // fp32: not packed
+    static constexpr bool kOn = false;
+    static constexpr int kScale = 1;
+};
+template <>
+struct Packed<TB_BF16> {
+    static constexpr bool kOn = true;
+    static constexpr int kScale = 4;
+    static constexpr uint32_t kNegInf = 0xff80u;
+    __device__ static __forceinline__ uint32_t gtu2(uint32_t a, uint32_t b) {   // 0xffff per half-word that is > or unordered
+        uint32_t r;
+        asm("set.gtu.u32.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+        return r;
+    }
+    __device__ static __forceinline__ uint32_t max2(uint32_t a, uint32_t b) {
+        uint32_t r;
+        asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+        return r;
+    }
+    __device__ static __forceinline__ float lo(uint32_t w) { return __uint_as_float(w << 16); }
+    __device__ static __forceinline__ float hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+};
+template <>
+struct Packed<TB_F16> {
+    static constexpr bool kOn = true;
+    static constexpr int kScale = 4;
+    static constexpr uint32_t kNegInf = 0xfc00u;
+    __device__ static __forceinline__ uint32_t gtu2(uint32_t a, uint32_t b) {
+        uint32_t r;
+        asm("set.gtu.u32.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+        return r;
+    }
+    __device__ static __forceinline__ uint32_t max2(uint32_t a, uint32_t b) {
+        uint32_t r;
+        asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+        return r;
+    }
+    __device__ static __forceinline__ float lo(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)w)); }
+    __device__ static __forceinline__ float hi(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w >> 16))); }
+};
+
+template <int DT>
 struct RowAcc {
+    using E = Elem<DT>;
+    using P = Packed<DT>;
+    static constexpr int VE = E::VE;
     int bestk, bj0, bn;     // key of the best vector, its first element index and length
-    int cnt;                // minus the number of elements that outrank the label
+    float bm;               // value behind bestk (NaN until the first update)
+    int cnt;                // kScale x the number of elements that outrank the label
     int y, ky;
     float lo, hi;           // thresholds for j < y and j >= y
+    uint32_t lo2, hi2;      // the same, as packed pairs (16-bit logits)
     bool ynan;
 
-    __device__ __forceinline__ void init(float ly, int label) {
+    __device__ __forceinline__ void init(typename E::type raw, int label) {
         y = label;
+        const float ly = E::to_float(raw);
         ky = tb_key(ly);
         ynan = ly != ly;
-        const float c = ly + 0.0f;
-        const uint32_t b = __float_as_uint(c);
-        hi = c;
-        if (b == 0xff800000u) lo = __uint_as_float(0x7fffffffu);            // >= -inf: everything counts
-        else if (b == 0u) lo = __uint_as_float(0x80000001u);                // below zero: -denorm_min
-        else lo = __uint_as_float((b & 0x80000000u) ? b + 1u : b - 1u);
         bestk = INT_MIN; bj0 = INT_MAX; bn = 0; cnt = 0;
+        bm = __uint_as_float(0x7fffffffu);
+        lo2 = hi2 = 0;
+        if constexpr (P::kOn) {
+            // thresholds in the logits' own 16-bit format (exact in fp32 as well)
+            uint32_t c = (uint32_t)raw;
+            if (c == 0x8000u) c = 0;                                   // -0 == +0
+            uint32_t l;
+            if (c == P::kNegInf) l = 0x7fffu;                          // >= -inf: everything counts
+            else if (c == 0u) l = 0x8001u;                             // just below zero
+            else l = (c & 0x8000u) ? c + 1u : c - 1u;
+            hi2 = c * 0x10001u;
+            lo2 = l * 0x10001u;
+            hi = P::lo(hi2);
+            lo = P::lo(lo2);
+        } else {
+            const float c = ly + 0.0f;
+            const uint32_t b = __float_as_uint(c);
+            hi = c;
+            if (b == 0xff800000u) lo = __uint_as_float(0x7fffffffu);
+            else if (b == 0u) lo = __uint_as_float(0x80000001u);
+            else lo = __uint_as_float((b & 0x80000000u) ? b + 1u : b - 1u);
+        }
     }
     // scalar element (row head / tail, NaN-label rows)
     __device__ __forceinline__ void one(float x, int j) {
         const int k = tb_key(x);
-        cnt -= (k > ky - (j < y ? 1 : 0)) ? 1 : 0;
-        if (k > bestk) { bestk = k; bj0 = j; bn = 1; }
+        cnt += (k > ky - (j < y ? 1 : 0)) ? P::kScale : 0;
+        if (k > bestk) { bestk = k; bm = x; bj0 = j; bn = 1; }
     }
-    template <int VE>
-    __device__ __forceinline__ void vec(const float* f, int j0) {
-        float m = tb_max_nan(f[0], f[1]);
-#pragma unroll
-        for (int e = 2; e < VE; ++e) m = tb_max_nan(m, f[e]);
-        const int k = tb_key(m);
-        if (k > bestk) { bestk = k; bj0 = j0; bn = VE; }
-        const int d = y - j0;
-        if ((unsigned)d < (unsigned)VE) {
-#pragma unroll
-            for (int e = 0; e < VE; ++e) cnt += tb_gtu(f[e], e < d ? lo : hi);
+    __device__ __forceinline__ void candidate(float m, int j0) {
+        if (!(m <= bm)) {                     // greater or unordered: rare after the first vectors
+            const int k = tb_key(m);
+            if (k > bestk) { bestk = k; bm = m; bj0 = j0; bn = VE; }
+        }
+    }
+    // NaN-propagating maximum of one 16-byte vector
+    __device__ __forceinline__ float vec_max(const uint4& r) const {
+        if constexpr (P::kOn) {
+            const uint32_t m = P::max2(P::max2(r.x, r.y), P::max2(r.z, r.w));
+            return tb_max_nan(P::lo(m), P::hi(m));
         } else {
+            float f[VE];
+            E::unpack(r, f);
+            float m = tb_max_nan(f[0], f[1]);
+#pragma unroll
+            for (int e = 2; e < VE; ++e) m = tb_max_nan(m, f[e]);
+            return m;
+        }
+    }
+    // elements of one vector that outrank the label
+    __device__ __forceinline__ void vec_count(const uint4& r, int j0) {
+        const int d = y - j0;
+        if ((unsigned)d < (unsigned)VE) {        // the one vector that straddles the label
+            float f[VE];
+            E::unpack(r, f);
+#pragma unroll
+            for (int e = 0; e < VE; ++e) cnt -= P::kScale * tb_gtu(f[e], e < d ? lo : hi);
+        } else if constexpr (P::kOn) {
+            const uint32_t thr = d > 0 ? lo2 : hi2;
+            // nibble i of each half-word <- hit mask of word i; popcount = 4 x hits
+            const uint32_t t = tb_bitsel(tb_bitsel(P::gtu2(r.x, thr), P::gtu2(r.y, thr), 0x000f000fu),
+                                         tb_bitsel(P::gtu2(r.z, thr), P::gtu2(r.w, thr), 0x0f000f00u), 0x00ff00ffu);
+            cnt += __popc(t);
+        } else {
+            float f[VE];
+            E::unpack(r, f);
             const float thr = d > 0 ? lo : hi;
 #pragma unroll
-            for (int e = 0; e < VE; ++e) cnt += tb_gtu(f[e], thr);
+            for (int e = 0; e < VE; ++e) cnt -= tb_gtu(f[e], thr);
         }
+    }
+    // one batch of UN vectors (vector i holds elements j0 + i * stride ...): count every vector, but
+    // rank only the batch maximum against the best so far
+    template <int UN>
+    __device__ __forceinline__ void batch(const uint4* r, int v, int nfull, int jf) {
+        const float ninf = __uint_as_float(0xff800000u);
+        float m[UN];
+#pragma unroll
+        for (int i = 0; i < UN; ++i) {
+            const bool ok = v + 32 * i < nfull;
+            m[i] = ok ? vec_max(r[i]) : ninf;
+            if (ok) vec_count(r[i], jf + (v + 32 * i) * VE);
+        }
+        float M = m[0];
+#pragma unroll
+        for (int i = 1; i < UN; ++i) M = tb_max_nan(M, m[i]);
+        if (v < nfull && !(M <= bm)) {       // (vector 0 invalid = no vector of this lane is valid)
+            const bool nanmax = M != M;
+            int pick = 0;
+#pragma unroll
+            for (int i = UN - 1; i >= 0; --i)
+                if (nanmax ? (m[i] != m[i]) : (m[i] >= M)) pick = i;
+            candidate(M, jf + (v + 32 * pick) * VE);
+        }
+    }
+    // first index attaining the row maximum inside this lane's best vector
+    __device__ __forceinline__ int resolve(const typename E::type* row) const {
+        if (bn == 1) return bj0;
+        const uint4 r = *reinterpret_cast<const uint4*>(row + bj0);
+        float f[VE];
+        E::unpack(r, f);
+        const bool nanmax = bm != bm;
+        int e0 = 0;
+#pragma unroll
+        for (int e = VE - 1; e >= 0; --e)
+            if (nanmax ? (f[e] != f[e]) : (f[e] >= bm)) e0 = e;
+        return bj0 + e0;
     }
 };
 
-template <int DT>
+// ALIGNED: every row starts on a 16-byte boundary (base and row stride are multiples of 16
+// bytes), so the head / body / tail split is the same for all rows.
+template <int DT, bool ALIGNED>
 __global__ void __launch_bounds__(kMxThreads) tb_metrics_kernel(const void* __restrict__ logits, int64_t N, int C,
                                                                 int64_t row_stride, const int64_t* __restrict__ labels,
                                                                 int k, unsigned long long* __restrict__ counters,
@@ -150,51 +283,54 @@ __global__ void __launch_bounds__(kMxThreads) tb_metrics_kernel(const void* __re
     const int64_t nwarps = (int64_t)gridDim.x * kMxWarps;
     unsigned int c1 = 0, ck = 0, inv = 0;
 
+    // One DRAM round trip per row: the next row's label is fetched a row ahead, and the row's
+    // vectors, its head / tail elements and the label's own logit are all issued before any of
+    // them is used.
+    long long y64 = warp0 < N ? labels[warp0] : -1;
     for (int64_t n = warp0; n < N; n += nwarps) {
-        const long long y64 = labels[n];
-        if (y64 < 0 || y64 >= C) { inv += 1; continue; }
+        const long long ycur = y64;
+        if (n + nwarps < N) y64 = labels[n + nwarps];
+        if (ycur < 0 || ycur >= C) { inv += 1; continue; }
+        const int y = (int)ycur;
         const typename E::type* row = (const typename E::type*)logits + n * row_stride;
-        RowAcc a;
-        a.init(E::get(row, (int)y64), (int)y64);
 
-        const int mis = (int)(((uintptr_t)row & 15) / ES);          // elements past the previous 16-byte boundary
+        const int mis = ALIGNED ? 0 : (int)(((uintptr_t)row & 15) / ES);   // elements past the previous 16-byte boundary
         const int jf = mis ? min(VE - mis, C) : 0;                  // head elements before the first aligned vector
         const int nfull = (C - jf) / VE;
         const int jt = jf + nfull * VE;                             // first tail element
         const uint4* vp = reinterpret_cast<const uint4*>(row + jf);
 
+        // UN vectors per lane in flight at once (a 1000-class fp32 row is 250 vectors: one batch)
+        uint4 r[UN];
+#pragma unroll
+        for (int i = 0; i < UN; ++i)
+            if (lane + 32 * i < nfull) r[i] = __ldcs(vp + lane + 32 * i);
+        const typename E::type raw_y = row[y];
+        typename E::type raw_head = raw_y, raw_tail = raw_y;
+        if (lane < jf) raw_head = row[lane];
+        if (jt + lane < C) raw_tail = row[jt + lane];                 // tail: fewer than VE <= 32 elements
+
+        RowAcc<DT> a;
+        a.init(raw_y, y);
         if (a.ynan) {
             // rare: the label's own logit is NaN -- everything through the key route
             for (int j = lane; j < C; j += 32) a.one(E::get(row, j), j);
         } else {
-            if (lane < jf) a.one(E::get(row, lane), lane);
-            // UN vectors per lane in flight at once (a 1000-class fp32 row is 250 vectors: one batch)
-            for (int v = lane; v < nfull; v += 32 * UN) {
-                uint4 r[UN];
+            if (lane < jf) a.one(E::to_float(raw_head), lane);
+            a.template batch<UN>(r, lane, nfull, jf);
+            for (int v = lane + 32 * UN; v < nfull; v += 32 * UN) {   // rows longer than one batch
 #pragma unroll
                 for (int i = 0; i < UN; ++i)
                     if (v + 32 * i < nfull) r[i] = __ldcs(vp + v + 32 * i);
-#pragma unroll
-                for (int i = 0; i < UN; ++i) {
-                    if (v + 32 * i < nfull) {
-                        float f[VE];
-                        E::unpack(r[i], f);
-                        a.template vec<VE>(f, jf + (v + 32 * i) * VE);
-                    }
-                }
+                a.template batch<UN>(r, v, nfull, jf);
             }
-            if (jt + lane < C) a.one(E::get(row, jt + lane), jt + lane);   // tail: fewer than VE <= 32 elements
+            if (jt + lane < C) a.one(E::to_float(raw_tail), jt + lane);
         }
 
         const int mx = __reduce_max_sync(0xffffffffu, a.bestk);
-        int cand = INT_MAX;
-        if (a.bestk == mx) {
-            // first element of this lane's best vector that attains the maximum
-            for (int e = a.bn - 1; e >= 0; --e)
-                if (tb_key(E::get(row, a.bj0 + e)) == mx) cand = a.bj0 + e;
-        }
+        const int cand = a.bestk == mx ? a.resolve(row) : INT_MAX;
         const int pred = __reduce_min_sync(0xffffffffu, cand);
-        const int rank = -__reduce_add_sync(0xffffffffu, a.cnt);
+        const int rank = __reduce_add_sync(0xffffffffu, a.cnt) / Packed<DT>::kScale;
         if (lane == 0) {
             c1 += (rank < 1) ? 1u : 0u;
             ck += (rank < k) ? 1u : 0u;
@@ -254,13 +390,9 @@ extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N
     int rc = tb_device(&dev);
     if (rc) return rc;
     int64_t blocks = (N + kMxWarps - 1) / kMxWarps;
-    const int64_t cap = (int64_t)dev.sm_count * 8;   // 8 x 256 threads = full occupancy
-    if (blocks > cap) blocks = cap;
-    TB_REQUIRE(N / (blocks * kMxWarps) < ((int64_t)1 << 28), "tb_metrics_update: N too large for one launch");
     auto* cnt = reinterpret_cast<unsigned long long*>(counters);
     auto* cm = reinterpret_cast<unsigned long long*>(confusion);
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)blocks);
     cfg.blockDim = dim3(kMxThreads);
     cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute attr[1];
@@ -268,12 +400,23 @@ extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (logits_dtype == TB_F32)
-        TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<TB_F32>, logits, N, C, row_stride, labels, k, cnt, cm));
-    else if (logits_dtype == TB_BF16)
-        TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<TB_BF16>, logits, N, C, row_stride, labels, k, cnt, cm));
-    else
-        TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<TB_F16>, logits, N, C, row_stride, labels, k, cnt, cm));
+
+    const int64_t cap = (int64_t)dev.sm_count * 8;   // 8 x 256 threads = full occupancy
+    if (blocks > cap) blocks = cap;
+    TB_REQUIRE(N / (blocks * kMxWarps) < ((int64_t)1 << 28), "tb_metrics_update: N too large for one launch");
+    cfg.gridDim = dim3((unsigned)blocks);
+    const bool aligned = ((uintptr_t)logits % 16) == 0 && ((row_stride * es) % 16) == 0;
+#define TB_MX_LAUNCH(DT)                                                                                              \
+    do {                                                                                                              \
+        if (aligned)                                                                                                  \
+            TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<DT, true>, logits, N, C, row_stride, labels, k, cnt, cm));  \
+        else                                                                                                          \
+            TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<DT, false>, logits, N, C, row_stride, labels, k, cnt, cm)); \
+    } while (0)
+    if (logits_dtype == TB_F32) TB_MX_LAUNCH(TB_F32);
+    else if (logits_dtype == TB_BF16) TB_MX_LAUNCH(TB_BF16);
+    else TB_MX_LAUNCH(TB_F16);
+#undef TB_MX_LAUNCH
     TB_LAUNCH_CHECK("tb_metrics_kernel");
     return TB_OK;
 }
