@@ -79,6 +79,50 @@ def metrics_case(name, n, c, dtype, iters):
                       "frac_measured": gbs / PEAK, "frac_nominal": gbs / 8000, "nbuf": nbuf}), flush=True)
 
 
+def two_stream_case(name, B, iters, nstreams):
+    """C2 transform launched round-robin on `nstreams` streams through the C ABI (no Python
+    wrapper): does the tail of launch i overlap the prologue of launch i+1?"""
+    if CASE and CASE not in name:
+        return
+    dev = torch.device("cuda", 0)
+    spec = TransformSpec(crop=224, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
+    bt = BatchTransform(spec, device=dev)
+    lut = bt.lut(3)
+    L = N.lib()
+    nbuf = 6
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    srcs = [torch.randint(0, 256, (B, 256, 256, 3), dtype=torch.uint8, device=dev, generator=gen) for _ in range(nbuf)]
+    t, l, f = CropFlipParams(42).draw(B, 256, 256, (224, 224), (0, 0), .5)
+    t, l, f = (torch.from_numpy(a).to(dev) for a in (t, l, f))
+    outs = [torch.empty((B, 3, 224, 224), dtype=torch.bfloat16, device=dev) for _ in range(max(2, nstreams))]
+    streams = [torch.cuda.Stream(dev) for _ in range(nstreams)]
+    main = torch.cuda.current_stream(dev)
+
+    def run(n):
+        for st in streams:
+            st.wait_stream(main)
+        for i in range(n):
+            s, o = srcs[i % nbuf], outs[i % len(outs)]
+            rc = L.tb_transform_u8_nhwc_to_nchw(s.data_ptr(), B, 256, 256, 3, s.stride(0), s.stride(1), o.data_ptr(), 1, 224, 224,
+                                                t.data_ptr(), l.data_ptr(), f.data_ptr(), 0, 0, 0, lut.data_ptr(), 0,
+                                                streams[i % nstreams].cuda_stream)
+            assert rc == 0
+        for st in streams:
+            main.wait_stream(st)
+
+    run(10)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(main)
+    run(iters)
+    e1.record(main)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    gbs = 224 * 224 * 9 * B / (ms * 1e-3) / 1e9
+    print(json.dumps({"case": name, "B": B, "ms": ms, "images_per_s": B / (ms * 1e-3), "alg_GBps": gbs,
+                      "frac_measured": gbs / PEAK, "streams": nstreams}), flush=True)
+
+
 def calibrate():
     """Library reference points on the same buffers: a read-only reduction and a copy."""
     dev = torch.device("cuda", 0)
@@ -127,6 +171,12 @@ def main():
         c4 = dict(resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1])
         transform_case("c4_stt_b32", 32, 512, 512, c4, 1572864, 200, params=False)
         transform_case("c4_stt_b256", 256, 512, 512, c4, 1572864, 50, params=False)
+    if want("streams"):
+        for ns in (1, 2, 3):
+            two_stream_case(f"c2_abi_{ns}stream", 512, 400, ns)
+        two_stream_case("c2_abi_1stream_B128", 128, 400, 1)
+        two_stream_case("c2_abi_1stream_B256", 256, 400, 1)
+        two_stream_case("c2_abi_1stream_B1024", 1024, 200, 1)
     if want("calib"):
         calibrate()
     if want("c5"):
