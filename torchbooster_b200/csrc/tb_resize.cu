@@ -222,20 +222,42 @@ __global__ void __launch_bounds__(256) tb_resize_fused_kernel(RsParams p) {
 
 
 // ----------------------------------------------------------------------------------------------
-// fast path: both passes active with at most kRsKS taps (scale factors up to 2, and any upscale),
-// source rows readable as aligned 32-bit words.  Same tiling; per thread the horizontal taps of
-// its column live in registers for the whole tile, the source bytes of a tap window are fetched
-// as words and funnel-shifted once, and the vertical taps of the tile's rows sit in shared memory.
+// fast path: both passes active, scale factor <= 2 on both axes (so every output touches at most
+// FOUR input samples: n <= ceil(2 * support) = 4), source rows readable as aligned 32-bit words.
+//
+// Four 8-bit samples times four 22-bit taps is three DP4A instructions: split each tap into its
+// three bytes, k = k0 + 2^8 k1 + 2^16 k2, then sum(p*k) = D0 + 2^8 D1 + 2^16 D2 with
+// Dm = dp4a(samples, {km of the 4 taps}); every Dm < 2^18, the chain is exact.  The rounding
+// constant 2^21 rides in as 32 << 16.  The result needs no clip: taps are >= 0 and sum to at most
+// 2^22 + 2, so (2^21 + 255 * sum) >> 22 <= 255.
+//
+//   phase 1  horizontal pass, thread <-> resized column for all input rows of the tile: its taps
+//            are three packed registers; a row's 4*C-byte window comes as aligned words + funnel
+//            shift, two PRMTs per channel gather the 4 samples; results go to shared memory
+//            TRANSPOSED and planar, inter[c][column][row], so that ...
+//   phase 2  ... the vertical pass finds its 4 samples (4 consecutive rows) in ONE unaligned word
+//            (two LDS + funnel shift), runs the same DP4A chain, looks the byte up and stores.
+// The column pitch is 4 * odd bytes: lanes (= consecutive columns) never share a bank.
 // ----------------------------------------------------------------------------------------------
-constexpr int kRsKS = 5;
+__device__ __forceinline__ uint32_t tb_dot4(uint32_t px, uint32_t kb0, uint32_t kb1, uint32_t kb2) {
+    uint32_t a = __dp4a(px, kb2, 32u);
+    a = __dp4a(px, kb1, a << 8);
+    a = __dp4a(px, kb0, a << 8);
+    return a >> kPrecisionBits;
+}
+// byte m of each of (up to) four taps -> one word per m
+__device__ __forceinline__ void tb_pack_taps(const int* k, uint32_t* kb) {
+#pragma unroll
+    for (int m = 0; m < 3; ++m)
+        kb[m] = ((uint32_t)(k[0] >> (8 * m)) & 0xffu) | (((uint32_t)(k[1] >> (8 * m)) & 0xffu) << 8) |
+                (((uint32_t)(k[2] >> (8 * m)) & 0xffu) << 16) | (((uint32_t)(k[3] >> (8 * m)) & 0xffu) << 24);
+}
 
 template <typename T, int C>
 __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
-    constexpr int NBYTES = kRsKS * C;                 // bytes of one tap window
-    constexpr int NQ = (NBYTES + 3) / 4;              // aligned words after the shift
-    extern __shared__ __align__(16) uint8_t inter[];  // [nin][row_bytes]
+    extern __shared__ __align__(16) uint8_t inter[];  // [C][TC][col_pitch]
     __shared__ T s_lut[C * 256];
-    __shared__ int s_ky[32][kRsKS];
+    __shared__ uint32_t s_kyb[32][3];
     __shared__ int s_ymin[32];
     tb_grid_dependency_wait();
     for (int i = threadIdx.x; i < C * 256; i += 256) s_lut[i] = ((const T*)p.lut)[i];
@@ -259,12 +281,20 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
         nin = p.by[2 * (ry1 - 1)] + p.by[2 * (ry1 - 1) + 1] - iy0;
     }
     const int ncols = any ? rx1 - rx0 : 0;
-    // vertical taps of the resized rows this tile touches (zero beyond each row's tap count)
-    for (int i = threadIdx.x; i < (ry1 - ry0) * kRsKS; i += 256) {
-        const int rr = i / kRsKS, j = i - rr * kRsKS;
-        const int ry = ry0 + rr;
-        s_ky[rr][j] = (j < p.ksy && j < p.by[2 * ry + 1]) ? p.ky[(size_t)ry * p.ksy + j] : 0;
-        if (j == 0) s_ymin[rr] = p.by[2 * ry] - iy0;
+    const int cp = p.row_bytes;                      // column pitch (bytes), 4 * odd
+    const int plane_b = p.TC * cp;                   // bytes per channel plane of the intermediate
+
+    // vertical taps of the resized rows this tile touches, packed for DP4A
+    if (threadIdx.x < ry1 - ry0) {
+        const int ry = ry0 + threadIdx.x;
+        const int n = p.by[2 * ry + 1];
+        int k[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) k[j] = (j < p.ksy && j < n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+        uint32_t kb[3];
+        tb_pack_taps(k, kb);
+        s_kyb[threadIdx.x][0] = kb[0]; s_kyb[threadIdx.x][1] = kb[1]; s_kyb[threadIdx.x][2] = kb[2];
+        s_ymin[threadIdx.x] = p.by[2 * ry] - iy0;
     }
 
     // ---- phase 1: horizontal pass; thread <-> column, looping over the input rows
@@ -278,34 +308,45 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
             const int cx = c0 + threadIdx.x - grp * nch;
             const int rx = rx0 + cx;
             const int xmin = p.bx[2 * rx], n = p.bx[2 * rx + 1];
-            int k[kRsKS];
+            int k[4];
 #pragma unroll
-            for (int j = 0; j < kRsKS; ++j) k[j] = (j < p.ksx && j < n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+            for (int j = 0; j < 4; ++j) k[j] = (j < p.ksx && j < n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+            uint32_t kb[3];
+            tb_pack_taps(k, kb);
             const int boff = xmin * C;
             const int a = boff & 3;
-            const int nw = (a + n * C + 3) >> 2;                 // words that hold this window
+            const int nw = (a + n * C + 3) >> 2;                 // words that hold this window (<= 4)
             const uint32_t* wp = reinterpret_cast<const uint32_t*>(simg + (boff - a)) + (size_t)(iy0 + grp) * pitch_w;
-            uint8_t* o = inter + (size_t)grp * p.row_bytes + cx * C;
-            for (int r = grp; r < nin; r += ngrp, wp += (size_t)ngrp * pitch_w, o += (size_t)ngrp * p.row_bytes) {
-                uint32_t w[NQ + 1];
+            uint8_t* o = inter + (size_t)cx * cp + grp;
+            constexpr int NQ = C == 3 ? 3 : 1;               // aligned words after the shift
+            constexpr int UR = 4;                            // rows in flight per thread
+            for (int r = grp; r < nin; r += UR * ngrp, wp += (size_t)UR * ngrp * pitch_w, o += UR * ngrp) {
+                uint32_t w[UR][NQ + 1];
 #pragma unroll
-                for (int i = 0; i <= NQ; ++i) w[i] = i < nw ? __ldg(wp + i) : 0u;
-                uint32_t q[NQ];
+                for (int u = 0; u < UR; ++u) {
+                    const bool ok = r + u * ngrp < nin;
 #pragma unroll
-                for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[i], w[i + 1], a * 8);
-                int acc[C];
-#pragma unroll
-                for (int c = 0; c < C; ++c) acc[c] = 1 << (kPrecisionBits - 1);
-#pragma unroll
-                for (int j = 0; j < kRsKS; ++j) {
-#pragma unroll
-                    for (int c = 0; c < C; ++c) {
-                        const int bi = j * C + c;
-                        acc[c] += (int)((q[bi >> 2] >> (8 * (bi & 3))) & 0xffu) * k[j];
-                    }
+                    for (int i = 0; i <= NQ; ++i) w[u][i] = (ok && i < nw) ? __ldg(wp + (size_t)u * ngrp * pitch_w + i) : 0u;
                 }
 #pragma unroll
-                for (int c = 0; c < C; ++c) o[c] = tb_clip8(acc[c]);
+                for (int u = 0; u < UR; ++u) {
+                    if (r + u * ngrp >= nin) break;
+                    uint32_t q[NQ];
+#pragma unroll
+                    for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[u][i], w[u][i + 1], a * 8);
+                    uint8_t* ou = o + u * ngrp;
+                    if (C == 3) {
+                        // samples of channel c sit at bytes c, c+3, c+6, c+9 of the 12-byte window
+                        const uint32_t p0 = __byte_perm(__byte_perm(q[0], q[1], 0x0630), q[2], 0x5210);
+                        const uint32_t p1 = __byte_perm(__byte_perm(q[0], q[1], 0x0741), q[2], 0x6210);
+                        const uint32_t p2 = __byte_perm(__byte_perm(q[0], q[1], 0x0052), q[2], 0x7410);
+                        ou[0] = (uint8_t)tb_dot4(p0, kb[0], kb[1], kb[2]);
+                        ou[plane_b] = (uint8_t)tb_dot4(p1, kb[0], kb[1], kb[2]);
+                        ou[2 * plane_b] = (uint8_t)tb_dot4(p2, kb[0], kb[1], kb[2]);
+                    } else {
+                        ou[0] = (uint8_t)tb_dot4(q[0], kb[0], kb[1], kb[2]);
+                    }
+                }
             }
         }
     }
@@ -314,6 +355,7 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
     // ---- phase 2: vertical pass out of shared memory; thread <-> output column, looping over rows
     T* dimg = (T*)p.dst + (int64_t)b * C * p.out_h * p.out_w;
     const int64_t plane = (int64_t)p.out_h * p.out_w;
+    const uint32_t inter_addr = tb_smem_addr(inter);
     for (int c0 = 0; c0 < nc; c0 += 256) {
         const int nch = min(256, nc - c0);
         const int ngrp = max(1, 256 / nch);
@@ -323,7 +365,7 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
         const int x = x0 + xx;
         const int rx = ox + (flip ? p.out_w - 1 - x : x);
         const bool colin = rx >= 0 && rx < p.rs_w;
-        const uint8_t* col = inter + (size_t)(colin ? rx - rx0 : 0) * C;
+        const uint32_t col = inter_addr + (uint32_t)((colin ? rx - rx0 : 0) * cp);
         for (int yy = grp; yy < nr; yy += ngrp) {
             const int y = y0 + yy;
             const int ry = oy + y;
@@ -332,20 +374,17 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
             for (int c = 0; c < C; ++c) e[c] = 0;
             if (colin && ry >= 0 && ry < p.rs_h) {
                 const int rr = ry - ry0;
-                const uint8_t* q = col + (size_t)s_ymin[rr] * p.row_bytes;
-                int acc[C];
+                const uint32_t kb0 = s_kyb[rr][0], kb1 = s_kyb[rr][1], kb2 = s_kyb[rr][2];
+                const int ymin = s_ymin[rr];
+                const uint32_t wa = col + (uint32_t)(ymin & ~3);
+                const int sh = (ymin & 3) * 8;
 #pragma unroll
-                for (int c = 0; c < C; ++c) acc[c] = 1 << (kPrecisionBits - 1);
-#pragma unroll
-                for (int j = 0; j < kRsKS; ++j) {
-                    const int kk = s_ky[rr][j];
-                    // taps past the row's count are zero; keep their reads inside the tile
-                    const uint8_t* qq = q + (size_t)min(j, nin - 1 - s_ymin[rr]) * p.row_bytes;
-#pragma unroll
-                    for (int c = 0; c < C; ++c) acc[c] += (int)qq[c] * kk;
+                for (int c = 0; c < C; ++c) {
+                    uint32_t lo, hi;
+                    asm("ld.shared.u32 %0, [%1];" : "=r"(lo) : "r"(wa + c * plane_b));
+                    asm("ld.shared.u32 %0, [%1];" : "=r"(hi) : "r"(wa + c * plane_b + 4));
+                    e[c] = tb_dot4(__funnelshift_r(lo, hi, sh), kb0, kb1, kb2);
                 }
-#pragma unroll
-                for (int c = 0; c < C; ++c) e[c] = tb_clip8(acc[c]);
             }
             T* d = dimg + (int64_t)y * p.out_w + x;
 #pragma unroll
@@ -353,6 +392,7 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
         }
     }
 }
+
 
 template <typename T, int C>
 int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, bool fast, cudaStream_t s) {
@@ -415,8 +455,9 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     // resized rows can touch: at most ceil(TR * scale_y) + ks_y rows.
     const double scale_y = rs_h != H ? (double)H / rs_h : 1.0;
     const int budget = 40 * 1024;
-    const bool fast = !(flags & TB_FLAG_FORCE_GENERIC) && p.words_ok && rs_w != W && rs_h != H && ks_x <= kRsKS &&
-                      ks_y <= kRsKS;
+    // scale <= 2 on both axes: at most 4 taps are ever non-zero (n <= ceil(2 * support))
+    const bool fast = !(flags & TB_FLAG_FORCE_GENERIC) && p.words_ok && rs_w != W && rs_h != H &&
+                      (int64_t)W <= 2 * (int64_t)rs_w && (int64_t)H <= 2 * (int64_t)rs_h;
     int TC = out_w < 256 ? out_w : 256;
     // taller tiles recompute fewer halo rows; keep at least ~4 CTAs per SM in the grid
     int TR = ((int64_t)B * ((out_h + 15) / 16) * ((out_w + TC - 1) / TC) >= 4 * (int64_t)dev.sm_count) ? 16 : 8;
@@ -424,14 +465,22 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     auto rowb = [&](int tc) { return (tc * C + 3) & ~3; };
     while (TR > 1 && (int64_t)rows_for(TR) * rowb(TC) > budget) TR >>= 1;
     while (TC > 8 && (int64_t)rows_for(TR) * rowb(TC) > budget) TC = (TC + 1) / 2;
-    const int64_t smem = (int64_t)rows_for(TR) * rowb(TC);
+    int64_t smem = (int64_t)rows_for(TR) * rowb(TC);
     TB_REQUIRE(smem <= dev.max_smem_optin - 8192, "tb_resize: a %dx%d tile needs %lld bytes of shared memory",
                TR, TC, (long long)smem);
+    int col_pitch = 0;
+    if (fast) {
+        // transposed planar intermediate [C][TC][col_pitch]: a column holds the tile's input rows plus
+        // room for the 4-sample window of the last row; pitch = 4 * odd keeps lanes on distinct banks
+        col_pitch = (rows_for(TR) + 4 + 3) & ~3;
+        if (((col_pitch >> 2) & 1) == 0) col_pitch += 4;
+        smem = (int64_t)C * TC * col_pitch + 16;   // + slack: the last 8-byte window may poke past the last column
+    }
     if (TR > out_h) TR = out_h;
     p.TR = TR; p.TC = TC;
     p.tiles_x = (out_w + TC - 1) / TC;
     p.tiles_y = (out_h + TR - 1) / TR;
-    p.row_bytes = rowb(TC);
+    p.row_bytes = fast ? col_pitch : rowb(TC);
     const int64_t blocks = (int64_t)p.tiles_x * p.tiles_y * B;
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize: grid too large");
     cudaStream_t s = (cudaStream_t)stream;
