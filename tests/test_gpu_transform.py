@@ -177,3 +177,21 @@ def test_argument_errors():
     # empty batch is a no-op
     assert L.tb_transform_u8_nhwc_to_nchw(None, 0, 8, 8, 3, 192, 24, None, 0, 8, 8, None, None, None, 0, 0, 0, None,
                                           0, None) == 0
+
+
+def test_pinned_batch_is_read_in_place():
+    """Zero-copy: a pinned host batch goes to the kernel as is (host pointer); same bits as the
+    copied path, for the streaming kernel and for the gather kernel."""
+    rng = np.random.default_rng(12)
+    B = 6
+    batch = torch.from_numpy(rng.integers(0, 256, (B, 64, 80, 3), dtype=np.uint8)).pin_memory()
+    top = rng.integers(0, 64 - 48 + 1, B).astype(np.int32); left = rng.integers(0, 80 - 64 + 1, B).astype(np.int32)
+    flip = rng.integers(0, 2, B).astype(np.uint8)
+    want = TO.transform_batch(batch.numpy(), crop_top=top, crop_left=left, out_size=(48, 64), flip=flip,
+                              mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
+    spec = TransformSpec(crop=(48, 64), flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
+    for flags in (0, N.FLAG_FORCE_GENERIC):
+        for zero_copy in (True, False):
+            bt = BatchTransform(spec, device="cuda", zero_copy=zero_copy)
+            bt.flags = flags
+            assert same(bt(batch, params=(top, left, flip)), want)

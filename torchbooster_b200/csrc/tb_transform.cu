@@ -98,6 +98,7 @@ __global__ void __launch_bounds__(256) tb_xf_generic_kernel(XfParams p, int bloc
 //     [0x10000, 0x20000)  rows: words 0-31 = c0, words 32-63 = c1
 //     [0x20000, 0x30000)  rows: words 0-31 = c2
 constexpr uint32_t kXfSmemEnd = 0x30000u;
+constexpr int kXfHostCtas = 8;       // CTAs of a launch whose source is pinned host memory
 
 __device__ __forceinline__ uint32_t tb_lds32(uint32_t addr) {
     uint32_t v;
@@ -356,8 +357,8 @@ int launch_generic(const XfParams& p, cudaStream_t s) {
 }
 
 template <typename T>
-int launch_stream(const XfParams& p, const TbDevice& dev, cudaStream_t s, int force_rows, int force_warps, bool pdl,
-                  bool* taken) {
+int launch_stream(const XfParams& p, const TbDevice& dev, cudaStream_t s, int force_rows, int force_warps,
+                  int max_ctas, bool pdl, bool* taken) {
     using X = Xf<T>;
     constexpr int PX = X::PX;
     *taken = false;
@@ -404,6 +405,7 @@ int launch_stream(const XfParams& p, const TbDevice& dev, cudaStream_t s, int fo
     g.step_g = 32 % g.gpr;
     int64_t grid = (total + warps - 1) / warps;
     if (grid > dev.sm_count) grid = dev.sm_count;
+    if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
     const int64_t stride = grid * warps;
     g.tile_db = (int)(stride / g.tiles_per_image);
     g.tile_dt = (int)(stride % g.tiles_per_image);
@@ -484,11 +486,24 @@ extern "C" int tb_transform_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, in
         stream_ok = false;
     if (stream_ok) {
         bool taken = false;
-        // development knobs: bits 16-23 warps per CTA, bits 24-31 rows per warp tile
+        // development knobs: bits 8-15 CTA limit, bits 16-23 warps per CTA, bits 24-31 rows per warp tile
         const int fw = (flags >> 16) & 0xff, fr = (flags >> 24) & 0xff;
         const bool pdl = !(flags & TB_FLAG_NO_PDL);
-        rc = dst_dtype == TB_F32 ? launch_stream<float>(p, dev, s, fr, fw, pdl, &taken)
-                                 : launch_stream<uint16_t>(p, dev, s, fr, fw, pdl, &taken);
+        // A batch that lives in pinned HOST memory is read in place: the bulk copies go over PCIe
+        // and fetch only the crop rows.  PCIe needs little parallelism (4 CTAs already saturate it;
+        // whole-row requests were measured slower than row windows), so such a launch takes a few
+        // SMs only and leaves the rest of the GPU to whatever else is running.
+        int max_ctas = (flags >> 8) & 0xff;
+        if (max_ctas == 0) {
+            cudaPointerAttributes pa;
+            if (cudaPointerGetAttributes(&pa, src) == cudaSuccess) {
+                if (pa.type == cudaMemoryTypeHost) max_ctas = kXfHostCtas;
+            } else {
+                (void)cudaGetLastError();
+            }
+        }
+        rc = dst_dtype == TB_F32 ? launch_stream<float>(p, dev, s, fr, fw, max_ctas, pdl, &taken)
+                                 : launch_stream<uint16_t>(p, dev, s, fr, fw, max_ctas, pdl, &taken);
         if (rc) return rc;
         if (taken) return TB_OK;
     }
