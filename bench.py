@@ -186,13 +186,21 @@ def run_reference(args, wl):
         return
     workers = min(host_threads(), 64)
     torch.set_num_threads(max(1, host_threads()))
+    # A step is one batch of the workload; for very long runs the per-step sample shrinks so that
+    # the whole run stays within a few minutes (about one million images in total).
+    wl = dict(wl)
+    full_b = wl["B"]
+    if args.steps * full_b > 1_000_000:
+        wl["B"] = max(16, (1_000_000 // args.steps) // 16 * 16)
     # untimed warm-up covers one full round of worker prefetch, so that timed steps are steady state
     ips, done, dt = cpu_path(wl, args.steps, max(args.warmup, workers + 2), workers)
     line = {
         "impl": "reference", "metric": "images/sec transformed+scored", "value": ips, "unit": "images/s",
         "n_gpus": args.gpus, "steps": done, "warmup": args.warmup, "ms_per_step": dt / max(done, 1) * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": wl["desc"], "per_step": f"one batch of {wl['B']} images on the host CPU"},
+        "config": {"workload": wl["desc"],
+                   "per_step": f"one batch of {wl['B']} images on the host CPU" +
+                               ("" if wl["B"] == full_b else f" (bounded sample of the {full_b}-image batch)")},
         "cpu_baseline": {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
                          "sample": f"{done} batches of {wl['B']} images; torchvision {__import__('torchvision').__version__} "
                                    f"PIL transforms in {workers} DataLoader workers + accuracy/topk/bincount; {cpu_model()}"},
