@@ -1,5 +1,5 @@
-"""Dataset drop-ins: ``Split`` and ``BaseDataset`` with the signatures of
-``torchbooster/dataset.py:15-22`` and ``:25-73``."""
+"""Dataset drop-ins with the reference's surface: ``Split`` (``torchbooster/dataset.py:15-22``) and
+``BaseDataset`` (``:25-73``), backed by this package's own read-only LMDB reader."""
 from __future__ import annotations
 
 from enum import Enum
@@ -11,36 +11,27 @@ from torch.utils.data import Dataset
 
 from .lmdb import LMDBReader
 
-
-class Split(Enum):
-    """Dataset split (train, validation, test)."""
-    TRAIN = "train"
-    VALID = "validation"
-    TEST = "test"
+Split = Enum("Split", {"TRAIN": "train", "VALID": "validation", "TEST": "test"})
+Split.__doc__ = "Dataset split: ``TRAIN`` / ``VALID`` / ``TEST`` (values 'train', 'validation', 'test')."
 
 
 class BaseDataset(Dataset):
-    """Base class of LMDB-backed datasets.
+    """Root of LMDB-backed datasets.
 
-    Holds an ``LMDBReader`` over ``path`` (opened lazily, per process) and a ``transform``;
-    subclasses implement ``__getitem__`` (decode ``self.lmdb_reader[idx]``, apply
-    ``self.transform``) and ``prepare``.  Defaults follow the reference, including its
-    ``map_size = 1024 * 4`` (``torchbooster/dataset.py:49``), which is harmless for a read-only map.
+    The constructor only records its arguments and builds ``self.lmdb_reader`` (which opens the
+    database lazily, once per process).  A concrete dataset decodes ``self.lmdb_reader[idx]`` in
+    ``__getitem__`` and applies ``self.transform``; ``prepare`` builds the database.  Both raise
+    ``NotImplementedError`` here.  ``len(dataset)`` is the database's ``length`` record.
+
+    ``map_size`` keeps the reference default of ``1024 * 4`` (``torchbooster/dataset.py:49``); it
+    is irrelevant for a read-only mapping, as is ``max_readers``.
     """
 
-    def __init__(
-        self,
-        path: Path,
-        transform: Module = None,
-        map_size: int = 1024 * 4,
-        max_readers: int = 126,
-    ) -> None:
+    def __init__(self, path: Path, transform: Module = None, map_size: int = 1024 * 4, max_readers: int = 126) -> None:
         super().__init__()
-        self.path = path
-        self.transform = transform
-        self.map_size = map_size
-        self.max_readers = max_readers
-        self.lmdb_reader = LMDBReader(self.path, map_size=self.map_size, max_readers=self.max_readers)
+        self.path, self.transform = path, transform
+        self.map_size, self.max_readers = map_size, max_readers
+        self.lmdb_reader = LMDBReader(path, map_size=map_size, max_readers=max_readers)
 
     def __len__(self) -> int:
         return len(self.lmdb_reader)
