@@ -145,3 +145,34 @@ def test_full_size_c5_properties():
 def test_cpu_tensors_are_rejected():
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         M.accuracy(torch.randn(4, 3), torch.zeros(4, dtype=torch.int64))
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_fuzz_rows_against_rank_rule(seed):
+    """Random widths, strides, dtypes, duplicated values (ties), NaN / inf sprinkles and invalid
+    labels against the rank-rule oracle."""
+    gen = torch.Generator().manual_seed(500 + seed)
+    for _ in range(8):
+        C = int(torch.randint(1, 300, (1,), generator=gen))
+        n = int(torch.randint(1, 80, (1,), generator=gen))
+        k = int(torch.randint(1, 7, (1,), generator=gen))
+        dtype = [torch.float32, torch.bfloat16, torch.float16][int(torch.randint(0, 3, (1,), generator=gen))]
+        pad = int(torch.randint(0, 9, (1,), generator=gen))
+        base = torch.randint(-4, 5, (n, C + pad), generator=gen).float() / 2            # heavy ties
+        mask = torch.rand(n, C + pad, generator=gen)
+        base[mask < 0.02] = float("nan")
+        base[(mask >= 0.02) & (mask < 0.03)] = float("inf")
+        base[(mask >= 0.03) & (mask < 0.04)] = float("-inf")
+        base[(mask >= 0.04) & (mask < 0.06)] = -0.0
+        logits = base.to(dtype).cuda()[:, pad // 2: pad // 2 + C]                        # strided, often misaligned rows
+        labels = torch.randint(-1, C + 1, (n,), generator=gen)
+        st = M.MetricState(C, k=k, device="cuda")
+        st.update(logits, labels.cuda())
+        res = st.compute()
+        ref = logits.float().cpu()
+        rank = MO.label_rank(ref, labels)
+        valid = ((labels >= 0) & (labels < C)).numpy()
+        assert res["correct_1"] == int(((rank < 1) & valid).sum()), (seed, C, n, dtype)
+        assert res[f"correct_{k}"] == int(((rank < k) & valid).sum()), (seed, C, n, k, dtype)
+        assert res["invalid_labels"] == int((~valid).sum())
+        assert np.array_equal(res["confusion"].cpu().numpy(), MO.confusion(ref, labels, C)), (seed, C, n, dtype)

@@ -83,3 +83,48 @@ def test_resize_linearity_property_full_size():
     assert bool((oa <= ob).all())
     c = torch.full((2, 512, 512, 3), 77, dtype=torch.uint8, device="cuda")
     assert bool((bt(c) == torch.tensor(77.0).div(255)).all())
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_fuzz_resize_against_integer_oracle(seed):
+    """Random source / target sizes (up- and down-scaling, one-pass cases, > 2x reductions), crops
+    with constant padding and flips against the integer restatement of Pillow's resample (pinned
+    to Pillow in tests/test_oracle.py) followed by the index map."""
+    from oracle import resize_oracle as RO
+    rng = np.random.default_rng(2000 + seed)
+    for _ in range(8):
+        C = int(rng.choice([1, 3, 3]))
+        H, W = int(rng.integers(6, 110)), int(rng.integers(6, 130))
+        if rng.random() < 0.5:
+            W = int(rng.choice([32, 64, 96, 128]))            # word-readable rows: the DP4A path when scale <= 2
+        rs_h = int(np.clip(int(H * rng.uniform(0.3, 1.6)), 1, 200))
+        rs_w = int(np.clip(int(W * rng.uniform(0.3, 1.6)), 1, 200))
+        if rng.random() < 0.15:
+            rs_h = H
+        if rng.random() < 0.15:
+            rs_w = W
+        pad = int(rng.integers(0, 4))
+        th = int(rng.integers(1, rs_h + 2 * pad + 1)); tw = int(rng.integers(1, rs_w + 2 * pad + 1))
+        B = int(rng.integers(1, 4))
+        dtype = [torch.float32, torch.bfloat16][int(rng.integers(0, 2))]
+        batch = rng.integers(0, 256, (B, H, W, C), dtype=np.uint8)
+        top = rng.integers(0, rs_h + 2 * pad - th + 1, B).astype(np.int32)
+        left = rng.integers(0, rs_w + 2 * pad - tw + 1, B).astype(np.int32)
+        flip = rng.integers(0, 2, B).astype(np.uint8)
+        mean = tuple(float(v) for v in rng.uniform(0.2, 0.6, C)); std = tuple(float(v) for v in rng.uniform(0.1, 0.4, C))
+        x = torch.arange(256, dtype=torch.uint8).to(torch.float32).div(255)
+        lut = ((x[None, :] - torch.tensor(mean)[:, None]) / torch.tensor(std)[:, None]).to(dtype)
+        view = torch.int32 if dtype == torch.float32 else torch.int16
+        want = []
+        for b in range(B):
+            img = batch[b] if C == 3 else batch[b, :, :, 0]
+            rs = RO.resize_u8(img, rs_h, rs_w)
+            rs = rs if C == 3 else rs[:, :, None]
+            want.append(TO.index_map_sample(rs, lut.view(view).numpy(), top=int(top[b]), left=int(left[b]), out_h=th,
+                                            out_w=tw, flip=bool(flip[b]), pad_y=pad, pad_x=pad, pad_mode="constant"))
+        spec = TransformSpec(resize=(rs_h, rs_w), crop=(th, tw), padding=pad, flip_p=.5, mean=mean, std=std, dtype=dtype)
+        for flags in (0, 1):
+            bt = BatchTransform(spec, device="cuda")
+            bt.flags = flags
+            got = bt(torch.from_numpy(batch).cuda(), params=(top, left, flip)).cpu().view(view).numpy()
+            assert np.array_equal(got, np.stack(want)), (seed, C, H, W, rs_h, rs_w, th, tw, pad, dtype, flags)

@@ -195,3 +195,48 @@ def test_pinned_batch_is_read_in_place():
             bt = BatchTransform(spec, device="cuda", zero_copy=zero_copy)
             bt.flags = flags
             assert same(bt(batch, params=(top, left, flip)), want)
+
+
+def _cpu_lut(mean, std, dtype):
+    x = torch.arange(256, dtype=torch.uint8).to(torch.float32).div(255)
+    t = (x[None, :] - torch.tensor(mean, dtype=torch.float32)[:, None]) / torch.tensor(std, dtype=torch.float32)[:, None]
+    return t.to(dtype)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_fuzz_geometry_against_index_map(seed):
+    """Random shapes / paddings / modes / dtypes against the numpy index-map restatement (itself
+    pinned to torchvision in tests/test_oracle.py); C == 3 cases run the streaming kernel, the
+    gather kernel and the forced-streaming route."""
+    rng = np.random.default_rng(1000 + seed)
+    for _ in range(10):
+        C = int(rng.choice([1, 3, 3, 3, 4]))
+        H, W = int(rng.integers(4, 90)), int(rng.integers(4, 120))
+        if rng.random() < 0.4:
+            W = int(rng.choice([16, 32, 64, 48, 80, 96]))        # 16-byte aligned pitches reach the streaming kernel
+        mode = str(rng.choice(["constant", "reflect", "edge", "symmetric"]))
+        pad = int(rng.integers(0, min(H, W, 9)))
+        dtype = [torch.float32, torch.bfloat16, torch.float16][int(rng.integers(0, 3))]
+        px = 4 if dtype == torch.float32 else 8
+        th = int(rng.integers(1, H + 2 * pad + 1))
+        tw = int(rng.integers(1, W + 2 * pad + 1))
+        if rng.random() < 0.6 and (W + 2 * pad) >= px:
+            tw = max(px, tw // px * px)
+        B = int(rng.integers(1, 6))
+        batch = rng.integers(0, 256, (B, H, W, C), dtype=np.uint8)
+        top = rng.integers(0, H + 2 * pad - th + 1, B).astype(np.int32)
+        left = rng.integers(0, W + 2 * pad - tw + 1, B).astype(np.int32)
+        flip = rng.integers(0, 2, B).astype(np.uint8)
+        mean = tuple(float(v) for v in rng.uniform(0.2, 0.6, C))
+        std = tuple(float(v) for v in rng.uniform(0.1, 0.4, C))
+        lut = _cpu_lut(mean, std, dtype)
+        lut_np = lut.view(torch.int16 if dtype != torch.float32 else torch.int32).numpy()
+        want = np.stack([TO.index_map_sample(batch[b], lut_np, top=int(top[b]), left=int(left[b]), out_h=th, out_w=tw,
+                                             flip=bool(flip[b]), pad_y=pad, pad_x=pad, pad_mode=mode) for b in range(B)])
+        spec = TransformSpec(crop=(th, tw), padding=pad, padding_mode=mode, flip_p=.5, mean=mean, std=std, dtype=dtype)
+        for flags in (0, N.FLAG_FORCE_GENERIC, N.FLAG_FORCE_STREAM):
+            bt = BatchTransform(spec, device="cuda")
+            bt.flags = flags
+            got = bt(torch.from_numpy(batch).cuda(), params=(top, left, flip)).cpu()
+            got_bits = got.view(torch.int16 if dtype != torch.float32 else torch.int32).numpy()
+            assert np.array_equal(got_bits, want), (seed, C, H, W, th, tw, pad, mode, dtype, flags)

@@ -164,7 +164,6 @@ struct XfGeom {
     int contiguous;           // crop rows are whole source rows back to back: one bulk copy per tile
     int tiles_per_image, total_tiles;
     int gpr;                  // 16-byte output groups ("units") per row
-    uint32_t gpr_magic;
     int step_r, step_g;       // 32 units further = (step_r rows, step_g groups) further
     int tile_db, tile_dt;     // stride of the tile walk (all warps of the grid) as (images, tiles)
     int stage_bytes;
@@ -257,7 +256,7 @@ __global__ void __launch_bounds__(768, 1) tb_xf_stream_kernel(XfParams p, XfGeom
 
     const uint32_t base0 = X::base(0, lane), base1 = X::base(1, lane), base2 = X::base(2, lane);
     const int64_t plane = (int64_t)p.out_h * p.out_w;
-    const int ur0 = (int)__umulhi((uint32_t)lane, g.gpr_magic);   // (row, group) of this lane's first unit
+    const int ur0 = lane / g.gpr;                                   // (row, group) of this lane's first unit
     const int ug0 = lane - ur0 * g.gpr;
 
     uint32_t phases = 0;     // bit s = parity to wait for on stage s
@@ -400,7 +399,6 @@ int launch_stream(const XfParams& p, const TbDevice& dev, cudaStream_t s, int fo
     const int64_t total = (int64_t)g.tiles_per_image * p.B;
     if (total >= (int64_t)1 << 30) return TB_OK;
     g.total_tiles = (int)total;
-    g.gpr_magic = (uint32_t)(((uint64_t)1 << 32) / (uint32_t)g.gpr) + 1u;
     g.step_r = 32 / g.gpr;
     g.step_g = 32 % g.gpr;
     int64_t grid = (total + warps - 1) / warps;
