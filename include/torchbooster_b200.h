@@ -138,6 +138,22 @@ TB_API int tb_resize_bilinear_u8_nhwc_to_nchw(
     const void* lut, int flags, tb_stream_t stream);
 
 /*
+ * T.RandomResizedCrop: every sample's own source box is resized (Pillow-exact bilinear, taps
+ * computed on the device in float64 exactly as Pillow does) to (out_h, out_w), then flip, table
+ * lookup and cast.  Replaces T.RandomResizedCrop + T.ToTensor + T.Normalize
+ * (examples/img_stt/online/online.py:173 -> torchvision/transforms/transforms.py RandomResizedCrop.forward
+ * -> F.resized_crop = F.crop then F.resize).
+ *   box : DEVICE int32 [B][4] = top, left, height, width of the source box (RandomResizedCrop.get_params);
+ *         a box outside the image yields zeros for that sample
+ * C in {1,3}.  The source may be at most twice the output size per axis (TB_ENOTSUP otherwise) and
+ * its base / row pitch / batch stride must be multiples of 4 bytes.
+ */
+TB_API int tb_resized_crop_bilinear_u8_nhwc_to_nchw(
+    const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride, int64_t src_row_pitch,
+    const int32_t* box, void* dst, int dst_dtype, int out_h, int out_w,
+    const uint8_t* flip, const void* lut, int flags, tb_stream_t stream);
+
+/*
  * One pass over a logits matrix: top-1 and top-k correct counts and confusion-matrix bins.
  * Replaces torchbooster.metrics.accuracy (torchbooster/metrics.py:11-27: argmax == labels, sum)
  * -- the count, before the division -- and adds the top-k / confusion accumulators the north

@@ -34,3 +34,20 @@ def draw_crop_flip(seed: int, batch: int, h: int, w: int, th: int, tw: int, padd
     finally:
         torch.set_rng_state(state)
     return top, left, flip
+
+
+def draw_resized_crop_flip(seed: int, batch: int, h: int, w: int, scale=(0.08, 1.0), ratio=(3 / 4, 4 / 3), p: float = 0.5):
+    """Literal per-sample ``T.RandomResizedCrop.get_params`` then ``torch.rand(1) < p`` draws
+    (``examples/img_stt/online/online.py:173`` builds ``T.RandomResizedCrop(conf.size)``)."""
+    state = torch.get_rng_state()
+    try:
+        torch.manual_seed(seed)
+        img = Image.new("L", (w, h))
+        box = np.zeros((batch, 4), np.int32)
+        flip = np.zeros(batch, np.uint8)
+        for b in range(batch):
+            box[b] = T.RandomResizedCrop.get_params(img, list(scale), list(ratio))
+            flip[b] = 1 if bool(torch.rand(1) < p) else 0
+    finally:
+        torch.set_rng_state(state)
+    return box, flip

@@ -31,6 +31,7 @@ def transform_sample(
     padding: int = 0,
     padding_mode: str = "constant",
     crop: Optional[Sequence[int]] = None,   # (top, left, h, w) in padded coordinates
+    resized_crop: Optional[Sequence[int]] = None,   # (top, left, h, w, out_h, out_w): T.RandomResizedCrop.forward
     flip: bool = False,
     mean=None,
     std=None,
@@ -54,6 +55,9 @@ def transform_sample(
         pil = F.pad(pil, padding, 0, padding_mode)
     if crop is not None:
         pil = F.crop(pil, *[int(v) for v in crop])
+    if resized_crop is not None:
+        i, j, h, w, oh, ow = [int(v) for v in resized_crop]
+        pil = F.resized_crop(pil, i, j, h, w, [oh, ow])
     if flip:
         pil = F.hflip(pil)
     t = F.to_tensor(pil)
@@ -65,7 +69,7 @@ def transform_sample(
 
 
 def transform_batch(batch: np.ndarray, *, crop_top=None, crop_left=None, out_size=None,
-                    flip=None, **kw) -> torch.Tensor:
+                    flip=None, boxes=None, **kw) -> torch.Tensor:
     """``[B,H,W,C]`` uint8 -> ``[B,C,h,w]``; default collate = ``torch.stack``."""
     if isinstance(batch, torch.Tensor):
         batch = batch.cpu().numpy()
@@ -75,7 +79,10 @@ def transform_batch(batch: np.ndarray, *, crop_top=None, crop_left=None, out_siz
         if out_size is not None and crop_top is not None:
             crop = (int(crop_top[b]), int(crop_left[b]), int(out_size[0]), int(out_size[1]))
         f = bool(flip[b]) if flip is not None else False
-        out.append(transform_sample(batch[b], crop=crop, flip=f, **kw))
+        rc = None
+        if boxes is not None:
+            rc = tuple(int(v) for v in boxes[b]) + (int(out_size[0]), int(out_size[1]))
+        out.append(transform_sample(batch[b], crop=crop, resized_crop=rc, flip=f, **kw))
     return torch.stack(out)
 
 

@@ -123,6 +123,15 @@ def transform_torchvision():
     res = [F.normalize(F.to_tensor(F.center_crop(F.resize(Image.fromarray(batch_e[b]), 32), 32)), *IMAGENET)
            for b in range(2)]
     out["c4_in"], out["c4_out"] = batch_e, torch.stack(res).numpy()
+    batch_f = rng.integers(0, 256, (3, 40, 48, 3), dtype=np.uint8)    # RandomResizedCrop(24) with explicit boxes + flip
+    boxes = np.array([[3, 5, 30, 36], [0, 0, 40, 48], [10, 20, 13, 17]]); flip = np.array([1, 0, 1])
+    res = []
+    for b in range(3):
+        im = F.resized_crop(Image.fromarray(batch_f[b]), *[int(v) for v in boxes[b]], [24, 24])
+        if flip[b]:
+            im = F.hflip(im)
+        res.append(F.normalize(F.to_tensor(im), IMAGENET[0], IMAGENET[1]))
+    out["rrc_in"], out["rrc_boxes"], out["rrc_flip"], out["rrc_out"] = batch_f, boxes, flip, torch.stack(res).numpy()
     np.savez_compressed(HERE / "transform_torchvision.npz", **out)
 
 
@@ -150,6 +159,18 @@ def params_torchvision():
             i, j, _, _ = T.RandomCrop.get_params(img, (th, tw))
             rows.append((i, j, int(bool(torch.rand(1) < 0.5))))
         out[f"{name}_cfg"] = np.array([seed, B, h, w, th, tw, pad])
+        out[f"{name}_params"] = np.array(rows, np.int64)
+    # T.RandomResizedCrop.get_params + flip draw (examples/img_stt/online/online.py:173)
+    for name, (seed, B, h, w, scale, ratio) in {"rrc_c2": (42, 96, 256, 256, (0.08, 1.0), (3 / 4, 4 / 3)),
+                                                "rrc_wide": (5, 64, 48, 300, (0.3, 1.0), (0.9, 1.1)),
+                                                "rrc_tall": (9, 64, 300, 40, (0.08, 1.0), (3 / 4, 4 / 3))}.items():
+        torch.manual_seed(seed)
+        img = Image.new("L", (w, h))
+        rows = []
+        for _ in range(B):
+            i, j, hh, ww = T.RandomResizedCrop.get_params(img, list(scale), list(ratio))
+            rows.append((i, j, hh, ww, int(bool(torch.rand(1) < 0.5))))
+        out[f"{name}_cfg"] = np.array([seed, B, h, w, *scale, *ratio], np.float64)
         out[f"{name}_params"] = np.array(rows, np.int64)
     np.savez_compressed(HERE / "params_torchvision.npz", **out)
 

@@ -206,3 +206,20 @@ def test_world_size_2_gloo(tmp_path):
         assert np.array_equal(r["buffer"][4:].view(7, 7).numpy(), MO.confusion(L, Y, 7))
         assert r["loss"].tolist() == [1.0, 2.0]
     assert res[0]["gathered"] == [0.0, 1.0] and res[1]["gathered"] is None
+
+
+def test_resized_crop_replay_equals_torchvision_golden(golden):
+    from torchbooster_b200.transforms import ResizedCropParams
+    g = golden("params_torchvision.npz")
+    for name in ("rrc_c2", "rrc_wide", "rrc_tall"):
+        cfg = g[f"{name}_cfg"]
+        seed, B, h, w = (int(v) for v in cfg[:4])
+        rng = ResizedCropParams(seed, scale=tuple(cfg[4:6]), ratio=tuple(cfg[6:8]))
+        half = B // 3
+        b1, f1 = rng.draw(half, h, w, 0.5)          # two calls: the unused words carry over
+        b2, f2 = rng.draw(B - half, h, w, 0.5)
+        want = g[f"{name}_params"]
+        assert np.array_equal(np.concatenate([b1, b2]), want[:, :4]), name
+        assert np.array_equal(np.concatenate([f1, f2]), want[:, 4]), name
+    with pytest.raises(ValueError, match="excludes"):
+        TransformSpec(random_resized_crop=24, crop=8)

@@ -149,3 +149,19 @@ def test_rank_rule_ties_and_nan():
     assert MO.label_rank(lg, torch.tensor([2, 3, 0])).tolist() == [2, 1, 1]
     assert MO.label_rank(lg, torch.tensor([0, 0, 1])).tolist() == [0, 0, 0]
     assert MO.label_rank(lg, torch.tensor([7, -1, 0])).tolist() == [4, 4, 1]
+
+
+def test_resized_crop_oracle_matches_golden_and_integer_restatement(golden):
+    g = golden("transform_torchvision.npz")
+    out = TO.transform_batch(g["rrc_in"], boxes=g["rrc_boxes"], out_size=(24, 24), flip=g["rrc_flip"],
+                             mean=IMAGENET[0], std=IMAGENET[1])
+    assert np.array_equal(out.numpy(), g["rrc_out"])
+    # F.resized_crop == integer resample of the cropped box
+    for b in range(3):
+        i, j, h, w = g["rrc_boxes"][b]
+        rs = RO.resize_u8(np.ascontiguousarray(g["rrc_in"][b][i:i + h, j:j + w]), 24, 24)
+        if g["rrc_flip"][b]:
+            rs = rs[:, ::-1]
+        ref = torch.from_numpy(np.ascontiguousarray(rs)).permute(2, 0, 1).float().div(255)
+        ref = (ref - torch.tensor(IMAGENET[0]).view(3, 1, 1)) / torch.tensor(IMAGENET[1]).view(3, 1, 1)
+        assert torch.equal(ref, out[b])

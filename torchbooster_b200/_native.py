@@ -34,6 +34,8 @@ SIGNATURES = {
     "tb_resize_bilinear_u8_nhwc_to_nchw": (_i32, [_vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _i32,
                                                   _vp, _vp, _i32, _vp, _vp, _i32, _vp, _i32, _i32, _i32,
                                                   _vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp]),
+    "tb_resized_crop_bilinear_u8_nhwc_to_nchw": (_i32, [_vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp, _vp, _i32, _i32, _i32,
+                                                        _vp, _vp, _i32, _vp]),
     "tb_metrics_update": (_i32, [_vp, _i32, _i64, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
     "tb_running_sum_update": (_i32, [_vp, _i32, _i64, _vp, _vp]),
     "tb_lmdb_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),

@@ -85,6 +85,7 @@ struct RsParams {
     int TR, TC, tiles_x, tiles_y;
     int row_bytes;     // bytes per intermediate row in shared memory (multiple of 4)
     int words_ok;      // source rows may be read as aligned 32-bit words
+    const int32_t* box;  // resized-crop mode: per-sample source box [B][4] = top, left, height, width
 };
 
 __device__ __forceinline__ uint8_t tb_clip8(int acc) {
@@ -253,7 +254,45 @@ __device__ __forceinline__ void tb_pack_taps(const int* k, uint32_t* kb) {
                 (((uint32_t)(k[2] >> (8 * m)) & 0xffu) << 16) | (((uint32_t)(k[3] >> (8 * m)) & 0xffu) << 24);
 }
 
-template <typename T, int C>
+// One output position's taps, computed on the device exactly as tb_resize_taps does on the host
+// (and Pillow in C): float64, explicit round-to-nearest operations in Pillow's evaluation order,
+// no FMA contraction.  Valid for support <= 2 (at most 4 taps).
+struct Tap4 {
+    int xmin, n;
+    int k[4];
+};
+__device__ __forceinline__ Tap4 tb_bilinear_tap(int in_size, int out_size, int xx) {
+    const double scale = __ddiv_rn((double)in_size, (double)out_size);
+    const double fs = scale < 1.0 ? 1.0 : scale;      // filterscale; support = 1.0 * filterscale
+    const double center = __dmul_rn((double)xx + 0.5, scale);
+    const double ss = __ddiv_rn(1.0, fs);
+    Tap4 t;
+    t.xmin = (int)__dadd_rn(__dsub_rn(center, fs), 0.5);
+    if (t.xmin < 0) t.xmin = 0;
+    int xmax = (int)__dadd_rn(__dadd_rn(center, fs), 0.5);
+    if (xmax > in_size) xmax = in_size;
+    t.n = xmax - t.xmin;
+    double w[4], ww = 0.0;
+#pragma unroll
+    for (int x = 0; x < 4; ++x) {
+        double a = __dmul_rn(__dadd_rn(__dsub_rn((double)(x + t.xmin), center), 0.5), ss);
+        if (a < 0.0) a = -a;
+        w[x] = (x < t.n && a < 1.0) ? __dsub_rn(1.0, a) : 0.0;
+        if (x < t.n) ww = __dadd_rn(ww, w[x]);
+    }
+#pragma unroll
+    for (int x = 0; x < 4; ++x) {
+        double v = w[x];
+        if (x < t.n && ww != 0.0) v = __ddiv_rn(v, ww);
+        t.k[x] = x < t.n ? (int)__dadd_rn(0.5, __dmul_rn(v, 4194304.0)) : 0;
+    }
+    return t;
+}
+
+// BOX = false: T.Resize of the whole image, taps from the host-built tables, then crop / flip.
+// BOX = true : T.RandomResizedCrop -- every sample resizes its own source box to the output size;
+//              taps are computed in the kernel (tb_bilinear_tap), no tables, no extra crop.
+template <typename T, int C, bool BOX>
 __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
     extern __shared__ __align__(16) uint8_t inter[];  // [C][TC][col_pitch]
     __shared__ T s_lut[C * 256];
@@ -268,33 +307,52 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
     const int b = t / p.tiles_y;
     const int y0 = ty * p.TR, x0 = tx * p.TC;
     const int nr = min(p.TR, p.out_h - y0), nc = min(p.TC, p.out_w - x0);
-    const int oy = (p.top ? p.top[b] : 0) + p.off_y;
-    const int ox = (p.left ? p.left[b] : 0) + p.off_x;
+    // source box of this sample (whole image unless BOX) and placement of the output in the resized image
+    int box_top = 0, box_left = 0, in_h = p.H, in_w = p.W;
+    if constexpr (BOX) {
+        box_top = p.box[4 * b]; box_left = p.box[4 * b + 1]; in_h = p.box[4 * b + 2]; in_w = p.box[4 * b + 3];
+        // a box the host did not vouch for (outside the image, or more than 2x the output) yields zeros
+        if (box_top < 0 || box_left < 0 || in_h < 1 || in_w < 1 || box_top + in_h > p.H || box_left + in_w > p.W ||
+            in_h > 2 * p.rs_h || in_w > 2 * p.rs_w)
+            in_h = in_w = 0;
+    }
+    const int oy = BOX ? 0 : (p.top ? p.top[b] : 0) + p.off_y;
+    const int ox = BOX ? 0 : (p.left ? p.left[b] : 0) + p.off_x;
     const bool flip = p.flip ? (p.flip[b] != 0) : false;
     const int ry0 = max(oy + y0, 0), ry1 = min(oy + y0 + nr, p.rs_h);
     const int xs0 = flip ? p.out_w - x0 - nc : x0;
     const int rx0 = max(ox + xs0, 0), rx1 = min(ox + xs0 + nc, p.rs_w);
-    const bool any = ry1 > ry0 && rx1 > rx0;
+    const bool any = ry1 > ry0 && rx1 > rx0 && in_h > 0;
     int iy0 = 0, nin = 0;
     if (any) {
-        iy0 = p.by[2 * ry0];
-        nin = p.by[2 * (ry1 - 1)] + p.by[2 * (ry1 - 1) + 1] - iy0;
+        if constexpr (BOX) {
+            const Tap4 first = tb_bilinear_tap(in_h, p.rs_h, ry0), last = tb_bilinear_tap(in_h, p.rs_h, ry1 - 1);
+            iy0 = first.xmin;
+            nin = last.xmin + last.n - iy0;
+        } else {
+            iy0 = p.by[2 * ry0];
+            nin = p.by[2 * (ry1 - 1)] + p.by[2 * (ry1 - 1) + 1] - iy0;
+        }
     }
     const int ncols = any ? rx1 - rx0 : 0;
     const int cp = p.row_bytes;                      // column pitch (bytes), 4 * odd
     const int plane_b = p.TC * cp;                   // bytes per channel plane of the intermediate
 
     // vertical taps of the resized rows this tile touches, packed for DP4A
-    if (threadIdx.x < ry1 - ry0) {
+    if (any && threadIdx.x < ry1 - ry0) {
         const int ry = ry0 + threadIdx.x;
-        const int n = p.by[2 * ry + 1];
-        int k[4];
+        Tap4 tp;
+        if constexpr (BOX) {
+            tp = tb_bilinear_tap(in_h, p.rs_h, ry);
+        } else {
+            tp.xmin = p.by[2 * ry]; tp.n = p.by[2 * ry + 1];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) k[j] = (j < p.ksy && j < n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+            for (int j = 0; j < 4; ++j) tp.k[j] = (j < p.ksy && j < tp.n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+        }
         uint32_t kb[3];
-        tb_pack_taps(k, kb);
+        tb_pack_taps(tp.k, kb);
         s_kyb[threadIdx.x][0] = kb[0]; s_kyb[threadIdx.x][1] = kb[1]; s_kyb[threadIdx.x][2] = kb[2];
-        s_ymin[threadIdx.x] = p.by[2 * ry] - iy0;
+        s_ymin[threadIdx.x] = tp.xmin - iy0;
     }
 
     // ---- phase 1: horizontal pass; thread <-> column, looping over the input rows
@@ -307,16 +365,22 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
         if (grp < ngrp) {
             const int cx = c0 + threadIdx.x - grp * nch;
             const int rx = rx0 + cx;
-            const int xmin = p.bx[2 * rx], n = p.bx[2 * rx + 1];
-            int k[4];
+            Tap4 tp;
+            if constexpr (BOX) {
+                tp = tb_bilinear_tap(in_w, p.rs_w, rx);
+            } else {
+                tp.xmin = p.bx[2 * rx]; tp.n = p.bx[2 * rx + 1];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) k[j] = (j < p.ksx && j < n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+                for (int j = 0; j < 4; ++j) tp.k[j] = (j < p.ksx && j < tp.n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+            }
+            const int n = tp.n;
             uint32_t kb[3];
-            tb_pack_taps(k, kb);
-            const int boff = xmin * C;
+            tb_pack_taps(tp.k, kb);
+            const int boff = (box_left + tp.xmin) * C;
             const int a = boff & 3;
             const int nw = (a + n * C + 3) >> 2;                 // words that hold this window (<= 4)
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(simg + (boff - a)) + (size_t)(iy0 + grp) * pitch_w;
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(simg + (boff - a)) +
+                                 (size_t)(box_top + iy0 + grp) * pitch_w;
             uint8_t* o = inter + (size_t)cx * cp + grp;
             constexpr int NQ = C == 3 ? 3 : 1;               // aligned words after the shift
             constexpr int UR = 4;                            // rows in flight per thread
@@ -372,7 +436,7 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
             uint32_t e[C];
 #pragma unroll
             for (int c = 0; c < C; ++c) e[c] = 0;
-            if (colin && ry >= 0 && ry < p.rs_h) {
+            if (any && colin && ry >= 0 && ry < p.rs_h) {
                 const int rr = ry - ry0;
                 const uint32_t kb0 = s_kyb[rr][0], kb1 = s_kyb[rr][1], kb2 = s_kyb[rr][2];
                 const int ymin = s_ymin[rr];
@@ -405,10 +469,12 @@ int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, 
         attr_set[dev] = true;
     }
     if (fast && smem <= 40 * 1024) {
-        tb_resize_fast_kernel<T, C><<<(unsigned)blocks, 256, smem, s>>>(p);
+        if (p.box) tb_resize_fast_kernel<T, C, true><<<(unsigned)blocks, 256, smem, s>>>(p);
+        else tb_resize_fast_kernel<T, C, false><<<(unsigned)blocks, 256, smem, s>>>(p);
         TB_LAUNCH_CHECK("tb_resize_fast_kernel");
         return TB_OK;
     }
+    if (p.box) return tb_fail(TB_ENOTSUP, "tb_resized_crop: tile does not fit the fast path");
     tb_resize_fused_kernel<T, C><<<(unsigned)blocks, 256, smem, s>>>(p);
     TB_LAUNCH_CHECK("tb_resize_fused_kernel");
     return TB_OK;
@@ -449,6 +515,7 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     p.bx = bounds_x; p.kx = taps_x; p.ksx = ks_x; p.by = bounds_y; p.ky = taps_y; p.ksy = ks_y;
     p.dst = dst; p.out_h = out_h; p.out_w = out_w;
     p.top = crop_top; p.left = crop_left; p.flip = flip; p.off_y = off_y; p.off_x = off_x; p.lut = lut;
+    p.box = nullptr;
     p.words_ok = (((uintptr_t)src & 3) == 0 && (src_row_pitch & 3) == 0 && (src_batch_stride & 3) == 0) ? 1 : 0;
 
     // Tile: TC output columns x TR output rows; the intermediate holds every input row the TR
@@ -489,4 +556,53 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
                            : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, fast, s);
     return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, fast, s)
                : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, fast, s);
+}
+
+// T.RandomResizedCrop: every sample resizes its own source box to (out_h, out_w).
+extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int W, int C,
+                                                        int64_t src_batch_stride, int64_t src_row_pitch,
+                                                        const int32_t* box, void* dst, int dst_dtype, int out_h,
+                                                        int out_w, const uint8_t* flip, const void* lut, int flags,
+                                                        tb_stream_t stream) {
+    (void)flags;
+    TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_resized_crop: bad source shape B=%d H=%d W=%d", B, H, W);
+    TB_REQUIRE(C == 1 || C == 3, "tb_resized_crop: C=%d not supported (Pillow premultiplies alpha for RGBA); use C in {1,3}", C);
+    TB_REQUIRE(out_h >= 1 && out_w >= 1, "tb_resized_crop: bad output size");
+    TB_REQUIRE(tb_dtype_size(dst_dtype) != 0, "tb_resized_crop: unknown dst_dtype %d", dst_dtype);
+    TB_REQUIRE(src_row_pitch >= (int64_t)W * C && src_batch_stride >= 0, "tb_resized_crop: bad source strides");
+    if (B == 0) return TB_OK;
+    TB_REQUIRE(src && dst && lut && box, "tb_resized_crop: NULL src/dst/lut/box");
+    TB_REQUIRE(((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_resized_crop: dst misaligned for its dtype");
+    // every box is at most the whole image: a source within 2x of the output keeps every scale <= 2
+    if ((int64_t)H > 2 * (int64_t)out_h || (int64_t)W > 2 * (int64_t)out_w)
+        return tb_fail(TB_ENOTSUP, "tb_resized_crop: source %dx%d is more than twice the output %dx%d; "
+                       "reductions beyond 2x are not built for per-sample boxes yet", H, W, out_h, out_w);
+    if (((uintptr_t)src & 3) || (src_row_pitch & 3) || (src_batch_stride & 3))
+        return tb_fail(TB_ENOTSUP, "tb_resized_crop: source base, row pitch and batch stride must be multiples of 4 bytes");
+
+    TbDevice dev;
+    int rc = tb_device(&dev);
+    if (rc) return rc;
+    RsParams p = {};
+    p.src = src; p.B = B; p.H = H; p.W = W; p.bs = src_batch_stride; p.pitch = src_row_pitch;
+    p.rs_h = out_h; p.rs_w = out_w;
+    p.dst = dst; p.out_h = out_h; p.out_w = out_w;
+    p.flip = flip; p.lut = lut; p.box = box; p.words_ok = 1;
+    const int TC = out_w < 256 ? out_w : 256;
+    const int TR = ((int64_t)B * ((out_h + 15) / 16) * ((out_w + TC - 1) / TC) >= 4 * (int64_t)dev.sm_count) ? 16 : 8;
+    int col_pitch = (2 * TR + 6 + 4 + 3) & ~3;          // up to 2 input rows per output row + the tap overhang
+    if (((col_pitch >> 2) & 1) == 0) col_pitch += 4;
+    p.TR = TR > out_h ? out_h : TR; p.TC = TC;
+    p.tiles_x = (out_w + TC - 1) / TC;
+    p.tiles_y = (out_h + p.TR - 1) / p.TR;
+    p.row_bytes = col_pitch;
+    const int64_t smem = (int64_t)C * TC * col_pitch + 16;
+    const int64_t blocks = (int64_t)p.tiles_x * p.tiles_y * B;
+    TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resized_crop: grid too large");
+    cudaStream_t s = (cudaStream_t)stream;
+    const bool f32 = dst_dtype == TB_F32;
+    if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, true, s)
+                           : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, true, s);
+    return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, true, s)
+               : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, true, s);
 }

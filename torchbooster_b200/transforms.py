@@ -43,6 +43,9 @@ class TransformSpec:
     resize        ``T.Resize`` argument: int (short side) or (h, w); Pillow antialiased bilinear.
     center_crop   ``T.CenterCrop`` size (zero fill when larger than the image).
     crop          ``T.RandomCrop`` size; offsets come from ``params`` (0 when absent).
+    random_resized_crop  ``T.RandomResizedCrop(size, scale=rrc_scale, ratio=rrc_ratio)``: every sample's own
+                  source box (from ``params``) is resized to ``size`` (Pillow bilinear); exclusive of
+                  resize / center_crop / crop / padding.
     padding       ``T.RandomCrop`` padding: int or (left/right, top/bottom).
     padding_mode  "constant" (fill 0) | "reflect" | "edge" | "symmetric".
     flip_p        ``T.RandomHorizontalFlip`` probability; ``None`` = transform not in the pipeline.
@@ -51,6 +54,9 @@ class TransformSpec:
     dtype         output dtype: float32 (the reference), bfloat16 or float16 (RNE of the fp32 value).
     """
     crop: Optional[IntPair] = None
+    random_resized_crop: Optional[IntPair] = None
+    rrc_scale: Tuple[float, float] = (0.08, 1.0)
+    rrc_ratio: Tuple[float, float] = (3.0 / 4.0, 4.0 / 3.0)
     padding: IntPair = 0
     padding_mode: str = "constant"
     flip_p: Optional[float] = None
@@ -71,6 +77,9 @@ class TransformSpec:
             raise NotImplementedError("resize combined with non-constant padding is not supported")
         if self.center_crop is not None and _pair(self.padding) != (0, 0):
             raise NotImplementedError("center_crop combined with padding is not supported")
+        if self.random_resized_crop is not None and (self.resize is not None or self.center_crop is not None or
+                                                     self.crop is not None or _pair(self.padding) != (0, 0)):
+            raise ValueError("random_resized_crop excludes resize, center_crop, crop and padding")
         N.dtype_code(self.dtype)
 
 
@@ -126,6 +135,91 @@ class CropFlipParams:
         return top, left, flip
 
 
+class ResizedCropParams:
+    """Replay of ``T.RandomResizedCrop.get_params`` (+ ``T.RandomHorizontalFlip``) draws from torch's
+    global CPU generator after ``torch.manual_seed(seed)``
+    (``torchvision/transforms/transforms.py`` RandomResizedCrop.get_params: up to ten attempts of
+    ``area * uniform(scale)``, ``exp(uniform(log ratio))``, then two ``randint``; central fallback).
+
+    ``torch.empty(1).uniform_(a, b)`` spends one 32-bit word: ``fl32(fl32((w & (2**24 - 1)) * 2**-24 * fl32(b - a)) + a)``.
+    The number of words per sample varies with the rejection loop, so words are drawn in blocks
+    and the unused tail is kept for the next batch; the per-word candidates (area, aspect) are
+    computed vectorised, the accept / reject walk is sequential.
+    """
+
+    def __init__(self, seed: int, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0)) -> None:
+        self._rs = np.random.RandomState(int(seed) & 0xFFFFFFFF)
+        self.scale = (float(scale[0]), float(scale[1]))
+        self.ratio = (float(ratio[0]), float(ratio[1]))
+        log_ratio = torch.log(torch.tensor(self.ratio))            # float32, as torchvision computes it
+        self._lr = (np.float32(log_ratio[0].item()), np.float32(log_ratio[1].item()))
+        self._words = np.zeros(0, np.uint64)
+
+    def _take(self, n: int) -> np.ndarray:
+        if self._words.shape[0] < n:
+            more = self._rs.randint(0, 2 ** 32, size=max(n - self._words.shape[0], 4096), dtype=np.uint64)
+            self._words = np.concatenate([self._words, more])
+        return self._words
+
+    @staticmethod
+    def _uniform(words: np.ndarray, a: np.float32, b: np.float32) -> np.ndarray:
+        x = (words & np.uint64(0xFFFFFF)).astype(np.float32) * np.float32(2.0 ** -24)
+        return (x * np.float32(b - a)).astype(np.float32) + np.float32(a)
+
+    def draw(self, batch: int, height: int, width: int, flip_p: Optional[float] = None):
+        """Returns numpy ``(box int32[B,4] = top, left, h, w ; flip uint8[B])``."""
+        import math
+        area = height * width
+        s0, s1 = np.float32(self.scale[0]), np.float32(self.scale[1])
+        box = np.zeros((batch, 4), np.int32)
+        flip = np.zeros(batch, np.uint8)
+        pos = 0
+        need = batch * 5 + 64
+        words = self._take(need)
+        ta_all = ar_all = None
+
+        def prepare():
+            nonlocal ta_all, ar_all
+            ta_all = area * self._uniform(words, s0, s1).astype(np.float64)
+            ar_all = torch.exp(torch.from_numpy(self._uniform(words, self._lr[0], self._lr[1]))).numpy().astype(np.float64)
+
+        prepare()
+        for b in range(batch):
+            if words.shape[0] < pos + 24:                      # room for a full rejection loop + flip
+                words = self._take(pos + 24 + 4096)
+                prepare()
+            found = False
+            for _ in range(10):
+                ta, ar = float(ta_all[pos]), float(ar_all[pos + 1])
+                pos += 2
+                w = int(round(math.sqrt(ta * ar)))
+                h = int(round(math.sqrt(ta / ar)))
+                if 0 < w <= width and 0 < h <= height:
+                    i = int(words[pos] % np.uint64(height - h + 1))
+                    j = int(words[pos + 1] % np.uint64(width - w + 1))
+                    pos += 2
+                    box[b] = (i, j, h, w)
+                    found = True
+                    break
+            if not found:                                      # central crop fallback
+                in_ratio = float(width) / float(height)
+                if in_ratio < min(self.ratio):
+                    w = width
+                    h = int(round(w / min(self.ratio)))
+                elif in_ratio > max(self.ratio):
+                    h = height
+                    w = int(round(h * max(self.ratio)))
+                else:
+                    w, h = width, height
+                box[b] = ((height - h) // 2, (width - w) // 2, h, w)
+            if flip_p is not None:
+                u = np.float32(int(words[pos]) & 0xFFFFFF) * np.float32(2.0 ** -24)
+                flip[b] = 1 if u < np.float32(flip_p) else 0
+                pos += 1
+        self._words = words[pos:]
+        return box, flip
+
+
 class BatchTransform:
     """``uint8 [B,H,W,C]`` -> ``[B,C,h,w]`` on the GPU, bit-identical to the reference pipeline.
 
@@ -143,7 +237,12 @@ class BatchTransform:
         self.device = N.cuda_device(device)
         self._luts = {}
         self._taps = {}
-        self._rng = CropFlipParams(seed) if seed is not None else None
+        if seed is None:
+            self._rng = None
+        elif spec.random_resized_crop is not None:
+            self._rng = ResizedCropParams(seed, spec.rrc_scale, spec.rrc_ratio)
+        else:
+            self._rng = CropFlipParams(seed)
         self._param_host = None
         self.flags = 0
 
@@ -197,6 +296,9 @@ class BatchTransform:
         """Static geometry for a source of ``h x w``: resized size, static offsets, output size,
         padding and whether random offsets apply."""
         sp = self.spec
+        if sp.random_resized_crop is not None:
+            out = _pair(sp.random_resized_crop)
+            return dict(rs=out, off=(0, 0), cur=out, pad=(0, 0), crop=None, out=out)
         rs_h, rs_w = (resized_output_size(h, w, sp.resize) if sp.resize is not None else (h, w))
         cur_h, cur_w, off_y, off_x = rs_h, rs_w, 0, 0
         if sp.center_crop is not None:
@@ -221,6 +323,8 @@ class BatchTransform:
         """Next ``(top, left, flip)`` from the replayed torch generator (needs ``seed=``)."""
         if self._rng is None:
             raise RuntimeError("BatchTransform was built without a seed; pass params= explicitly")
+        if self.spec.random_resized_crop is not None:
+            return self._rng.draw(batch, h, w, self.spec.flip_p)
         g = self.geometry(h, w)
         return self._rng.draw(batch, g["cur"][0], g["cur"][1], g["crop"], g["pad"], self.spec.flip_p)
 
@@ -239,13 +343,29 @@ class BatchTransform:
         self._param_host = host  # keep the pinned source alive until the copy has run
         return dev[:4 * batch].view(torch.int32), dev[4 * batch:8 * batch].view(torch.int32), dev[8 * batch:]
 
+    def _boxes_to_device(self, params, batch: int):
+        box, flip = params
+        if isinstance(box, torch.Tensor) and box.is_cuda:
+            dbox = box.to(device=self.device, dtype=torch.int32).contiguous()
+            dflip = None if flip is None else (flip if isinstance(flip, torch.Tensor) else torch.as_tensor(flip)).to(
+                device=self.device, dtype=torch.uint8).contiguous()
+            return dbox, dflip
+        host = torch.empty(17 * batch, dtype=torch.uint8, pin_memory=True)     # [box i32 x 4B][flip u8 x B]
+        hv = host.numpy()
+        hv[:16 * batch].view(np.int32)[:] = np.asarray(box, dtype=np.int32).reshape(-1)
+        hv[16 * batch:] = 0 if flip is None else np.asarray(flip, dtype=np.uint8)
+        dev = host.to(self.device, non_blocking=True)
+        self._param_host = host
+        return dev[:16 * batch].view(torch.int32).view(batch, 4), dev[16 * batch:]
+
     # -- the call --------------------------------------------------------------------------
     def __call__(self, batch: torch.Tensor, params=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         if batch.dtype != torch.uint8 or batch.dim() != 4:
             raise TypeError(f"batch must be uint8 [B,H,W,C]; got {batch.dtype} {tuple(batch.shape)}")
         sp = self.spec
         if not batch.is_cuda:
-            in_place = (self.zero_copy and batch.is_pinned() and sp.resize is None and sp.center_crop is None)
+            in_place = (self.zero_copy and batch.is_pinned() and sp.resize is None and sp.center_crop is None and
+                        sp.random_resized_crop is None)
             if not in_place:
                 batch = batch.to(self.device, non_blocking=True)
         elif batch.device != self.device:
@@ -255,10 +375,15 @@ class BatchTransform:
             batch = batch.contiguous()
         g = self.geometry(H, W)
         out_h, out_w = g["out"]
-        if params is None and self._rng is not None and (g["crop"] is not None or sp.flip_p is not None):
+        rrc = sp.random_resized_crop is not None
+        if params is None and self._rng is not None and (rrc or g["crop"] is not None or sp.flip_p is not None):
             params = self.draw_params(B, H, W)
-        top = left = flip = None
-        if params is not None:
+        top = left = flip = box = None
+        if rrc:
+            if params is None:
+                raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
+            box, flip = self._boxes_to_device(params, B)
+        elif params is not None:
             top, left, flip = self._params_to_device(params, B)
         if out is None:
             out = torch.empty((B, Cn, out_h, out_w), dtype=sp.dtype, device=self.device)
@@ -273,7 +398,11 @@ class BatchTransform:
         L = N.lib()
         with torch.cuda.device(self.device):
             stream = N.current_stream_ptr(self.device)
-            if sp.resize is None and g["off"] == (0, 0) and sp.center_crop is None:
+            if rrc:
+                rc = L.tb_resized_crop_bilinear_u8_nhwc_to_nchw(
+                    batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1), box.data_ptr(),
+                    out.data_ptr(), N.dtype_code(sp.dtype), out_h, out_w, ptr(flip), lut.data_ptr(), self.flags, stream)
+            elif sp.resize is None and g["off"] == (0, 0) and sp.center_crop is None:
                 mode = N.PAD_MODES[sp.padding_mode] if (px or py) else N.PAD_MODES["none"]
                 rc = L.tb_transform_u8_nhwc_to_nchw(
                     batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1),
