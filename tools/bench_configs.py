@@ -123,6 +123,28 @@ def two_stream_case(name, B, iters, nstreams):
                       "frac_measured": gbs / PEAK, "streams": nstreams}), flush=True)
 
 
+def rrc_case(name, B, iters, flags=0):
+    """T.RandomResizedCrop(224) + flip + normalise -> bf16 on 256x256 sources (per-sample boxes)."""
+    if CASE and CASE not in name:
+        return
+    from torchbooster_b200.transforms import ResizedCropParams
+    dev = torch.device("cuda", 0)
+    spec = TransformSpec(random_resized_crop=224, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
+    bt = BatchTransform(spec, device=dev)
+    bt.flags = flags
+    nbuf = 6
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    srcs = [torch.randint(0, 256, (B, 256, 256, 3), dtype=torch.uint8, device=dev, generator=gen) for _ in range(nbuf)]
+    box, flip = ResizedCropParams(42).draw(B, 256, 256, .5)
+    prm = (torch.from_numpy(box).to(dev), torch.from_numpy(flip).to(dev))
+    out = [torch.empty((B, 3, 224, 224), dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    ms = time_loop(lambda i: bt(srcs[i % nbuf], params=prm, out=out[i & 1]), iters)
+    alg = float((box[:, 2] * box[:, 3]).sum()) * 3 + B * 224 * 224 * 3 * 2
+    gbs = alg / (ms * 1e-3) / 1e9
+    print(json.dumps({"case": name, "B": B, "ms": ms, "images_per_s": B / (ms * 1e-3), "alg_GBps": gbs,
+                      "frac_measured": gbs / PEAK, "alg_bytes_per_image": alg / B}), flush=True)
+
+
 def calibrate():
     """Library reference points on the same buffers: a read-only reduction and a copy."""
     dev = torch.device("cuda", 0)
@@ -171,6 +193,17 @@ def main():
         c4 = dict(resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1])
         transform_case("c4_stt_b32", 32, 512, 512, c4, 1572864, 200, params=False)
         transform_case("c4_stt_b256", 256, 512, 512, c4, 1572864, 50, params=False)
+        if a.quick:
+            for per in (1, 2, 4, 8, 16):
+                transform_case(f"c4_stt_b256_per{per}", 256, 512, 512, c4, 1572864, 50, flags=per << 16, params=False)
+                transform_case(f"c4_stt_b32_per{per}", 32, 512, 512, c4, 1572864, 100, flags=per << 16, params=False)
+    if want("rrc"):
+        rrc_case("rrc_c2_b512", 512, 100)
+        rrc_case("rrc_c2_b2048", 2048, 30)
+        if a.quick:
+            for per in (1, 2, 4, 7, 14):
+                rrc_case(f"rrc_c2_b512_per{per}", 512, 100, flags=per << 16)
+                rrc_case(f"rrc_c2_b2048_per{per}", 2048, 30, flags=per << 16)
     if want("streams"):
         for ns in (1, 2, 3):
             two_stream_case(f"c2_abi_{ns}stream", 512, 400, ns)

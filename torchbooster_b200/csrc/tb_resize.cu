@@ -83,6 +83,7 @@ struct RsParams {
     int off_y, off_x;
     const void* lut;
     int TR, TC, tiles_x, tiles_y;
+    int ty_per_cta, chunks_y;   // fast kernel: row tiles per CTA and CTAs per (sample, column tile)
     int row_bytes;     // bytes per intermediate row in shared memory (multiple of 4)
     int words_ok;      // source rows may be read as aligned 32-bit words
     const int32_t* box;  // resized-crop mode: per-sample source box [B][4] = top, left, height, width
@@ -257,6 +258,8 @@ __device__ __forceinline__ void tb_pack_taps(const int* k, uint32_t* kb) {
 // One output position's taps, computed on the device exactly as tb_resize_taps does on the host
 // (and Pillow in C): float64, explicit round-to-nearest operations in Pillow's evaluation order,
 // no FMA contraction.  Valid for support <= 2 (at most 4 taps).
+constexpr int kRsCtasPerSm = 16;     // a CTA takes several row tiles only while the grid keeps this many CTAs per SM
+
 struct Tap4 {
     int xmin, n;
     int k[4];
@@ -297,16 +300,18 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
     extern __shared__ __align__(16) uint8_t inter[];  // [C][TC][col_pitch]
     __shared__ T s_lut[C * 256];
     __shared__ uint32_t s_kyb[32][3];
-    __shared__ int s_ymin[32];
+    __shared__ int s_ymin[32], s_yn[32];
     tb_grid_dependency_wait();
     for (int i = threadIdx.x; i < C * 256; i += 256) s_lut[i] = ((const T*)p.lut)[i];
 
+    // CTA <-> (sample b, column tile tx, a run of row tiles): the per-column set-up (taps, source
+    // window) is done once and reused for every row tile of the run
     int t = blockIdx.x;
     const int tx = t % p.tiles_x; t /= p.tiles_x;
-    const int ty = t % p.tiles_y;
-    const int b = t / p.tiles_y;
-    const int y0 = ty * p.TR, x0 = tx * p.TC;
-    const int nr = min(p.TR, p.out_h - y0), nc = min(p.TC, p.out_w - x0);
+    const int chunk = t % p.chunks_y;
+    const int b = t / p.chunks_y;
+    const int x0 = tx * p.TC;
+    const int nc = min(p.TC, p.out_w - x0);
     // source box of this sample (whole image unless BOX) and placement of the output in the resized image
     int box_top = 0, box_left = 0, in_h = p.H, in_w = p.W;
     if constexpr (BOX) {
@@ -319,141 +324,144 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
     const int oy = BOX ? 0 : (p.top ? p.top[b] : 0) + p.off_y;
     const int ox = BOX ? 0 : (p.left ? p.left[b] : 0) + p.off_x;
     const bool flip = p.flip ? (p.flip[b] != 0) : false;
-    const int ry0 = max(oy + y0, 0), ry1 = min(oy + y0 + nr, p.rs_h);
     const int xs0 = flip ? p.out_w - x0 - nc : x0;
     const int rx0 = max(ox + xs0, 0), rx1 = min(ox + xs0 + nc, p.rs_w);
-    const bool any = ry1 > ry0 && rx1 > rx0 && in_h > 0;
-    int iy0 = 0, nin = 0;
-    if (any) {
-        if constexpr (BOX) {
-            const Tap4 first = tb_bilinear_tap(in_h, p.rs_h, ry0), last = tb_bilinear_tap(in_h, p.rs_h, ry1 - 1);
-            iy0 = first.xmin;
-            nin = last.xmin + last.n - iy0;
-        } else {
-            iy0 = p.by[2 * ry0];
-            nin = p.by[2 * (ry1 - 1)] + p.by[2 * (ry1 - 1) + 1] - iy0;
-        }
-    }
-    const int ncols = any ? rx1 - rx0 : 0;
+    const int ncols = (rx1 > rx0 && in_h > 0) ? rx1 - rx0 : 0;      // resized columns this CTA needs (<= TC <= 256)
     const int cp = p.row_bytes;                      // column pitch (bytes), 4 * odd
     const int plane_b = p.TC * cp;                   // bytes per channel plane of the intermediate
-
-    // vertical taps of the resized rows this tile touches, packed for DP4A
-    if (any && threadIdx.x < ry1 - ry0) {
-        const int ry = ry0 + threadIdx.x;
-        Tap4 tp;
-        if constexpr (BOX) {
-            tp = tb_bilinear_tap(in_h, p.rs_h, ry);
-        } else {
-            tp.xmin = p.by[2 * ry]; tp.n = p.by[2 * ry + 1];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) tp.k[j] = (j < p.ksy && j < tp.n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
-        }
-        uint32_t kb[3];
-        tb_pack_taps(tp.k, kb);
-        s_kyb[threadIdx.x][0] = kb[0]; s_kyb[threadIdx.x][1] = kb[1]; s_kyb[threadIdx.x][2] = kb[2];
-        s_ymin[threadIdx.x] = tp.xmin - iy0;
-    }
-
-    // ---- phase 1: horizontal pass; thread <-> column, looping over the input rows
     const uint8_t* simg = p.src + (int64_t)b * p.bs;
     const int pitch_w = (int)(p.pitch >> 2);
-    for (int c0 = 0; c0 < ncols; c0 += 256) {
-        const int nch = min(256, ncols - c0);
-        const int ngrp = max(1, 256 / nch);
-        const int grp = threadIdx.x / nch;
-        if (grp < ngrp) {
-            const int cx = c0 + threadIdx.x - grp * nch;
-            const int rx = rx0 + cx;
+    constexpr int NQ = C == 3 ? 3 : 1;               // aligned words of a 4-sample window after the shift
+
+    // ---- this thread's column in the horizontal pass
+    const int ngrp1 = ncols ? max(1, 256 / ncols) : 1;
+    const int grp1 = ncols ? threadIdx.x / ncols : 0;
+    const bool active1 = ncols > 0 && grp1 < ngrp1;
+    uint32_t kbx[3] = {0, 0, 0};
+    int a1 = 0, nw1 = 0;
+    const uint32_t* wp0 = nullptr;
+    uint8_t* o0 = inter;
+    if (active1) {
+        const int cx = threadIdx.x - grp1 * ncols;
+        const int rx = rx0 + cx;
+        Tap4 tp;
+        if constexpr (BOX) {
+            tp = tb_bilinear_tap(in_w, p.rs_w, rx);
+        } else {
+            tp.xmin = p.bx[2 * rx]; tp.n = p.bx[2 * rx + 1];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) tp.k[j] = (j < p.ksx && j < tp.n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+        }
+        tb_pack_taps(tp.k, kbx);
+        const int boff = (box_left + tp.xmin) * C;
+        a1 = boff & 3;
+        nw1 = (a1 + tp.n * C + 3) >> 2;                  // words that hold this window (<= 4)
+        wp0 = reinterpret_cast<const uint32_t*>(simg + (boff - a1)) + (size_t)box_top * pitch_w;
+        o0 = inter + (size_t)cx * cp;
+    }
+    // ---- this thread's column in the vertical pass
+    const int ngrp2 = max(1, 256 / nc);
+    const int grp2 = threadIdx.x / nc;
+    const bool active2 = grp2 < ngrp2;
+    const int x = x0 + threadIdx.x - grp2 * nc;
+    const int rx2 = ox + (flip ? p.out_w - 1 - x : x);
+    const bool colin = active2 && ncols > 0 && rx2 >= rx0 && rx2 < rx1;
+    const uint32_t col = tb_smem_addr(inter) + (uint32_t)((colin ? rx2 - rx0 : 0) * cp);
+    T* dcol = (T*)p.dst + (int64_t)b * C * p.out_h * p.out_w + x;
+    const int64_t plane = (int64_t)p.out_h * p.out_w;
+
+    const int ty_end = min(p.tiles_y, (chunk + 1) * p.ty_per_cta);
+    for (int ty = chunk * p.ty_per_cta; ty < ty_end; ++ty) {
+        const int y0 = ty * p.TR;
+        const int nr = min(p.TR, p.out_h - y0);
+        const int ry0 = max(oy + y0, 0), ry1 = min(oy + y0 + nr, p.rs_h);
+        const bool any = ncols > 0 && ry1 > ry0;
+
+        // vertical taps of the resized rows this tile touches, packed for DP4A
+        if (any && threadIdx.x < ry1 - ry0) {
+            const int ry = ry0 + threadIdx.x;
             Tap4 tp;
             if constexpr (BOX) {
-                tp = tb_bilinear_tap(in_w, p.rs_w, rx);
+                tp = tb_bilinear_tap(in_h, p.rs_h, ry);
             } else {
-                tp.xmin = p.bx[2 * rx]; tp.n = p.bx[2 * rx + 1];
+                tp.xmin = p.by[2 * ry]; tp.n = p.by[2 * ry + 1];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) tp.k[j] = (j < p.ksx && j < tp.n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+                for (int j = 0; j < 4; ++j) tp.k[j] = (j < p.ksy && j < tp.n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
             }
-            const int n = tp.n;
             uint32_t kb[3];
             tb_pack_taps(tp.k, kb);
-            const int boff = (box_left + tp.xmin) * C;
-            const int a = boff & 3;
-            const int nw = (a + n * C + 3) >> 2;                 // words that hold this window (<= 4)
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(simg + (boff - a)) +
-                                 (size_t)(box_top + iy0 + grp) * pitch_w;
-            uint8_t* o = inter + (size_t)cx * cp + grp;
-            constexpr int NQ = C == 3 ? 3 : 1;               // aligned words after the shift
+            s_kyb[threadIdx.x][0] = kb[0]; s_kyb[threadIdx.x][1] = kb[1]; s_kyb[threadIdx.x][2] = kb[2];
+            s_ymin[threadIdx.x] = tp.xmin;
+            s_yn[threadIdx.x] = tp.n;
+        }
+        __syncthreads();
+        const int iy0 = any ? s_ymin[0] : 0;                                            // first input row of the tile
+        const int nin = any ? s_ymin[ry1 - ry0 - 1] + s_yn[ry1 - ry0 - 1] - iy0 : 0;    // input rows the tile touches
+
+        // ---- phase 1: horizontal pass; thread <-> column, looping over the input rows
+        if (any && active1) {
             constexpr int UR = 4;                            // rows in flight per thread
-            for (int r = grp; r < nin; r += UR * ngrp, wp += (size_t)UR * ngrp * pitch_w, o += UR * ngrp) {
+            const uint32_t* wp = wp0 + (size_t)(iy0 + grp1) * pitch_w;
+            uint8_t* o = o0 + grp1;
+            for (int r = grp1; r < nin; r += UR * ngrp1, wp += (size_t)UR * ngrp1 * pitch_w, o += UR * ngrp1) {
                 uint32_t w[UR][NQ + 1];
 #pragma unroll
                 for (int u = 0; u < UR; ++u) {
-                    const bool ok = r + u * ngrp < nin;
+                    const bool ok = r + u * ngrp1 < nin;
 #pragma unroll
-                    for (int i = 0; i <= NQ; ++i) w[u][i] = (ok && i < nw) ? __ldg(wp + (size_t)u * ngrp * pitch_w + i) : 0u;
+                    for (int i = 0; i <= NQ; ++i) w[u][i] = (ok && i < nw1) ? __ldg(wp + (size_t)u * ngrp1 * pitch_w + i) : 0u;
                 }
 #pragma unroll
                 for (int u = 0; u < UR; ++u) {
-                    if (r + u * ngrp >= nin) break;
+                    if (r + u * ngrp1 >= nin) break;
                     uint32_t q[NQ];
 #pragma unroll
-                    for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[u][i], w[u][i + 1], a * 8);
-                    uint8_t* ou = o + u * ngrp;
+                    for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[u][i], w[u][i + 1], a1 * 8);
+                    uint8_t* ou = o + u * ngrp1;
                     if (C == 3) {
                         // samples of channel c sit at bytes c, c+3, c+6, c+9 of the 12-byte window
                         const uint32_t p0 = __byte_perm(__byte_perm(q[0], q[1], 0x0630), q[2], 0x5210);
                         const uint32_t p1 = __byte_perm(__byte_perm(q[0], q[1], 0x0741), q[2], 0x6210);
                         const uint32_t p2 = __byte_perm(__byte_perm(q[0], q[1], 0x0052), q[2], 0x7410);
-                        ou[0] = (uint8_t)tb_dot4(p0, kb[0], kb[1], kb[2]);
-                        ou[plane_b] = (uint8_t)tb_dot4(p1, kb[0], kb[1], kb[2]);
-                        ou[2 * plane_b] = (uint8_t)tb_dot4(p2, kb[0], kb[1], kb[2]);
+                        ou[0] = (uint8_t)tb_dot4(p0, kbx[0], kbx[1], kbx[2]);
+                        ou[plane_b] = (uint8_t)tb_dot4(p1, kbx[0], kbx[1], kbx[2]);
+                        ou[2 * plane_b] = (uint8_t)tb_dot4(p2, kbx[0], kbx[1], kbx[2]);
                     } else {
-                        ou[0] = (uint8_t)tb_dot4(q[0], kb[0], kb[1], kb[2]);
+                        ou[0] = (uint8_t)tb_dot4(q[0], kbx[0], kbx[1], kbx[2]);
                     }
                 }
             }
         }
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // ---- phase 2: vertical pass out of shared memory; thread <-> output column, looping over rows
-    T* dimg = (T*)p.dst + (int64_t)b * C * p.out_h * p.out_w;
-    const int64_t plane = (int64_t)p.out_h * p.out_w;
-    const uint32_t inter_addr = tb_smem_addr(inter);
-    for (int c0 = 0; c0 < nc; c0 += 256) {
-        const int nch = min(256, nc - c0);
-        const int ngrp = max(1, 256 / nch);
-        const int grp = threadIdx.x / nch;
-        if (grp >= ngrp) continue;
-        const int xx = c0 + threadIdx.x - grp * nch;
-        const int x = x0 + xx;
-        const int rx = ox + (flip ? p.out_w - 1 - x : x);
-        const bool colin = rx >= 0 && rx < p.rs_w;
-        const uint32_t col = inter_addr + (uint32_t)((colin ? rx - rx0 : 0) * cp);
-        for (int yy = grp; yy < nr; yy += ngrp) {
-            const int y = y0 + yy;
-            const int ry = oy + y;
-            uint32_t e[C];
+        // ---- phase 2: vertical pass out of shared memory; thread <-> output column, looping over rows
+        if (active2) {
+            for (int yy = grp2; yy < nr; yy += ngrp2) {
+                const int y = y0 + yy;
+                const int ry = oy + y;
+                uint32_t e[C];
 #pragma unroll
-            for (int c = 0; c < C; ++c) e[c] = 0;
-            if (any && colin && ry >= 0 && ry < p.rs_h) {
-                const int rr = ry - ry0;
-                const uint32_t kb0 = s_kyb[rr][0], kb1 = s_kyb[rr][1], kb2 = s_kyb[rr][2];
-                const int ymin = s_ymin[rr];
-                const uint32_t wa = col + (uint32_t)(ymin & ~3);
-                const int sh = (ymin & 3) * 8;
+                for (int c = 0; c < C; ++c) e[c] = 0;
+                if (any && colin && ry >= ry0 && ry < ry1) {
+                    const int rr = ry - ry0;
+                    const uint32_t kb0 = s_kyb[rr][0], kb1 = s_kyb[rr][1], kb2 = s_kyb[rr][2];
+                    const int ymin = s_ymin[rr] - iy0;
+                    const uint32_t wa = col + (uint32_t)(ymin & ~3);
+                    const int sh = (ymin & 3) * 8;
 #pragma unroll
-                for (int c = 0; c < C; ++c) {
-                    uint32_t lo, hi;
-                    asm("ld.shared.u32 %0, [%1];" : "=r"(lo) : "r"(wa + c * plane_b));
-                    asm("ld.shared.u32 %0, [%1];" : "=r"(hi) : "r"(wa + c * plane_b + 4));
-                    e[c] = tb_dot4(__funnelshift_r(lo, hi, sh), kb0, kb1, kb2);
+                    for (int c = 0; c < C; ++c) {
+                        uint32_t lo, hi;
+                        asm("ld.shared.u32 %0, [%1];" : "=r"(lo) : "r"(wa + c * plane_b));
+                        asm("ld.shared.u32 %0, [%1];" : "=r"(hi) : "r"(wa + c * plane_b + 4));
+                        e[c] = tb_dot4(__funnelshift_r(lo, hi, sh), kb0, kb1, kb2);
+                    }
                 }
-            }
-            T* d = dimg + (int64_t)y * p.out_w + x;
+                T* d = dcol + (int64_t)y * p.out_w;
 #pragma unroll
-            for (int c = 0; c < C; ++c) d[c * plane] = s_lut[c * 256 + e[c]];
+                for (int c = 0; c < C; ++c) d[c * plane] = s_lut[c * 256 + e[c]];
+            }
         }
+        __syncthreads();     // the next row tile overwrites the intermediate and the tap tables
     }
 }
 
@@ -548,7 +556,18 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     p.tiles_x = (out_w + TC - 1) / TC;
     p.tiles_y = (out_h + TR - 1) / TR;
     p.row_bytes = fast ? col_pitch : rowb(TC);
-    const int64_t blocks = (int64_t)p.tiles_x * p.tiles_y * B;
+    p.ty_per_cta = 1;
+    p.chunks_y = p.tiles_y;
+    if (fast) {
+        // several row tiles per CTA amortise the per-column set-up, as long as the grid stays >= 4 CTAs per SM
+        int64_t per = (int64_t)B * p.tiles_x * p.tiles_y / (kRsCtasPerSm * (int64_t)dev.sm_count);
+        if ((flags >> 16) & 0xff) per = (flags >> 16) & 0xff;      // development knob
+        if (per < 1) per = 1;
+        if (per > p.tiles_y) per = p.tiles_y;
+        p.ty_per_cta = (int)per;
+        p.chunks_y = (p.tiles_y + p.ty_per_cta - 1) / p.ty_per_cta;
+    }
+    const int64_t blocks = fast ? (int64_t)p.tiles_x * p.chunks_y * B : (int64_t)p.tiles_x * p.tiles_y * B;
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize: grid too large");
     cudaStream_t s = (cudaStream_t)stream;
     const bool f32 = dst_dtype == TB_F32;
@@ -564,7 +583,6 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
                                                         const int32_t* box, void* dst, int dst_dtype, int out_h,
                                                         int out_w, const uint8_t* flip, const void* lut, int flags,
                                                         tb_stream_t stream) {
-    (void)flags;
     TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_resized_crop: bad source shape B=%d H=%d W=%d", B, H, W);
     TB_REQUIRE(C == 1 || C == 3, "tb_resized_crop: C=%d not supported (Pillow premultiplies alpha for RGBA); use C in {1,3}", C);
     TB_REQUIRE(out_h >= 1 && out_w >= 1, "tb_resized_crop: bad output size");
@@ -596,8 +614,16 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
     p.tiles_x = (out_w + TC - 1) / TC;
     p.tiles_y = (out_h + p.TR - 1) / p.TR;
     p.row_bytes = col_pitch;
+    {
+        int64_t per = (int64_t)B * p.tiles_x * p.tiles_y / (kRsCtasPerSm * (int64_t)dev.sm_count);
+        if ((flags >> 16) & 0xff) per = (flags >> 16) & 0xff;      // development knob
+        if (per < 1) per = 1;
+        if (per > p.tiles_y) per = p.tiles_y;
+        p.ty_per_cta = (int)per;
+        p.chunks_y = (p.tiles_y + p.ty_per_cta - 1) / p.ty_per_cta;
+    }
     const int64_t smem = (int64_t)C * TC * col_pitch + 16;
-    const int64_t blocks = (int64_t)p.tiles_x * p.tiles_y * B;
+    const int64_t blocks = (int64_t)p.tiles_x * p.chunks_y * B;
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resized_crop: grid too large");
     cudaStream_t s = (cudaStream_t)stream;
     const bool f32 = dst_dtype == TB_F32;
