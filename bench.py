@@ -377,9 +377,13 @@ def run_ours(args, wl):
 
     # ---- timed region: K steps, device-resident inputs ---------------------------------------------
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev_mid = torch.cuda.Event(enable_timing=True)
     launches0 = L.tb_launch_count()
-    sync_all()
     with ClockSampler(local) as clocks:
+        # barrier + device sync immediately before the start event: the ranks enter the region
+        # together (the sampler's NVML start-up used to skew them by milliseconds, which the final
+        # all_reduce then charged to every rank)
+        sync_all()
         ev0.record(stream)
         n_graph = K // G if graph is not None else 0
         for _ in range(n_graph):
@@ -389,12 +393,22 @@ def run_ours(args, wl):
             step(i)
             score(i)
         join()
+        ev_mid.record(stream)
         if world > 1:
             state.all_reduce()        # the one cross-GPU exchange, once per evaluation interval
         ev1.record(stream)
         sync_all()
     launches = L.tb_launch_count() - launches0 + n_graph * 2 * G     # captured launches are counted once, at capture
     ms_total = ev0.elapsed_time(ev1)
+    ck = clocks.summary()
+    per_rank = None
+    if world > 1:
+        mine = torch.tensor([ev0.elapsed_time(ev_mid), ck["sm_mhz"] or 0.0, ev_mid.elapsed_time(ev1)],
+                            dtype=torch.float64, device=dev)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"ms_per_step_before_exchange": [round(float(a[0]) / K, 5) for a in allr],
+                    "sm_mhz": [float(a[1]) for a in allr], "exchange_ms": [round(float(a[2]), 3) for a in allr]}
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -453,7 +467,7 @@ def run_ours(args, wl):
                                   if graph is not None else "eager launches"),
                        "variant": args.variant},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clocks.summary(),
+            "clocks": ck, "per_rank": per_rank,
             "counts": {"n": counts["n"], "correct_1": counts["correct_1"], f"correct_{k}": counts[f"correct_{k}"]},
         }
         print(json.dumps(line), flush=True)
