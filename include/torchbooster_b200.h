@@ -199,6 +199,17 @@ TB_API int     tb_lmdb_get(const tb_lmdb* db, const void* key, int64_t klen, con
 TB_API int     tb_lmdb_gather(const tb_lmdb* db, const int64_t* indices, int64_t n, int64_t record_bytes,
                               void* dst, int threads);
 
+/*
+ * Host helper of the T.RandomResizedCrop parameter replay: the sequential accept / reject walk of
+ * RandomResizedCrop.get_params (torchvision/transforms/transforms.py; used at
+ * examples/img_stt/online/online.py:173) over pre-drawn generator words and their per-word
+ * candidates (computed by the caller with torch's own float32 arithmetic).  All pointers HOST.
+ * Returns the number of words consumed, or TB_EINVAL when n_words is too small.
+ */
+TB_API int64_t tb_rrc_params_walk(const uint64_t* words, const double* area_cand, const double* aspect_cand,
+                                  int64_t n_words, int64_t batch, int height, int width, double ratio_min,
+                                  double ratio_max, double flip_p, int32_t* box, uint8_t* flip);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,6 +43,7 @@ SIGNATURES = {
     "tb_lmdb_entries": (_i64, [_vp]),
     "tb_lmdb_get": (_i32, [_vp, C.c_char_p, _i64, C.POINTER(_vp), C.POINTER(_i64)]),
     "tb_lmdb_gather": (_i32, [_vp, _vp, _i64, _i64, _vp, _i32]),
+    "tb_rrc_params_walk": (_i64, [_vp, _vp, _vp, _i64, _i64, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
 }
 
 

@@ -259,3 +259,62 @@ extern "C" int tb_lmdb_gather(const tb_lmdb* db, const int64_t* indices, int64_t
     }
     return TB_OK;
 }
+
+// ----------------------------------------------------------------------------------------------
+// Host helper of T.RandomResizedCrop's parameter replay: the sequential accept / reject walk of
+// RandomResizedCrop.get_params (torchvision/transforms/transforms.py) over pre-drawn generator
+// words and their per-word candidates.  The candidates (area * uniform(scale), exp(uniform(log
+// ratio))) are computed by the caller with torch so that they carry torch's exact float32
+// arithmetic; this routine only walks them: two words per attempt, two more for the offsets of an
+// accepted box, one for the flip.
+//   words, area_cand, aspect_cand : n_words entries each (candidate i belongs to word i)
+//   box   : out, int32 [batch][4] = top, left, height, width ; flip : out, uint8 [batch]
+//   returns the number of words consumed, or a negative TB_E* code (TB_EINVAL when n_words is too
+//   small: the caller draws more and calls again from the start)
+// ----------------------------------------------------------------------------------------------
+#include <math.h>
+
+extern "C" int64_t tb_rrc_params_walk(const uint64_t* words, const double* area_cand, const double* aspect_cand,
+                                      int64_t n_words, int64_t batch, int height, int width, double ratio_min,
+                                      double ratio_max, double flip_p, int32_t* box, uint8_t* flip) {
+    if (!words || !area_cand || !aspect_cand || !box || !flip || batch < 0 || height < 1 || width < 1)
+        return tb_fail(TB_EINVAL, "tb_rrc_params_walk: bad argument");
+    int64_t pos = 0;
+    for (int64_t b = 0; b < batch; ++b) {
+        if (pos + 23 > n_words) return tb_fail(TB_EINVAL, "tb_rrc_params_walk: not enough words");
+        bool found = false;
+        for (int attempt = 0; attempt < 10 && !found; ++attempt) {
+            const double ta = area_cand[pos], ar = aspect_cand[pos + 1];
+            pos += 2;
+            // Python's int(round(x)): round half to even
+            const long w = lrint(nearbyint(sqrt(ta * ar)));
+            const long h = lrint(nearbyint(sqrt(ta / ar)));
+            if (w > 0 && w <= width && h > 0 && h <= height) {
+                box[4 * b + 0] = (int32_t)(words[pos] % (uint64_t)(height - h + 1));
+                box[4 * b + 1] = (int32_t)(words[pos + 1] % (uint64_t)(width - w + 1));
+                box[4 * b + 2] = (int32_t)h;
+                box[4 * b + 3] = (int32_t)w;
+                pos += 2;
+                found = true;
+            }
+        }
+        if (!found) {   // central crop fallback
+            const double in_ratio = (double)width / (double)height;
+            long w, h;
+            if (in_ratio < ratio_min) { w = width; h = lrint(nearbyint((double)w / ratio_min)); }
+            else if (in_ratio > ratio_max) { h = height; w = lrint(nearbyint((double)h * ratio_max)); }
+            else { w = width; h = height; }
+            box[4 * b + 0] = (int32_t)((height - h) / 2);
+            box[4 * b + 1] = (int32_t)((width - w) / 2);
+            box[4 * b + 2] = (int32_t)h;
+            box[4 * b + 3] = (int32_t)w;
+        }
+        flip[b] = 0;
+        if (flip_p >= 0.0) {
+            const float u = (float)(words[pos] & 0xFFFFFFull) * 5.9604644775390625e-08f;   // 2^-24
+            flip[b] = u < (float)flip_p ? 1 : 0;
+            pos += 1;
+        }
+    }
+    return pos;
+}

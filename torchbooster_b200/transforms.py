@@ -168,55 +168,28 @@ class ResizedCropParams:
 
     def draw(self, batch: int, height: int, width: int, flip_p: Optional[float] = None):
         """Returns numpy ``(box int32[B,4] = top, left, h, w ; flip uint8[B])``."""
-        import math
         area = height * width
         s0, s1 = np.float32(self.scale[0]), np.float32(self.scale[1])
         box = np.zeros((batch, 4), np.int32)
         flip = np.zeros(batch, np.uint8)
-        pos = 0
-        need = batch * 5 + 64
-        words = self._take(need)
-        ta_all = ar_all = None
-
-        def prepare():
-            nonlocal ta_all, ar_all
+        if batch == 0:
+            return box, flip
+        need = batch * 6 + 64
+        walk = N.lib().tb_rrc_params_walk
+        while True:
+            words = np.ascontiguousarray(self._take(need))
+            # per-word candidates with torch's own float32 arithmetic (uniform_, exp)
             ta_all = area * self._uniform(words, s0, s1).astype(np.float64)
             ar_all = torch.exp(torch.from_numpy(self._uniform(words, self._lr[0], self._lr[1]))).numpy().astype(np.float64)
-
-        prepare()
-        for b in range(batch):
-            if words.shape[0] < pos + 24:                      # room for a full rejection loop + flip
-                words = self._take(pos + 24 + 4096)
-                prepare()
-            found = False
-            for _ in range(10):
-                ta, ar = float(ta_all[pos]), float(ar_all[pos + 1])
-                pos += 2
-                w = int(round(math.sqrt(ta * ar)))
-                h = int(round(math.sqrt(ta / ar)))
-                if 0 < w <= width and 0 < h <= height:
-                    i = int(words[pos] % np.uint64(height - h + 1))
-                    j = int(words[pos + 1] % np.uint64(width - w + 1))
-                    pos += 2
-                    box[b] = (i, j, h, w)
-                    found = True
-                    break
-            if not found:                                      # central crop fallback
-                in_ratio = float(width) / float(height)
-                if in_ratio < min(self.ratio):
-                    w = width
-                    h = int(round(w / min(self.ratio)))
-                elif in_ratio > max(self.ratio):
-                    h = height
-                    w = int(round(h * max(self.ratio)))
-                else:
-                    w, h = width, height
-                box[b] = ((height - h) // 2, (width - w) // 2, h, w)
-            if flip_p is not None:
-                u = np.float32(int(words[pos]) & 0xFFFFFF) * np.float32(2.0 ** -24)
-                flip[b] = 1 if u < np.float32(flip_p) else 0
-                pos += 1
-        self._words = words[pos:]
+            used = walk(words.ctypes.data, ta_all.ctypes.data, ar_all.ctypes.data, words.shape[0], batch, height, width,
+                        min(self.ratio), max(self.ratio), -1.0 if flip_p is None else float(flip_p),
+                        box.ctypes.data, flip.ctypes.data)
+            if used >= 0:
+                break
+            need = words.shape[0] * 2 + 23 * batch        # a long rejection streak: draw more and walk again
+            if need > 64 * (23 * batch + 64):
+                N.check(int(used))
+        self._words = words[used:]
         return box, flip
 
 
