@@ -61,3 +61,29 @@ def test_device_stager_keeps_order_and_content():
     for (t, d), h in zip(seen, hosts):
         assert torch.equal(d.cpu(), h)
     assert list(stager.run(iter(()))) == []
+
+
+def test_batch_loader_feeds_transform(tmp_path):
+    """LMDB -> background gather into pinned slots -> zero-copy transform, sharded by the
+    reference's sampler; slots are recycled several times."""
+    from torchbooster_b200.distributed import data_sampler
+    from torchbooster_b200.loader import BatchLoader
+    rng = np.random.default_rng(8)
+    n = 150
+    imgs = rng.integers(0, 256, (n, 48, 64, 3), dtype=np.uint8)
+    write_image_lmdb(str(tmp_path / "db"), imgs, labels=np.arange(n) % 7)
+    reader = LMDBReader(str(tmp_path / "db"))
+    order = list(data_sampler(range(n), shuffle=True, distributed=False))
+    spec = TransformSpec(crop=(32, 48), flip_p=.5, mean=CIFAR[0], std=CIFAR[1], dtype=torch.bfloat16)
+    bt = BatchTransform(spec, device="cuda", seed=11)
+    loader = BatchLoader(reader, (48, 64, 3), batch_size=16, sampler=order, transform=bt, labels=reader.read_labels(),
+                         prefetch=2, threads=4)
+    top, left, flip = PO.draw_crop_flip(11, n, 48, 64, 32, 48, 0)
+    outs, ys = [], []
+    for x, y in loader:
+        outs.append(x.clone()); ys.append(y.clone())
+    torch.cuda.synchronize()
+    want = TO.transform_batch(imgs[order], crop_top=top, crop_left=left, out_size=(32, 48), flip=flip,
+                              mean=CIFAR[0], std=CIFAR[1], dtype=torch.bfloat16)
+    assert torch.equal(torch.cat(outs).cpu().view(torch.int16), want.view(torch.int16))
+    assert torch.cat(ys).cpu().tolist() == [i % 7 for i in order]

@@ -116,3 +116,35 @@ def test_base_dataset_contract(image_db):
 
     x, y = Cifar(path)[17]
     assert np.array_equal(x, imgs[17]) and y == 7
+
+
+def test_batch_loader_host_side(image_db):
+    """Order, ragged last batch, drop_last, labels, prefetch and early exit -- without a GPU."""
+    from torchbooster_b200.loader import BatchLoader
+    path, imgs = image_db
+    reader = LMDBReader(path)
+    labels = reader.read_labels()
+    assert labels.tolist() == (np.arange(200) % 10).tolist()
+    order = np.random.default_rng(3).permutation(200)[:77]
+    loader = BatchLoader(reader, (32, 32, 3), batch_size=16, sampler=order.tolist(), labels=labels, prefetch=3, threads=2)
+    assert len(loader) == 5
+    seen = list(loader)
+    assert [x.shape[0] for x, _ in seen] == [16, 16, 16, 16, 13]
+    got = np.concatenate([x.numpy() for x, _ in seen])
+    assert np.array_equal(got, imgs[order])
+    assert torch_equal_list([y for _, y in seen], labels[order])
+    dl = BatchLoader(reader, (32, 32, 3), batch_size=16, sampler=order.tolist(), drop_last=True)
+    assert len(dl) == 4 and sum(x.shape[0] for x, y in dl) == 64
+    full = BatchLoader(reader, (32, 32, 3), batch_size=64)
+    assert len(full) == 4 and sum(x.shape[0] for x, _ in full) == 200
+    it = iter(BatchLoader(reader, (32, 32, 3), batch_size=8, prefetch=1))
+    next(it); next(it)
+    it.close()                                    # early exit must not hang on the producer
+    bad = BatchLoader(reader, (32, 32, 3), batch_size=8, sampler=[1, 2, 999])
+    with pytest.raises(KeyError):
+        list(bad)
+
+
+def torch_equal_list(tensors, want):
+    import torch
+    return np.array_equal(torch.cat(tensors).numpy(), np.asarray(want))

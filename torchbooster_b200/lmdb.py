@@ -102,6 +102,15 @@ class LMDBReader:
         N.check(rc)
         return out
 
+    def read_labels(self):
+        """Label array written by ``write_image_lmdb`` (record ``labels`` = raw little-endian int64),
+        or ``None`` when the database has none."""
+        import numpy as np
+        try:
+            return np.frombuffer(self.get(b"labels"), dtype="<i8").copy()
+        except KeyError:
+            return None
+
     def __len__(self) -> int:
         if not self.length:
             self.open()
@@ -262,8 +271,8 @@ def write_lmdb(path: str, items: Iterable[Tuple[bytes, bytes]], subdir: bool = T
 
 def write_image_lmdb(path: str, images, labels: Optional[Iterable[int]] = None) -> str:
     """Value encoding used by this package (the reference leaves it open): record
-    ``str(i)`` = raw HWC uint8 bytes of image ``i``, ``label/<i>`` = ASCII label, ``length`` = count,
-    ``shape`` = ASCII ``H,W,C``."""
+    ``str(i)`` = raw HWC uint8 bytes of image ``i``, ``label/<i>`` = ASCII label, ``labels`` = all
+    labels as raw little-endian int64, ``length`` = count, ``shape`` = ASCII ``H,W,C``."""
     import numpy as np
     images = np.asarray(images)
     if images.dtype != np.uint8 or images.ndim != 4:
@@ -272,5 +281,7 @@ def write_image_lmdb(path: str, images, labels: Optional[Iterable[int]] = None) 
     items.append((b"length", str(images.shape[0]).encode()))
     items.append((b"shape", ",".join(str(s) for s in images.shape[1:]).encode()))
     if labels is not None:
-        items += [(f"label/{i}".encode(), str(int(l)).encode()) for i, l in enumerate(labels)]
+        labels = [int(l) for l in labels]
+        items += [(f"label/{i}".encode(), str(l).encode()) for i, l in enumerate(labels)]
+        items.append((b"labels", np.asarray(labels, dtype="<i8").tobytes()))
     return write_lmdb(path, items)
