@@ -103,6 +103,20 @@ TB_API int tb_transform_u8_nhwc_to_nchw(
     const void* lut, int flags, tb_stream_t stream);
 
 /*
+ * The same transform over records at arbitrary offsets from one base: image b starts at
+ * src + offsets[b] (DEVICE int64[B], multiples of 16 for the streaming path).  Meant for an LMDB map
+ * registered with tb_lmdb_cuda_register: the kernel reads the records in place, straight out of the
+ * page cache over PCIe.  Replaces, in addition to the above, the host-side collate
+ * (torchbooster/config.py:371-379).
+ */
+TB_API int tb_transform_u8_records_to_nchw(
+    const uint8_t* src, const int64_t* offsets, int B, int H, int W, int C, int64_t src_row_pitch,
+    void* dst, int dst_dtype, int out_h, int out_w,
+    const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
+    int pad_y, int pad_x, int pad_mode,
+    const void* lut, int flags, tb_stream_t stream);
+
+/*
  * Pillow's antialiased bilinear filter taps for one axis (host computation, float64 exactly as
  * libImaging/Resample.c precompute_coeffs + normalize_coeffs_8bpc, 22-bit fixed point).
  * Replaces the coefficient set-up inside T.Resize (examples/img_stt/adain/adain.py:170 ->
@@ -198,6 +212,21 @@ TB_API int64_t tb_lmdb_entries(const tb_lmdb* db);
 TB_API int     tb_lmdb_get(const tb_lmdb* db, const void* key, int64_t klen, const void** data, int64_t* len);
 TB_API int     tb_lmdb_gather(const tb_lmdb* db, const int64_t* indices, int64_t n, int64_t record_bytes,
                               void* dst, int threads);
+
+/*
+ * In-place GPU access to an LMDB database: tb_lmdb_cuda_register page-locks the read-only map and
+ * maps it into the device address space (cudaHostRegister); *device_base is the device address of
+ * the first byte of the map.  tb_lmdb_record_offsets gives the byte offsets of fixed-size records
+ * `str(idx)` from that base (HOST arrays).  Together with tb_transform_u8_records_to_nchw the
+ * kernel reads the records straight out of the page cache over PCIe: no host-side gather.
+ * Replaces the per-sample `txn.get` + decode + collate of the reference's workers
+ * (torchbooster/lmdb.py:72-97, torchbooster/config.py:371-379).  TB_ENOTSUP when the platform cannot
+ * register the mapping (callers fall back to tb_lmdb_gather).
+ */
+TB_API int tb_lmdb_cuda_register(tb_lmdb* db, void** device_base);
+TB_API int tb_lmdb_cuda_unregister(tb_lmdb* db);
+TB_API int tb_lmdb_record_offsets(const tb_lmdb* db, const int64_t* indices, int64_t n, int64_t record_bytes,
+                                  int64_t* offsets);
 
 /*
  * Host helper of the T.RandomResizedCrop parameter replay: the sequential accept / reject walk of

@@ -87,3 +87,39 @@ def test_batch_loader_feeds_transform(tmp_path):
                               mean=CIFAR[0], std=CIFAR[1], dtype=torch.bfloat16)
     assert torch.equal(torch.cat(outs).cpu().view(torch.int16), want.view(torch.int16))
     assert torch.cat(ys).cpu().tolist() == [i % 7 for i in order]
+
+
+def test_in_place_records_equal_gathered(tmp_path):
+    """The registered-map route (kernel reads LMDB records where they lie) gives the same bits as
+    the gather route, for the streaming kernel and the gather kernel."""
+    from torchbooster_b200 import _native as N
+    from torchbooster_b200.loader import BatchLoader
+    rng = np.random.default_rng(21)
+    n = 96
+    imgs = rng.integers(0, 256, (n, 64, 80, 3), dtype=np.uint8)           # 15 KiB records: overflow pages, 16-byte aligned
+    write_image_lmdb(str(tmp_path / "db"), imgs, labels=np.arange(n) % 5)
+    reader = LMDBReader(str(tmp_path / "db"))
+    try:
+        base = reader.cuda_register()
+    except NotImplementedError as e:
+        pytest.skip(f"map registration not available here: {e}")
+    order = rng.permutation(n)
+    off = reader.record_offsets(order, 64 * 80 * 3)
+    assert (off % 16 == 0).all()
+    spec = TransformSpec(crop=(48, 64), flip_p=.5, mean=CIFAR[0], std=CIFAR[1], dtype=torch.bfloat16)
+    top, left, flip = PO.draw_crop_flip(5, n, 64, 80, 48, 64, 0)
+    want = TO.transform_batch(imgs[order], crop_top=top, crop_left=left, out_size=(48, 64), flip=flip,
+                              mean=CIFAR[0], std=CIFAR[1], dtype=torch.bfloat16)
+    for flags in (0, N.FLAG_FORCE_GENERIC):
+        bt = BatchTransform(spec, device="cuda")
+        bt.flags = flags
+        got = bt.from_records(base, off, (64, 80, 3), params=(top, left, flip))
+        assert torch.equal(got.cpu().view(torch.int16), want.view(torch.int16))
+    loader = BatchLoader(reader, (64, 80, 3), batch_size=32, sampler=order.tolist(), labels=reader.read_labels(),
+                         transform=BatchTransform(spec, device="cuda", seed=5), in_place=True)
+    outs = [(x.clone(), y.clone()) for x, y in loader]
+    torch.cuda.synchronize()
+    assert torch.equal(torch.cat([x for x, _ in outs]).cpu().view(torch.int16), want.view(torch.int16))
+    assert torch.cat([y for _, y in outs]).cpu().tolist() == [int(i) % 5 for i in order]
+    with pytest.raises(KeyError):
+        reader.record_offsets([0, n + 3], 64 * 80 * 3)

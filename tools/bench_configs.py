@@ -145,6 +145,48 @@ def rrc_case(name, B, iters, flags=0):
                       "frac_measured": gbs / PEAK, "alg_bytes_per_image": alg / B}), flush=True)
 
 
+def loader_case(name, n_images, batch, threads, prefetch=2, in_place=False):
+    """LMDB (tmpfs) -> BatchLoader background gather into pinned slots -> zero-copy C2 transform."""
+    if CASE and CASE not in name:
+        return
+    import os
+    import shutil
+    import tempfile
+    import time
+    from torchbooster_b200.lmdb import LMDBReader, write_image_lmdb
+    from torchbooster_b200.loader import BatchLoader
+    dev = torch.device("cuda", 0)
+    root = tempfile.mkdtemp(dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    try:
+        rng = np.random.default_rng(0)
+        imgs = rng.integers(0, 256, (n_images, 256, 256, 3), dtype=np.uint8)
+        t0 = time.perf_counter()
+        write_image_lmdb(os.path.join(root, "db"), imgs, labels=np.arange(n_images) % 1000)
+        t_write = time.perf_counter() - t0
+        del imgs
+        reader = LMDBReader(os.path.join(root, "db"))
+        spec = TransformSpec(crop=224, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
+        bt = BatchTransform(spec, device=dev, seed=1)
+        labels = reader.read_labels()
+        order = np.random.default_rng(1).permutation(n_images).tolist()
+        best = None
+        for _ in range(3):
+            loader = BatchLoader(reader, (256, 256, 3), batch, sampler=order, transform=bt, labels=labels, drop_last=True,
+                                 prefetch=prefetch, threads=threads, in_place=in_place)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            cnt = 0
+            for x, y in loader:
+                cnt += x.shape[0]
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        print(json.dumps({"case": name, "images": cnt, "batch": batch, "threads": threads, "images_per_s": cnt / best,
+                          "host_gather_GBps": cnt * 196608 / best / 1e9, "lmdb_write_s": t_write}), flush=True)
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
+
+
 def calibrate():
     """Library reference points on the same buffers: a read-only reduction and a copy."""
     dev = torch.device("cuda", 0)
@@ -197,6 +239,10 @@ def main():
             for per in (1, 2, 4, 8, 16):
                 transform_case(f"c4_stt_b256_per{per}", 256, 512, 512, c4, 1572864, 50, flags=per << 16, params=False)
                 transform_case(f"c4_stt_b32_per{per}", 32, 512, 512, c4, 1572864, 100, flags=per << 16, params=False)
+    if want("loader"):
+        for th in (8, 16):
+            loader_case(f"loader_c2_threads{th}", 4096, 512, th)
+        loader_case("loader_c2_in_place", 4096, 512, 8, in_place=True)
     if want("rrc"):
         rrc_case("rrc_c2_b512", 512, 100)
         rrc_case("rrc_c2_b2048", 2048, 30)

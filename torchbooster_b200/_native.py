@@ -29,6 +29,8 @@ SIGNATURES = {
     "tb_build_lut": (_i32, [_i32, _vp, _vp, _i32, _i32, _vp, _vp]),
     "tb_transform_u8_nhwc_to_nchw": (_i32, [_vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp, _i32, _i32, _i32,
                                             _vp, _vp, _vp, _i32, _i32, _i32, _vp, _i32, _vp]),
+    "tb_transform_u8_records_to_nchw": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _i64, _vp, _i32, _i32, _i32,
+                                               _vp, _vp, _vp, _i32, _i32, _i32, _vp, _i32, _vp]),
     "tb_resize_ksize": (_i32, [_i32, _i32]),
     "tb_resize_taps": (_i32, [_i32, _i32, _vp, _vp]),
     "tb_resize_bilinear_u8_nhwc_to_nchw": (_i32, [_vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _i32,
@@ -43,6 +45,9 @@ SIGNATURES = {
     "tb_lmdb_entries": (_i64, [_vp]),
     "tb_lmdb_get": (_i32, [_vp, C.c_char_p, _i64, C.POINTER(_vp), C.POINTER(_i64)]),
     "tb_lmdb_gather": (_i32, [_vp, _vp, _i64, _i64, _vp, _i32]),
+    "tb_lmdb_cuda_register": (_i32, [_vp, C.POINTER(_vp)]),
+    "tb_lmdb_cuda_unregister": (_i32, [_vp]),
+    "tb_lmdb_record_offsets": (_i32, [_vp, _vp, _i64, _i64, _vp]),
     "tb_rrc_params_walk": (_i64, [_vp, _vp, _vp, _i64, _i64, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
 }
 

@@ -169,7 +169,11 @@ extern "C" int tb_lmdb_open(const char* path, tb_lmdb** out) {
         close(fd);
         return tb_fail(TB_EINVAL, "tb_lmdb_open: %s is too small to be an LMDB data file", file.c_str());
     }
-    void* map = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+    // Private copy-on-write mapping that is never written.  PROT_WRITE is only there because
+    // cudaHostRegister (tb_lmdb_cuda_register) refuses mappings without it (measured on this
+    // platform: every PROT_READ-only file mapping fails with cudaErrorInvalidValue, even with
+    // cudaHostRegisterReadOnly).
+    void* map = mmap(nullptr, size, PROT_READ | PROT_WRITE, MAP_PRIVATE, fd, 0);
     close(fd);
     if (map == MAP_FAILED) return tb_fail(TB_EINVAL, "tb_lmdb_open: mmap(%s): %s", file.c_str(), strerror(errno));
     // readahead=False in the reference: records are read at random
@@ -198,8 +202,11 @@ extern "C" int tb_lmdb_open(const char* path, tb_lmdb** out) {
     return TB_OK;
 }
 
+extern "C" int tb_lmdb_cuda_unregister(tb_lmdb* db);
+
 extern "C" int tb_lmdb_close(tb_lmdb* db) {
     if (!db) return TB_OK;
+    tb_lmdb_cuda_unregister(db);
     munmap((void*)db->map, db->size);
     delete db;
     return TB_OK;
@@ -317,4 +324,74 @@ extern "C" int64_t tb_rrc_params_walk(const uint64_t* words, const double* area_
         }
     }
     return pos;
+}
+
+// ----------------------------------------------------------------------------------------------
+// In-place GPU access to the records: the read-only map is registered with CUDA (page-locked and
+// mapped into the device address space), after which kernels can read records straight out of the
+// page cache over PCIe -- no gather into a pinned staging buffer at all.
+// ----------------------------------------------------------------------------------------------
+struct TbLmdbCuda {
+    const tb_lmdb* db;
+    void* device_base;
+};
+static TbLmdbCuda g_registered[16];
+
+extern "C" int tb_lmdb_cuda_register(tb_lmdb* db, void** device_base) {
+    TB_REQUIRE(db && device_base, "tb_lmdb_cuda_register: NULL argument");
+    for (auto& r : g_registered)
+        if (r.db == db) { *device_base = r.device_base; return TB_OK; }
+    int ro_supported = 0, dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    (void)cudaDeviceGetAttribute(&ro_supported, cudaDevAttrHostRegisterReadOnlySupported, dev);
+    unsigned flags = cudaHostRegisterMapped | cudaHostRegisterPortable;
+    if (ro_supported) flags |= cudaHostRegisterReadOnly;
+    cudaError_t e = cudaHostRegister((void*)db->map, db->size, flags);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return tb_fail(TB_ENOTSUP, "tb_lmdb_cuda_register: cudaHostRegister(%zu bytes, flags 0x%x) failed: %s "
+                       "(read-only registration supported: %d)", db->size, flags, cudaGetErrorString(e), ro_supported);
+    }
+    void* dptr = nullptr;
+    e = cudaHostGetDevicePointer(&dptr, (void*)db->map, 0);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        cudaHostUnregister((void*)db->map);
+        return tb_cuda_fail(e, "cudaHostGetDevicePointer");
+    }
+    for (auto& r : g_registered)
+        if (!r.db) { r.db = db; r.device_base = dptr; *device_base = dptr; return TB_OK; }
+    cudaHostUnregister((void*)db->map);
+    return tb_fail(TB_ENOTSUP, "tb_lmdb_cuda_register: too many registered databases");
+}
+
+extern "C" int tb_lmdb_cuda_unregister(tb_lmdb* db) {
+    for (auto& r : g_registered)
+        if (r.db == db) {
+            cudaHostUnregister((void*)db->map);
+            r.db = nullptr;
+            r.device_base = nullptr;
+        }
+    return TB_OK;
+}
+
+// Byte offsets (from the start of the map) of n fixed-size records `str(idx)`; every record must
+// be exactly record_bytes long and start on a 16-byte boundary (true for values LMDB keeps on
+// overflow pages: page start + 16).
+extern "C" int tb_lmdb_record_offsets(const tb_lmdb* db, const int64_t* indices, int64_t n, int64_t record_bytes,
+                                      int64_t* offsets) {
+    TB_REQUIRE(db && (n == 0 || (indices && offsets)) && n >= 0, "tb_lmdb_record_offsets: bad argument");
+    char key[24];
+    for (int64_t i = 0; i < n; ++i) {
+        const int kl = snprintf(key, sizeof(key), "%lld", (long long)indices[i]);
+        const uint8_t* d = nullptr;
+        size_t len = 0;
+        const int rc = lookup(db, key, (size_t)kl, &d, &len);
+        if (rc == 1) return tb_fail(TB_ENOENT, "tb_lmdb_record_offsets: key %lld not found", (long long)indices[i]);
+        if (rc < 0) return tb_fail(TB_EINVAL, "tb_lmdb_record_offsets: corrupt page structure at key %lld", (long long)indices[i]);
+        if ((int64_t)len != record_bytes)
+            return tb_fail(TB_EINVAL, "tb_lmdb_record_offsets: record %lld is not %lld bytes", (long long)indices[i], (long long)record_bytes);
+        offsets[i] = (int64_t)(d - db->map);
+    }
+    return TB_OK;
 }

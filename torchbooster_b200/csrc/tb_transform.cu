@@ -21,6 +21,7 @@ namespace {
 
 struct XfParams {
     const uint8_t* src;
+    const int64_t* offsets;     // per-image byte offsets from src (records mode), or NULL: image b at b * bs
     int B, H, W, C;
     int64_t bs, pitch;
     void* dst;
@@ -31,6 +32,10 @@ struct XfParams {
     int pad_y, pad_x, pad_mode;
     const void* lut;
 };
+
+__device__ __forceinline__ const uint8_t* tb_image(const XfParams& p, int b) {
+    return p.src + (p.offsets ? p.offsets[b] : (int64_t)b * p.bs);
+}
 
 // Source coordinate of padded coordinate i for an axis of length n; `inside` cleared when the
 // element is fill (0).  numpy.pad semantics (torchvision/transforms/_functional_pil.py:200-223).
@@ -74,7 +79,7 @@ __global__ void __launch_bounds__(256) tb_xf_generic_kernel(XfParams p, int bloc
     bool inside = true;
     const int u = tb_fold(top + y, p.H, p.pad_mode, inside);
     const int v = tb_fold(left + xs, p.W, p.pad_mode, inside);
-    const uint8_t* __restrict__ s = p.src + (int64_t)b * p.bs + (int64_t)u * p.pitch + (int64_t)v * p.C;
+    const uint8_t* __restrict__ s = tb_image(p, b) + (int64_t)u * p.pitch + (int64_t)v * p.C;
     T* __restrict__ d = (T*)p.dst + ((int64_t)b * p.C * p.out_h + y) * p.out_w + x;
     const int64_t plane = (int64_t)p.out_h * p.out_w;
     for (int c = 0; c < p.C; ++c) {
@@ -225,7 +230,7 @@ __global__ void __launch_bounds__(768, 1) tb_xf_stream_kernel(XfParams p, XfGeom
             const bool inside = top >= 0 && top + p.out_h <= p.H && left >= 0 && left + p.out_w <= p.W;
             if (inside) {
                 const int boff = left * 3;
-                const uint8_t* gsrc = p.src + (int64_t)bp * p.bs + (int64_t)(top + y0) * p.pitch + (boff & ~15);
+                const uint8_t* gsrc = tb_image(p, bp) + (int64_t)(top + y0) * p.pitch + (boff & ~15);
                 uint8_t* sdst = my_ring_ptr + stage * g.stage_bytes;
                 if (g.contiguous) {
                     if (lane == 0) {
@@ -328,7 +333,7 @@ __global__ void __launch_bounds__(768, 1) tb_xf_stream_kernel(XfParams p, XfGeom
                 bool in = true;
                 const int uu = tb_fold(top + y0 + r, p.H, p.pad_mode, in);
                 const int vv = tb_fold(left + xs, p.W, p.pad_mode, in);
-                const uint8_t* sp = p.src + (int64_t)bc * p.bs + (int64_t)uu * p.pitch + (int64_t)vv * 3;
+                const uint8_t* sp = tb_image(p, bc) + (int64_t)uu * p.pitch + (int64_t)vv * 3;
                 T* dd = dimg + (int64_t)(y0 + r) * p.out_w + x;
                 const uint32_t e0 = in ? sp[0] : 0u, e1 = in ? sp[1] : 0u, e2 = in ? sp[2] : 0u;
                 dd[0] = X::one(tb_lds32(base0 + (e0 << 8)), 0);
@@ -440,11 +445,10 @@ double inside_fraction(int n, int pad, int out) {
 
 }  // namespace
 
-extern "C" int tb_transform_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride,
-                                            int64_t src_row_pitch, void* dst, int dst_dtype, int out_h, int out_w,
-                                            const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
-                                            int pad_y, int pad_x, int pad_mode, const void* lut, int flags,
-                                            tb_stream_t stream) {
+static int tb_transform_impl(const uint8_t* src, const int64_t* offsets, int B, int H, int W, int C,
+                             int64_t src_batch_stride, int64_t src_row_pitch, void* dst, int dst_dtype, int out_h,
+                             int out_w, const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
+                             int pad_y, int pad_x, int pad_mode, const void* lut, int flags, tb_stream_t stream) {
     TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_transform: bad source shape B=%d H=%d W=%d", B, H, W);
     TB_REQUIRE(C >= 1 && C <= 4, "tb_transform: C=%d not in [1,4]", C);
     TB_REQUIRE(out_h >= 1 && out_w >= 1, "tb_transform: bad output size %dx%d", out_h, out_w);
@@ -462,7 +466,7 @@ extern "C" int tb_transform_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, in
     TB_REQUIRE(((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_transform: dst misaligned for its dtype");
 
     XfParams p;
-    p.src = src; p.B = B; p.H = H; p.W = W; p.C = C; p.bs = src_batch_stride; p.pitch = src_row_pitch;
+    p.src = src; p.offsets = offsets; p.B = B; p.H = H; p.W = W; p.C = C; p.bs = src_batch_stride; p.pitch = src_row_pitch;
     p.dst = dst; p.out_h = out_h; p.out_w = out_w;
     p.top = crop_top; p.left = crop_left; p.flip = flip;
     p.pad_y = pad_y; p.pad_x = pad_x; p.pad_mode = pad_mode; p.lut = lut;
@@ -507,4 +511,26 @@ extern "C" int tb_transform_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, in
     }
     if (dst_dtype == TB_F32) return launch_generic<float>(p, s);
     return launch_generic<uint16_t>(p, s);
+}
+
+extern "C" int tb_transform_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride,
+                                            int64_t src_row_pitch, void* dst, int dst_dtype, int out_h, int out_w,
+                                            const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
+                                            int pad_y, int pad_x, int pad_mode, const void* lut, int flags,
+                                            tb_stream_t stream) {
+    return tb_transform_impl(src, nullptr, B, H, W, C, src_batch_stride, src_row_pitch, dst, dst_dtype, out_h, out_w,
+                             crop_top, crop_left, flip, pad_y, pad_x, pad_mode, lut, flags, stream);
+}
+
+// Same transform over records that lie at arbitrary offsets from one base (an LMDB map registered
+// with tb_lmdb_cuda_register): image b starts at src + offsets[b].  Offsets must be multiples of 16
+// for the streaming path (the caller guarantees it; LMDB overflow values are).
+extern "C" int tb_transform_u8_records_to_nchw(const uint8_t* src, const int64_t* offsets, int B, int H, int W, int C,
+                                               int64_t src_row_pitch, void* dst, int dst_dtype, int out_h, int out_w,
+                                               const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
+                                               int pad_y, int pad_x, int pad_mode, const void* lut, int flags,
+                                               tb_stream_t stream) {
+    TB_REQUIRE(offsets != nullptr || B == 0, "tb_transform_u8_records: offsets is NULL");
+    return tb_transform_impl(src, offsets, B, H, W, C, 0, src_row_pitch, dst, dst_dtype, out_h, out_w, crop_top, crop_left,
+                             flip, pad_y, pad_x, pad_mode, lut, flags, stream);
 }

@@ -102,6 +102,33 @@ class LMDBReader:
         N.check(rc)
         return out
 
+    def cuda_register(self) -> int:
+        """Page-lock the map and map it into the GPU's address space; returns the device address
+        of its first byte.  Afterwards ``BatchTransform.from_records`` / ``BatchLoader(in_place=True)``
+        let the kernel read records where they lie (no gather into a staging buffer).  The whole
+        database becomes resident, so this is for databases that fit in host memory.  Raises
+        ``NotImplementedError`` when the platform cannot register the mapping."""
+        if self.env is None or getattr(self, "_pid", None) != os.getpid():
+            self.env = None
+            self.open()
+        base = C.c_void_p()
+        N.check(N.lib().tb_lmdb_cuda_register(self.env, C.byref(base)))
+        return int(base.value)
+
+    def record_offsets(self, indices, record_bytes: int):
+        """Byte offsets (from the start of the map) of the records ``str(i)``, as numpy int64."""
+        import numpy as np
+        if self.env is None or getattr(self, "_pid", None) != os.getpid():
+            self.env = None
+            self.open()
+        idx = np.ascontiguousarray(np.asarray(indices, dtype=np.int64))
+        off = np.empty(idx.shape[0], np.int64)
+        rc = N.lib().tb_lmdb_record_offsets(self.env, idx.ctypes.data, idx.shape[0], record_bytes, off.ctypes.data)
+        if rc == N.TB_ENOENT:
+            raise KeyError(N.last_error())
+        N.check(rc)
+        return off
+
     def read_labels(self):
         """Label array written by ``write_image_lmdb`` (record ``labels`` = raw little-endian int64),
         or ``None`` when the database has none."""

@@ -36,7 +36,7 @@ class BatchLoader:
 
     def __init__(self, reader: LMDBReader, shape: Tuple[int, int, int], batch_size: int,
                  sampler: Optional[Iterable[int]] = None, transform=None, labels=None, drop_last: bool = False,
-                 prefetch: int = 2, threads: int = 8) -> None:
+                 prefetch: int = 2, threads: int = 8, in_place: bool = False) -> None:
         if batch_size < 1 or prefetch < 1:
             raise ValueError("batch_size and prefetch must be >= 1")
         self.reader, self.shape, self.batch_size = reader, tuple(int(s) for s in shape), int(batch_size)
@@ -45,6 +45,13 @@ class BatchLoader:
         self.record_bytes = int(np.prod(self.shape))
         self.labels = None if labels is None else torch.as_tensor(np.asarray(labels), dtype=torch.int64)
         self._pin = torch.cuda.is_available()
+        # in_place: the database map is registered with CUDA and the kernel reads the records where
+        # they lie -- no gather at all; the background thread only looks the record offsets up.
+        self._base = None
+        if in_place:
+            if transform is None:
+                raise ValueError("in_place needs a transform")
+            self._base = reader.cuda_register()
 
     def _indices(self) -> Sequence[int]:
         return list(self.sampler) if self.sampler is not None else list(range(len(self.reader)))
@@ -58,8 +65,9 @@ class BatchLoader:
         n = indices.shape[0]
         nb = n // self.batch_size if self.drop_last else -(-n // self.batch_size)
         nslots = self.prefetch + 2
-        slots = [torch.empty((self.batch_size, self.record_bytes), dtype=torch.uint8, pin_memory=self._pin)
-                 for _ in range(nslots)]
+        slots = [] if self._base is not None else [
+            torch.empty((self.batch_size, self.record_bytes), dtype=torch.uint8, pin_memory=self._pin)
+            for _ in range(nslots)]
         released = [None] * nslots          # CUDA event after the last kernel that read the slot
         q: "queue.Queue" = queue.Queue(maxsize=self.prefetch)
         stop = threading.Event()
@@ -70,10 +78,13 @@ class BatchLoader:
                     if stop.is_set():
                         return
                     s = k % nslots
+                    idx = indices[k * self.batch_size:(k + 1) * self.batch_size]
+                    if self._base is not None:
+                        q.put((self.reader.record_offsets(idx, self.record_bytes), idx))
+                        continue
                     ev = released[s]
                     if ev is not None:
                         ev.synchronize()
-                    idx = indices[k * self.batch_size:(k + 1) * self.batch_size]
                     out = slots[s][:idx.shape[0]]
                     self.reader.get_batch(idx, self.record_bytes, out=out, threads=self.threads)
                     q.put((s, idx))
@@ -91,6 +102,13 @@ class BatchLoader:
                 if isinstance(item, BaseException):
                     raise item
                 s, idx = item
+                if self._base is not None:
+                    x = self.transform.from_records(self._base, s, self.shape)
+                    y = None
+                    if self.labels is not None:
+                        y = self.labels[torch.from_numpy(idx)].pin_memory().to(self.transform.device, non_blocking=True)
+                    yield x, y
+                    continue
                 raw = slots[s][:idx.shape[0]].view(idx.shape[0], *self.shape)
                 y = None
                 if self.transform is None:

@@ -331,6 +331,45 @@ class BatchTransform:
         self._param_host = host
         return dev[:16 * batch].view(torch.int32).view(batch, 4), dev[16 * batch:]
 
+    def from_records(self, base_ptr: int, offsets, shape: Tuple[int, int, int], params=None,
+                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Transform records that lie at ``base_ptr + offsets[b]`` (device-visible memory, e.g. an
+        LMDB map registered with ``LMDBReader.cuda_register``): the kernel reads them in place.
+        Crop / flip pipelines only."""
+        sp = self.spec
+        if sp.resize is not None or sp.center_crop is not None or sp.random_resized_crop is not None:
+            raise NotImplementedError("from_records supports crop / flip / normalise pipelines")
+        H, W, Cn = (int(v) for v in shape)
+        off = np.ascontiguousarray(np.asarray(offsets, dtype=np.int64)) if not isinstance(offsets, torch.Tensor) else None
+        B = int(off.shape[0]) if off is not None else int(offsets.shape[0])
+        flags = self.flags
+        if off is not None:
+            if B and (int((off % 16).max()) != 0 or base_ptr % 16):
+                flags |= N.FLAG_FORCE_GENERIC          # bulk copies need 16-byte aligned records
+            host = torch.from_numpy(off)
+            host = host.pin_memory() if torch.cuda.is_available() else host
+            self._offsets_host = host
+            offsets = host.to(self.device, non_blocking=True)
+        g = self.geometry(H, W)
+        out_h, out_w = g["out"]
+        if params is None and self._rng is not None and (g["crop"] is not None or sp.flip_p is not None):
+            params = self.draw_params(B, H, W)
+        top = left = flip = None
+        if params is not None:
+            top, left, flip = self._params_to_device(params, B)
+        if out is None:
+            out = torch.empty((B, Cn, out_h, out_w), dtype=sp.dtype, device=self.device)
+        lut = self.lut(Cn)
+        px, py = g["pad"]
+        ptr = lambda t: None if t is None else t.data_ptr()
+        mode = N.PAD_MODES[sp.padding_mode] if (px or py) else N.PAD_MODES["none"]
+        with torch.cuda.device(self.device):
+            rc = N.lib().tb_transform_u8_records_to_nchw(
+                base_ptr, offsets.data_ptr(), B, H, W, Cn, W * Cn, out.data_ptr(), N.dtype_code(sp.dtype), out_h, out_w,
+                ptr(top), ptr(left), ptr(flip), py, px, mode, lut.data_ptr(), flags, N.current_stream_ptr(self.device))
+        N.check(rc)
+        return out
+
     # -- the call --------------------------------------------------------------------------
     def __call__(self, batch: torch.Tensor, params=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         if batch.dtype != torch.uint8 or batch.dim() != 4:
