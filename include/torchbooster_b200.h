@@ -159,7 +159,8 @@ TB_API int tb_resize_bilinear_u8_nhwc_to_nchw(
  * -> F.resized_crop = F.crop then F.resize).
  *   box : DEVICE int32 [B][4] = top, left, height, width of the source box (RandomResizedCrop.get_params);
  *         a box outside the image yields zeros for that sample
- * C in {1,3}.  The source may be at most twice the output size per axis (TB_ENOTSUP otherwise) and
+ * C in {1,3}.  The source may be at most four times the output size per axis (TB_ENOTSUP otherwise;
+ * four DP4A taps up to 2x, eight up to 4x) and
  * its base / row pitch / batch stride must be multiples of 4 bytes.
  */
 TB_API int tb_resized_crop_bilinear_u8_nhwc_to_nchw(

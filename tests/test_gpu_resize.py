@@ -47,6 +47,9 @@ CASES = [
     (1, 41, 57, 3, (19, 57), None, torch.float32),   # vertical pass only
     (1, 1000, 900, 3, 64, 64, torch.float32),        # large reduction: 31-tap filters
     (1, 37, 61, 3, None, 24, torch.float16),         # centre crop only
+    (2, 300, 260, 3, 96, 96, torch.float32),         # 2.7x - 3.1x reduction: eight-tap DP4A path
+    (2, 256, 512, 3, (64, 128), None, torch.bfloat16),   # exactly 4x
+    (1, 250, 128, 1, (63, 32), None, torch.float32),     # just under 4x, grayscale
 ]
 
 
@@ -139,7 +142,9 @@ def test_resized_crop_golden(golden):
 
 
 @pytest.mark.parametrize("B,H,W,C,size,dtype", [(24, 256, 256, 3, 224, torch.bfloat16), (16, 64, 96, 3, 48, torch.float32),
-                                                (8, 50, 40, 1, 32, torch.float32), (6, 300, 200, 3, (160, 100), torch.float16)])
+                                                (8, 50, 40, 1, 32, torch.float32), (6, 300, 200, 3, (160, 100), torch.float16),
+                                                (12, 375, 500, 3, 224, torch.bfloat16),      # ImageNet-sized source: up to 2.2x
+                                                (8, 120, 100, 3, 32, torch.float32)])        # up to 3.75x: eight taps
 def test_random_resized_crop_vs_torchvision(B, H, W, C, size, dtype):
     """Seeded RandomResizedCrop + flip: boxes drawn by the replayed torch generator, every box
     resized on the GPU with taps computed in-kernel; bit-exact against torchvision's own draws
@@ -170,7 +175,7 @@ def test_resized_crop_edge_boxes_and_limits():
     bad = boxes.copy(); bad[0] = [60, 60, 10, 10]
     out = bt(torch.from_numpy(batch).cuda(), params=(bad, flip))
     assert same(out[1:], want[1:]) and bool((out[0] == bt.lut(3)[:, 0].view(3, 1, 1)).all())
-    # more than 2x reduction is not built for per-sample boxes yet
-    big = torch.zeros((1, 100, 100, 3), dtype=torch.uint8, device="cuda")
-    with pytest.raises(NotImplementedError, match="twice"):
-        bt(big, params=(np.array([[0, 0, 100, 100]], np.int32), None))
+    # reductions beyond 4x are not built for per-sample boxes
+    big = torch.zeros((1, 200, 200, 3), dtype=torch.uint8, device="cuda")
+    with pytest.raises(NotImplementedError, match="four times"):
+        bt(big, params=(np.array([[0, 0, 200, 200]], np.int32), None))

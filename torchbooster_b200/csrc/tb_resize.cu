@@ -224,67 +224,81 @@ __global__ void __launch_bounds__(256) tb_resize_fused_kernel(RsParams p) {
 
 
 // ----------------------------------------------------------------------------------------------
-// fast path: both passes active, scale factor <= 2 on both axes (so every output touches at most
-// FOUR input samples: n <= ceil(2 * support) = 4), source rows readable as aligned 32-bit words.
+// fast path: both passes active, scale factor <= 4 on both axes (so every output touches at most
+// NT = 4 input samples for scales up to 2, NT = 8 up to 4: n <= ceil(2 * support)), source rows
+// readable as aligned 32-bit words.
 //
 // Four 8-bit samples times four 22-bit taps is three DP4A instructions: split each tap into its
 // three bytes, k = k0 + 2^8 k1 + 2^16 k2, then sum(p*k) = D0 + 2^8 D1 + 2^16 D2 with
-// Dm = dp4a(samples, {km of the 4 taps}); every Dm < 2^18, the chain is exact.  The rounding
-// constant 2^21 rides in as 32 << 16.  The result needs no clip: taps are >= 0 and sum to at most
-// 2^22 + 2, so (2^21 + 255 * sum) >> 22 <= 255.
+// Dm = dp4a(samples, {km of the 4 taps}); every Dm < 2^18, the chain is exact (eight taps: two
+// DP4A per byte plane).  The rounding constant 2^21 rides in as 32 << 16.  The result needs no
+// clip: taps are >= 0 and sum to at most 2^22 + NT/2, so (2^21 + 255 * sum) >> 22 <= 255.
 //
 //   phase 1  horizontal pass, thread <-> resized column for all input rows of the tile: its taps
-//            are three packed registers; a row's 4*C-byte window comes as aligned words + funnel
-//            shift, two PRMTs per channel gather the 4 samples; results go to shared memory
-//            TRANSPOSED and planar, inter[c][column][row], so that ...
-//   phase 2  ... the vertical pass finds its 4 samples (4 consecutive rows) in ONE unaligned word
-//            (two LDS + funnel shift), runs the same DP4A chain, looks the byte up and stores.
+//            are packed registers; a row's NT*C-byte window comes as aligned words + funnel
+//            shift, two PRMTs per channel and tap group gather the samples; results go to shared
+//            memory TRANSPOSED and planar, inter[c][column][row], so that ...
+//   phase 2  ... the vertical pass finds its NT samples (consecutive rows) in one unaligned word
+//            group (LDS + funnel shift), runs the same DP4A chain, looks the byte up and stores.
 // The column pitch is 4 * odd bytes: lanes (= consecutive columns) never share a bank.
 // ----------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t tb_dot4(uint32_t px, uint32_t kb0, uint32_t kb1, uint32_t kb2) {
-    uint32_t a = __dp4a(px, kb2, 32u);
-    a = __dp4a(px, kb1, a << 8);
-    a = __dp4a(px, kb0, a << 8);
+template <int G>   // G tap groups of four
+__device__ __forceinline__ uint32_t tb_dot(const uint32_t* px, const uint32_t (*kb)[3]) {
+    uint32_t a = 32u;
+#pragma unroll
+    for (int g = 0; g < G; ++g) a = __dp4a(px[g], kb[g][2], a);
+    a <<= 8;
+#pragma unroll
+    for (int g = 0; g < G; ++g) a = __dp4a(px[g], kb[g][1], a);
+    a <<= 8;
+#pragma unroll
+    for (int g = 0; g < G; ++g) a = __dp4a(px[g], kb[g][0], a);
     return a >> kPrecisionBits;
 }
-// byte m of each of (up to) four taps -> one word per m
-__device__ __forceinline__ void tb_pack_taps(const int* k, uint32_t* kb) {
+// byte m of each tap of a group of four -> one word per m
+template <int G>
+__device__ __forceinline__ void tb_pack_taps(const int* k, uint32_t (*kb)[3]) {
 #pragma unroll
-    for (int m = 0; m < 3; ++m)
-        kb[m] = ((uint32_t)(k[0] >> (8 * m)) & 0xffu) | (((uint32_t)(k[1] >> (8 * m)) & 0xffu) << 8) |
-                (((uint32_t)(k[2] >> (8 * m)) & 0xffu) << 16) | (((uint32_t)(k[3] >> (8 * m)) & 0xffu) << 24);
+    for (int g = 0; g < G; ++g)
+#pragma unroll
+        for (int m = 0; m < 3; ++m)
+            kb[g][m] = ((uint32_t)(k[4 * g] >> (8 * m)) & 0xffu) | (((uint32_t)(k[4 * g + 1] >> (8 * m)) & 0xffu) << 8) |
+                       (((uint32_t)(k[4 * g + 2] >> (8 * m)) & 0xffu) << 16) |
+                       (((uint32_t)(k[4 * g + 3] >> (8 * m)) & 0xffu) << 24);
 }
+
+constexpr int kRsCtasPerSm = 16;     // a CTA takes several row tiles only while the grid keeps this many CTAs per SM
 
 // One output position's taps, computed on the device exactly as tb_resize_taps does on the host
 // (and Pillow in C): float64, explicit round-to-nearest operations in Pillow's evaluation order,
-// no FMA contraction.  Valid for support <= 2 (at most 4 taps).
-constexpr int kRsCtasPerSm = 16;     // a CTA takes several row tiles only while the grid keeps this many CTAs per SM
-
-struct Tap4 {
+// no FMA contraction.  Valid while at most NT taps are non-zero (support <= NT / 2).
+template <int NT>
+struct TapN {
     int xmin, n;
-    int k[4];
+    int k[NT];
 };
-__device__ __forceinline__ Tap4 tb_bilinear_tap(int in_size, int out_size, int xx) {
+template <int NT>
+__device__ __forceinline__ TapN<NT> tb_bilinear_tap(int in_size, int out_size, int xx) {
     const double scale = __ddiv_rn((double)in_size, (double)out_size);
     const double fs = scale < 1.0 ? 1.0 : scale;      // filterscale; support = 1.0 * filterscale
     const double center = __dmul_rn((double)xx + 0.5, scale);
     const double ss = __ddiv_rn(1.0, fs);
-    Tap4 t;
+    TapN<NT> t;
     t.xmin = (int)__dadd_rn(__dsub_rn(center, fs), 0.5);
     if (t.xmin < 0) t.xmin = 0;
     int xmax = (int)__dadd_rn(__dadd_rn(center, fs), 0.5);
     if (xmax > in_size) xmax = in_size;
     t.n = xmax - t.xmin;
-    double w[4], ww = 0.0;
+    double w[NT], ww = 0.0;
 #pragma unroll
-    for (int x = 0; x < 4; ++x) {
+    for (int x = 0; x < NT; ++x) {
         double a = __dmul_rn(__dadd_rn(__dsub_rn((double)(x + t.xmin), center), 0.5), ss);
         if (a < 0.0) a = -a;
         w[x] = (x < t.n && a < 1.0) ? __dsub_rn(1.0, a) : 0.0;
         if (x < t.n) ww = __dadd_rn(ww, w[x]);
     }
 #pragma unroll
-    for (int x = 0; x < 4; ++x) {
+    for (int x = 0; x < NT; ++x) {
         double v = w[x];
         if (x < t.n && ww != 0.0) v = __ddiv_rn(v, ww);
         t.k[x] = x < t.n ? (int)__dadd_rn(0.5, __dmul_rn(v, 4194304.0)) : 0;
@@ -295,11 +309,12 @@ __device__ __forceinline__ Tap4 tb_bilinear_tap(int in_size, int out_size, int x
 // BOX = false: T.Resize of the whole image, taps from the host-built tables, then crop / flip.
 // BOX = true : T.RandomResizedCrop -- every sample resizes its own source box to the output size;
 //              taps are computed in the kernel (tb_bilinear_tap), no tables, no extra crop.
-template <typename T, int C, bool BOX>
+template <typename T, int C, bool BOX, int NT>
 __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
+    constexpr int G = NT / 4;
     extern __shared__ __align__(16) uint8_t inter[];  // [C][TC][col_pitch]
     __shared__ T s_lut[C * 256];
-    __shared__ uint32_t s_kyb[32][3];
+    __shared__ uint32_t s_kyb[32][G][3];
     __shared__ int s_ymin[32], s_yn[32];
     tb_grid_dependency_wait();
     for (int i = threadIdx.x; i < C * 256; i += 256) s_lut[i] = ((const T*)p.lut)[i];
@@ -316,9 +331,9 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
     int box_top = 0, box_left = 0, in_h = p.H, in_w = p.W;
     if constexpr (BOX) {
         box_top = p.box[4 * b]; box_left = p.box[4 * b + 1]; in_h = p.box[4 * b + 2]; in_w = p.box[4 * b + 3];
-        // a box the host did not vouch for (outside the image, or more than 2x the output) yields zeros
+        // a box the host did not vouch for (outside the image, or too large for NT taps) yields zeros
         if (box_top < 0 || box_left < 0 || in_h < 1 || in_w < 1 || box_top + in_h > p.H || box_left + in_w > p.W ||
-            in_h > 2 * p.rs_h || in_w > 2 * p.rs_w)
+            in_h > (NT / 2) * p.rs_h || in_w > (NT / 2) * p.rs_w)
             in_h = in_w = 0;
     }
     const int oy = BOX ? 0 : (p.top ? p.top[b] : 0) + p.off_y;
@@ -331,31 +346,33 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
     const int plane_b = p.TC * cp;                   // bytes per channel plane of the intermediate
     const uint8_t* simg = p.src + (int64_t)b * p.bs;
     const int pitch_w = (int)(p.pitch >> 2);
-    constexpr int NQ = C == 3 ? 3 : 1;               // aligned words of a 4-sample window after the shift
+    constexpr int NQ = NT * C / 4;                   // aligned words of an NT-sample window after the shift
 
     // ---- this thread's column in the horizontal pass
     const int ngrp1 = ncols ? max(1, 256 / ncols) : 1;
     const int grp1 = ncols ? threadIdx.x / ncols : 0;
     const bool active1 = ncols > 0 && grp1 < ngrp1;
-    uint32_t kbx[3] = {0, 0, 0};
+    uint32_t kbx[G][3];
+#pragma unroll
+    for (int g = 0; g < G; ++g) kbx[g][0] = kbx[g][1] = kbx[g][2] = 0;
     int a1 = 0, nw1 = 0;
     const uint32_t* wp0 = nullptr;
     uint8_t* o0 = inter;
     if (active1) {
         const int cx = threadIdx.x - grp1 * ncols;
         const int rx = rx0 + cx;
-        Tap4 tp;
+        TapN<NT> tp;
         if constexpr (BOX) {
-            tp = tb_bilinear_tap(in_w, p.rs_w, rx);
+            tp = tb_bilinear_tap<NT>(in_w, p.rs_w, rx);
         } else {
             tp.xmin = p.bx[2 * rx]; tp.n = p.bx[2 * rx + 1];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) tp.k[j] = (j < p.ksx && j < tp.n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+            for (int j = 0; j < NT; ++j) tp.k[j] = (j < p.ksx && j < tp.n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
         }
-        tb_pack_taps(tp.k, kbx);
+        tb_pack_taps<G>(tp.k, kbx);
         const int boff = (box_left + tp.xmin) * C;
         a1 = boff & 3;
-        nw1 = (a1 + tp.n * C + 3) >> 2;                  // words that hold this window (<= 4)
+        nw1 = (a1 + tp.n * C + 3) >> 2;                  // words that hold this window (<= NQ + 1)
         wp0 = reinterpret_cast<const uint32_t*>(simg + (boff - a1)) + (size_t)box_top * pitch_w;
         o0 = inter + (size_t)cx * cp;
     }
@@ -380,17 +397,15 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
         // vertical taps of the resized rows this tile touches, packed for DP4A
         if (any && threadIdx.x < ry1 - ry0) {
             const int ry = ry0 + threadIdx.x;
-            Tap4 tp;
+            TapN<NT> tp;
             if constexpr (BOX) {
-                tp = tb_bilinear_tap(in_h, p.rs_h, ry);
+                tp = tb_bilinear_tap<NT>(in_h, p.rs_h, ry);
             } else {
                 tp.xmin = p.by[2 * ry]; tp.n = p.by[2 * ry + 1];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) tp.k[j] = (j < p.ksy && j < tp.n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+                for (int j = 0; j < NT; ++j) tp.k[j] = (j < p.ksy && j < tp.n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
             }
-            uint32_t kb[3];
-            tb_pack_taps(tp.k, kb);
-            s_kyb[threadIdx.x][0] = kb[0]; s_kyb[threadIdx.x][1] = kb[1]; s_kyb[threadIdx.x][2] = kb[2];
+            tb_pack_taps<G>(tp.k, s_kyb[threadIdx.x]);
             s_ymin[threadIdx.x] = tp.xmin;
             s_yn[threadIdx.x] = tp.n;
         }
@@ -400,7 +415,7 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
 
         // ---- phase 1: horizontal pass; thread <-> column, looping over the input rows
         if (any && active1) {
-            constexpr int UR = 4;                            // rows in flight per thread
+            constexpr int UR = NT == 4 ? 4 : 2;              // rows in flight per thread
             const uint32_t* wp = wp0 + (size_t)(iy0 + grp1) * pitch_w;
             uint8_t* o = o0 + grp1;
             for (int r = grp1; r < nin; r += UR * ngrp1, wp += (size_t)UR * ngrp1 * pitch_w, o += UR * ngrp1) {
@@ -419,15 +434,19 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
                     for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[u][i], w[u][i + 1], a1 * 8);
                     uint8_t* ou = o + u * ngrp1;
                     if (C == 3) {
-                        // samples of channel c sit at bytes c, c+3, c+6, c+9 of the 12-byte window
-                        const uint32_t p0 = __byte_perm(__byte_perm(q[0], q[1], 0x0630), q[2], 0x5210);
-                        const uint32_t p1 = __byte_perm(__byte_perm(q[0], q[1], 0x0741), q[2], 0x6210);
-                        const uint32_t p2 = __byte_perm(__byte_perm(q[0], q[1], 0x0052), q[2], 0x7410);
-                        ou[0] = (uint8_t)tb_dot4(p0, kbx[0], kbx[1], kbx[2]);
-                        ou[plane_b] = (uint8_t)tb_dot4(p1, kbx[0], kbx[1], kbx[2]);
-                        ou[2 * plane_b] = (uint8_t)tb_dot4(p2, kbx[0], kbx[1], kbx[2]);
+                        // samples of channel c sit at bytes c, c+3, c+6, c+9 of each 12-byte group of four pixels
+                        uint32_t p0[G], p1[G], p2[G];
+#pragma unroll
+                        for (int g = 0; g < G; ++g) {
+                            p0[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0630), q[3 * g + 2], 0x5210);
+                            p1[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0741), q[3 * g + 2], 0x6210);
+                            p2[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0052), q[3 * g + 2], 0x7410);
+                        }
+                        ou[0] = (uint8_t)tb_dot<G>(p0, kbx);
+                        ou[plane_b] = (uint8_t)tb_dot<G>(p1, kbx);
+                        ou[2 * plane_b] = (uint8_t)tb_dot<G>(p2, kbx);
                     } else {
-                        ou[0] = (uint8_t)tb_dot4(q[0], kbx[0], kbx[1], kbx[2]);
+                        ou[0] = (uint8_t)tb_dot<G>(q, kbx);
                     }
                 }
             }
@@ -444,16 +463,20 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
                 for (int c = 0; c < C; ++c) e[c] = 0;
                 if (any && colin && ry >= ry0 && ry < ry1) {
                     const int rr = ry - ry0;
-                    const uint32_t kb0 = s_kyb[rr][0], kb1 = s_kyb[rr][1], kb2 = s_kyb[rr][2];
+                    uint32_t kb[G][3];
+#pragma unroll
+                    for (int g = 0; g < G; ++g) { kb[g][0] = s_kyb[rr][g][0]; kb[g][1] = s_kyb[rr][g][1]; kb[g][2] = s_kyb[rr][g][2]; }
                     const int ymin = s_ymin[rr] - iy0;
                     const uint32_t wa = col + (uint32_t)(ymin & ~3);
                     const int sh = (ymin & 3) * 8;
 #pragma unroll
                     for (int c = 0; c < C; ++c) {
-                        uint32_t lo, hi;
-                        asm("ld.shared.u32 %0, [%1];" : "=r"(lo) : "r"(wa + c * plane_b));
-                        asm("ld.shared.u32 %0, [%1];" : "=r"(hi) : "r"(wa + c * plane_b + 4));
-                        e[c] = tb_dot4(__funnelshift_r(lo, hi, sh), kb0, kb1, kb2);
+                        uint32_t w[G + 1], px[G];
+#pragma unroll
+                        for (int i = 0; i <= G; ++i) asm("ld.shared.u32 %0, [%1];" : "=r"(w[i]) : "r"(wa + c * plane_b + 4 * i));
+#pragma unroll
+                        for (int g = 0; g < G; ++g) px[g] = __funnelshift_r(w[g], w[g + 1], sh);
+                        e[c] = tb_dot<G>(px, kb);
                     }
                 }
                 T* d = dcol + (int64_t)y * p.out_w;
@@ -467,7 +490,7 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
 
 
 template <typename T, int C>
-int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, bool fast, cudaStream_t s) {
+int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, bool fast, int nt, cudaStream_t s) {
     static bool attr_set[64] = {};
     int dev = 0;
     TB_CUDA(cudaGetDevice(&dev));
@@ -476,9 +499,14 @@ int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, 
                                      max_smem - 8192));
         attr_set[dev] = true;
     }
-    if (fast && smem <= 40 * 1024) {
-        if (p.box) tb_resize_fast_kernel<T, C, true><<<(unsigned)blocks, 256, smem, s>>>(p);
-        else tb_resize_fast_kernel<T, C, false><<<(unsigned)blocks, 256, smem, s>>>(p);
+    if (fast && smem <= 44 * 1024) {
+        if (p.box) {
+            if (nt == 4) tb_resize_fast_kernel<T, C, true, 4><<<(unsigned)blocks, 256, smem, s>>>(p);
+            else tb_resize_fast_kernel<T, C, true, 8><<<(unsigned)blocks, 256, smem, s>>>(p);
+        } else {
+            if (nt == 4) tb_resize_fast_kernel<T, C, false, 4><<<(unsigned)blocks, 256, smem, s>>>(p);
+            else tb_resize_fast_kernel<T, C, false, 8><<<(unsigned)blocks, 256, smem, s>>>(p);
+        }
         TB_LAUNCH_CHECK("tb_resize_fast_kernel");
         return TB_OK;
     }
@@ -530,9 +558,10 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     // resized rows can touch: at most ceil(TR * scale_y) + ks_y rows.
     const double scale_y = rs_h != H ? (double)H / rs_h : 1.0;
     const int budget = 40 * 1024;
-    // scale <= 2 on both axes: at most 4 taps are ever non-zero (n <= ceil(2 * support))
-    const bool fast = !(flags & TB_FLAG_FORCE_GENERIC) && p.words_ok && rs_w != W && rs_h != H &&
-                      (int64_t)W <= 2 * (int64_t)rs_w && (int64_t)H <= 2 * (int64_t)rs_h;
+    // scale <= 4 on both axes: at most 8 taps are ever non-zero (n <= ceil(2 * support)); 4 up to scale 2
+    bool fast = !(flags & TB_FLAG_FORCE_GENERIC) && p.words_ok && rs_w != W && rs_h != H &&
+                (int64_t)W <= 4 * (int64_t)rs_w && (int64_t)H <= 4 * (int64_t)rs_h;
+    const int nt = ((int64_t)W <= 2 * (int64_t)rs_w && (int64_t)H <= 2 * (int64_t)rs_h) ? 4 : 8;
     int TC = out_w < 256 ? out_w : 256;
     // taller tiles recompute fewer halo rows; keep at least ~4 CTAs per SM in the grid
     int TR = ((int64_t)B * ((out_h + 15) / 16) * ((out_w + TC - 1) / TC) >= 4 * (int64_t)dev.sm_count) ? 16 : 8;
@@ -546,11 +575,18 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     int col_pitch = 0;
     if (fast) {
         // transposed planar intermediate [C][TC][col_pitch]: a column holds the tile's input rows plus
-        // room for the 4-sample window of the last row; pitch = 4 * odd keeps lanes on distinct banks
-        col_pitch = (rows_for(TR) + 4 + 3) & ~3;
-        if (((col_pitch >> 2) & 1) == 0) col_pitch += 4;
-        smem = (int64_t)C * TC * col_pitch + 16;   // + slack: the last 8-byte window may poke past the last column
+        // room for the NT-sample window of the last row; pitch = 4 * odd keeps lanes on distinct banks
+        auto pitch_for = [&](int tr) {
+            int cpb = (rows_for(tr) + nt + 3) & ~3;
+            if (((cpb >> 2) & 1) == 0) cpb += 4;
+            return cpb;
+        };
+        while (TR > 1 && (int64_t)C * TC * pitch_for(TR) + 16 > 44 * 1024) TR >>= 1;
+        col_pitch = pitch_for(TR);
+        smem = (int64_t)C * TC * col_pitch + 16;   // + slack: the last window may poke past the last column
+        if (smem > 44 * 1024) fast = false;
     }
+    if (!fast) smem = (int64_t)rows_for(TR) * rowb(TC);
     if (TR > out_h) TR = out_h;
     p.TR = TR; p.TC = TC;
     p.tiles_x = (out_w + TC - 1) / TC;
@@ -571,10 +607,10 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize: grid too large");
     cudaStream_t s = (cudaStream_t)stream;
     const bool f32 = dst_dtype == TB_F32;
-    if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, fast, s)
-                           : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, fast, s);
-    return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, fast, s)
-               : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, fast, s);
+    if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, fast, nt, s)
+                           : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, fast, nt, s);
+    return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, fast, nt, s)
+               : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, fast, nt, s);
 }
 
 // T.RandomResizedCrop: every sample resizes its own source box to (out_h, out_w).
@@ -591,10 +627,11 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
     if (B == 0) return TB_OK;
     TB_REQUIRE(src && dst && lut && box, "tb_resized_crop: NULL src/dst/lut/box");
     TB_REQUIRE(((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_resized_crop: dst misaligned for its dtype");
-    // every box is at most the whole image: a source within 2x of the output keeps every scale <= 2
-    if ((int64_t)H > 2 * (int64_t)out_h || (int64_t)W > 2 * (int64_t)out_w)
-        return tb_fail(TB_ENOTSUP, "tb_resized_crop: source %dx%d is more than twice the output %dx%d; "
-                       "reductions beyond 2x are not built for per-sample boxes yet", H, W, out_h, out_w);
+    // every box is at most the whole image: a source within 4x of the output keeps every scale <= 4
+    if ((int64_t)H > 4 * (int64_t)out_h || (int64_t)W > 4 * (int64_t)out_w)
+        return tb_fail(TB_ENOTSUP, "tb_resized_crop: source %dx%d is more than four times the output %dx%d; "
+                       "reductions beyond 4x are not built for per-sample boxes", H, W, out_h, out_w);
+    const int nt = ((int64_t)H <= 2 * (int64_t)out_h && (int64_t)W <= 2 * (int64_t)out_w) ? 4 : 8;
     if (((uintptr_t)src & 3) || (src_row_pitch & 3) || (src_batch_stride & 3))
         return tb_fail(TB_ENOTSUP, "tb_resized_crop: source base, row pitch and batch stride must be multiples of 4 bytes");
 
@@ -607,9 +644,15 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
     p.dst = dst; p.out_h = out_h; p.out_w = out_w;
     p.flip = flip; p.lut = lut; p.box = box; p.words_ok = 1;
     const int TC = out_w < 256 ? out_w : 256;
-    const int TR = ((int64_t)B * ((out_h + 15) / 16) * ((out_w + TC - 1) / TC) >= 4 * (int64_t)dev.sm_count) ? 16 : 8;
-    int col_pitch = (2 * TR + 6 + 4 + 3) & ~3;          // up to 2 input rows per output row + the tap overhang
-    if (((col_pitch >> 2) & 1) == 0) col_pitch += 4;
+    int TR = ((int64_t)B * ((out_h + 15) / 16) * ((out_w + TC - 1) / TC) >= 4 * (int64_t)dev.sm_count) ? 16 : 8;
+    // up to nt/2 input rows per output row + the tap overhang
+    auto pitch_for = [&](int tr) {
+        int cpb = ((nt / 2) * tr + nt + 2 + nt + 3) & ~3;
+        if (((cpb >> 2) & 1) == 0) cpb += 4;
+        return cpb;
+    };
+    while (TR > 1 && (int64_t)C * TC * pitch_for(TR) + 16 > 44 * 1024) TR >>= 1;
+    const int col_pitch = pitch_for(TR);
     p.TR = TR > out_h ? out_h : TR; p.TC = TC;
     p.tiles_x = (out_w + TC - 1) / TC;
     p.tiles_y = (out_h + p.TR - 1) / p.TR;
@@ -627,8 +670,8 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resized_crop: grid too large");
     cudaStream_t s = (cudaStream_t)stream;
     const bool f32 = dst_dtype == TB_F32;
-    if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, true, s)
-                           : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, true, s);
-    return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, true, s)
-               : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, true, s);
+    if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, true, nt, s)
+                           : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, true, nt, s);
+    return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, true, nt, s)
+               : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, true, nt, s);
 }
