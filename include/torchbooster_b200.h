@@ -49,6 +49,20 @@ extern "C" {
 #define TB_LUT_NORMALIZE_ONE_MINUS 3  /* 1 - (fl(x)/255 - mean)/std */
 
 /* flags */
+/* tb_augment operation codes: word 0 of an 8-word int32 record; words 1..6 are its parameters */
+#define TB_AUG_IDENTITY     0
+#define TB_AUG_AFFINE       1   /* words 1-6: Pillow's 16.16 fixed-point a0 a1 a2 a3 a4 a5 (half-pixel folded into a2, a5) */
+#define TB_AUG_BRIGHTNESS   2   /* word 1: float32 bits of the enhancement factor (likewise 3, 4, 5) */
+#define TB_AUG_COLOR        3
+#define TB_AUG_CONTRAST     4
+#define TB_AUG_SHARPNESS    5
+#define TB_AUG_POSTERIZE    6   /* word 1: byte mask */
+#define TB_AUG_SOLARIZE     7   /* word 1: integer threshold t: v -> v < t ? v : 255 - v */
+#define TB_AUG_AUTOCONTRAST 8
+#define TB_AUG_EQUALIZE     9
+#define TB_AUG_INVERT       10
+#define TB_AUG_MAX_OPS      8
+
 #define TB_FLAG_FORCE_GENERIC 1  /* tests: skip the streaming path, use the one-gather-per-pixel kernel */
 #define TB_FLAG_FORCE_STREAM  2  /* tests: take the streaming path even where the gather kernel is the better launch */
 #define TB_FLAG_NO_PDL        4  /* launch without programmatic stream serialization */
@@ -167,6 +181,46 @@ TB_API int tb_resized_crop_bilinear_u8_nhwc_to_nchw(
     const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride, int64_t src_row_pitch,
     const int32_t* box, void* dst, int dst_dtype, int out_h, int out_w,
     const uint8_t* flip, const void* lut, int flags, tb_stream_t stream);
+
+/*
+ * T.RandomRotation / T.RandAugment fused into the crop / flip / normalise launch: pad -> crop ->
+ * flip (exactly tb_transform_u8_nhwc_to_nchw's arguments), then the sample's own list of n_ops
+ * operations on the cropped uint8 image, then table lookup and cast.  One CTA keeps one image in
+ * shared memory for the whole chain.  Replaces, per sample on PIL images,
+ * T.RandomCrop + T.RandomHorizontalFlip + T.RandomRotation(15) + T.RandAugment() + T.ToTensor +
+ * T.Normalize (examples/img_cls/resnet/resnet.py:96-103 -> torchvision/transforms/autoaugment.py:13-90
+ * _apply_op, transforms.py RandomRotation.forward -> Pillow Image.rotate / Image.transform /
+ * ImageEnhance / ImageOps); every operation reproduces Pillow's result bit for bit.
+ *   ops : DEVICE int32 [B][n_ops][8], records of TB_AUG_* (torchbooster_b200/augment.py encodes
+ *         (name, magnitude) pairs); unknown codes are skipped.  Fill is 0, expand is False.
+ * C in {1,3}; 2 * C * out_h * out_w bytes (+ table) must fit in shared memory (TB_ENOTSUP
+ * otherwise; up to about 190 x 190 RGB).
+ */
+TB_API int tb_augment_u8_nhwc_to_nchw(
+    const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride, int64_t src_row_pitch,
+    void* dst, int dst_dtype, int out_h, int out_w,
+    const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
+    int pad_y, int pad_x, int pad_mode, const int32_t* ops, int n_ops,
+    const void* lut, int flags, tb_stream_t stream);
+
+/*
+ * Host helpers of tb_augment (no GPU work).  tb_augment_rotation_records: angles (degrees) ->
+ * records of PIL.Image.rotate (expand False, centre (w/2, h/2), nearest), float64 arithmetic in
+ * CPython's evaluation order.  tb_augment_params_walk: one pass over torch's mt19937 words making,
+ * per sample, the draws of T.RandomCrop.get_params (word % range, when crop_range_* > 0),
+ * T.RandomHorizontalFlip (flip_p >= 0), T.RandomRotation.get_params (uniform_ with rot_lo,
+ * rot_span = hi - lo in float32; fused = torch's CPU kernel contracts the multiply-add) and
+ * T.RandAugment.forward (word % n_choices, then word % 2 for signed operations;
+ * torchvision/transforms/autoaugment.py:356-362), writing records[batch][has_rotation + n_ops][8]
+ * from op_table[n_choices][2][8] (positive / negative magnitude).  Returns the number of words
+ * consumed, or a negative TB_E* code.
+ */
+TB_API int tb_augment_rotation_records(const double* angles, int64_t n, int height, int width, int32_t* records);
+TB_API int64_t tb_augment_params_walk(
+    const uint64_t* words, int64_t n_words, int64_t batch, int crop_range_h, int crop_range_w, double flip_p,
+    int has_rotation, float rot_lo, float rot_span, int fused, int height, int width,
+    int n_ops, int n_choices, const int32_t* op_table, const uint8_t* op_signed,
+    int32_t* top, int32_t* left, uint8_t* flip, int32_t* records);
 
 /*
  * One pass over a logits matrix: top-1 and top-k correct counts and confusion-matrix bins.

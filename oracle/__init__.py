@@ -24,6 +24,10 @@ versions installed in this image are therefore declared the oracle versions:
   ``tests/test_oracle.py`` and against ``tests/golden/resize_*.npz``.
 * ``params_oracle``     -- torchvision's own ``RandomCrop.get_params`` / ``torch.rand(1) < p``
   draws under ``torch.manual_seed``.
+* ``augment_oracle``    -- ``T.RandomRotation`` / ``T.RandAugment`` (``resnet.py:99-100``): torchvision's
+  own ``F.rotate`` / ``autoaugment._apply_op`` and its own draws, plus a numpy restatement of
+  Pillow's arithmetic for each operation, pinned bit-exact against torchvision live and against
+  ``tests/golden/augment_torchvision.npz`` (the reference's ``T.Compose`` run as written).
 * ``metrics_oracle``    -- restates ``torchbooster/metrics.py:27`` (accuracy) and ``:73-75``
   (RunningAverage).  Pinned: ``tests/golden/metrics_reference.npz`` was produced by importing
   the reference's ``torchbooster.metrics`` from ``/root/reference``

@@ -33,12 +33,14 @@ def transform_sample(
     crop: Optional[Sequence[int]] = None,   # (top, left, h, w) in padded coordinates
     resized_crop: Optional[Sequence[int]] = None,   # (top, left, h, w, out_h, out_w): T.RandomResizedCrop.forward
     flip: bool = False,
+    ops=None,                                       # [(name, magnitude)]: RandomRotation / RandAugment operations
     mean=None,
     std=None,
     one_minus: bool = False,
     dtype: torch.dtype = torch.float32,
 ) -> torch.Tensor:
-    """Resize -> CenterCrop -> pad -> crop -> hflip -> ToTensor -> Normalize -> (1 - X) -> cast.
+    """Resize -> CenterCrop -> pad -> crop -> hflip -> [rotation, RandAugment ops] -> ToTensor ->
+    Normalize -> (1 - X) -> cast.
 
     Each stage is the torchvision functional the matching ``T.*`` class calls:
     ``T.Resize`` (``transforms.py:354``), ``T.CenterCrop`` (``:381``), ``T.RandomCrop.forward``
@@ -60,6 +62,9 @@ def transform_sample(
         pil = F.resized_crop(pil, i, j, h, w, [oh, ow])
     if flip:
         pil = F.hflip(pil)
+    if ops:
+        from .augment_oracle import apply_ops_pil       # resnet.py:99-100: T.RandomRotation, T.RandAugment
+        pil = apply_ops_pil(pil, ops)
     t = F.to_tensor(pil)
     if mean is not None:
         t = F.normalize(t, list(mean), list(std))
@@ -69,7 +74,7 @@ def transform_sample(
 
 
 def transform_batch(batch: np.ndarray, *, crop_top=None, crop_left=None, out_size=None,
-                    flip=None, boxes=None, **kw) -> torch.Tensor:
+                    flip=None, boxes=None, ops=None, **kw) -> torch.Tensor:
     """``[B,H,W,C]`` uint8 -> ``[B,C,h,w]``; default collate = ``torch.stack``."""
     if isinstance(batch, torch.Tensor):
         batch = batch.cpu().numpy()
@@ -82,7 +87,7 @@ def transform_batch(batch: np.ndarray, *, crop_top=None, crop_left=None, out_siz
         rc = None
         if boxes is not None:
             rc = tuple(int(v) for v in boxes[b]) + (int(out_size[0]), int(out_size[1]))
-        out.append(transform_sample(batch[b], crop=crop, resized_crop=rc, flip=f, **kw))
+        out.append(transform_sample(batch[b], crop=crop, resized_crop=rc, flip=f, ops=None if ops is None else ops[b], **kw))
     return torch.stack(out)
 
 

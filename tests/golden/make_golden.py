@@ -5,6 +5,9 @@ container (needs /root/reference and torchvision/Pillow):
 
 * metrics_reference.npz  -- outputs of the REFERENCE ITSELF: ``torchbooster.metrics.accuracy`` and
   ``RunningAverage`` imported from /root/reference.
+* augment_torchvision.npz -- the reference's CIFAR training transform (resnet.py:96-103) run as the
+  very ``T.Compose`` it builds, sample after sample under ``torch.manual_seed``, plus every
+  RandAugment operation on its own through ``autoaugment._apply_op``.
 * transform_torchvision.npz, resize_pillow.npz, params_torchvision.npz -- outputs of the
   third-party code the reference's examples call (torchvision PIL backend / Pillow), which is
   where the transform arithmetic lives.
@@ -175,7 +178,45 @@ def params_torchvision():
     np.savez_compressed(HERE / "params_torchvision.npz", **out)
 
 
+def augment_torchvision():
+    from torchvision.transforms import autoaugment as AA
+    from torchvision.transforms import InterpolationMode
+    rng = np.random.default_rng(17)
+    out = {"versions": VERSIONS, "cpu_capability": np.array(str(torch.backends.cpu.get_cpu_capability()))}
+    # (a) the reference's own Compose (examples/img_cls/resnet/resnet.py:94-103), seed 42, 24 samples in order
+    batch = rng.integers(0, 256, (24, 32, 32, 3), dtype=np.uint8)
+    batch[3] = (batch[3] // 4) + 90          # low contrast
+    batch[5, :, :, 1] = 17                   # one constant band (AutoContrast / Equalize identity case)
+    normalize = T.Normalize(mean=CIFAR[0], std=CIFAR[1], inplace=True)
+    compose = T.Compose([T.RandomCrop(32, 4, padding_mode="reflect"), T.RandomHorizontalFlip(), T.RandomRotation(15),
+                         T.RandAugment(), T.ToTensor(), normalize])
+    torch.manual_seed(42)
+    res = torch.stack([compose(Image.fromarray(batch[b])) for b in range(batch.shape[0])])
+    out["cifar_input"], out["cifar_seed"], out["cifar_output"] = batch, np.array(42), res.numpy()
+    # (b) every operation alone, both signs, a few magnitudes, RGB and L
+    names, mags, idx, outs = [], [], [], []
+    imgs = [rng.integers(0, 256, (20, 28, 3), dtype=np.uint8), rng.integers(30, 200, (19, 19, 1), dtype=np.uint8)]
+    space = T.RandAugment()._augmentation_space(31, (20, 28))
+    for k, img in enumerate(imgs):
+        pil = Image.fromarray(img if img.shape[2] == 3 else img[:, :, 0])
+        for name, (table, signed) in space.items():
+            for bin_ in (3, 9, 30):
+                for sign in ((1.0, -1.0) if signed else (1.0,)):
+                    m = float(table[bin_].item()) * sign if table.ndim > 0 else 0.0
+                    r = np.asarray(AA._apply_op(pil, name, m, InterpolationMode.NEAREST, None)).reshape(img.shape)
+                    names.append(name); mags.append(m); idx.append(k); outs.append(r.ravel())
+        for angle in (-15.0, 7.25, 90.0, 180.0, 270.0, 359.5):
+            r = np.asarray(F.rotate(pil, angle)).reshape(img.shape)
+            names.append("RandomRotation"); mags.append(angle); idx.append(k); outs.append(r.ravel())
+    out["op_image0"], out["op_image1"] = imgs
+    out["op_names"], out["op_magnitudes"], out["op_image"] = np.array(names), np.array(mags, np.float64), np.array(idx)
+    out["op_offsets"] = np.cumsum([0] + [len(o) for o in outs])
+    out["op_outputs"] = np.concatenate(outs)
+    np.savez_compressed(HERE / "augment_torchvision.npz", **out)
+
+
 if __name__ == "__main__":
+    augment_torchvision()
     metrics_reference()
     transform_torchvision()
     resize_pillow()

@@ -1,0 +1,143 @@
+"""Parity of the fused RandomRotation / RandAugment kernel against torchvision (PIL backend),
+through the C ABI: every operation reproduces Pillow's bytes, so after the exact table the
+outputs must be BIT-EXACT."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import augment_oracle as AO
+from oracle import transform_oracle as TO
+from torchbooster_b200 import _native as N
+from torchbooster_b200 import _torchrng
+from torchbooster_b200 import augment as A
+from torchbooster_b200.transforms import BatchTransform, TransformSpec
+
+pytestmark = pytest.mark.gpu
+
+CIFAR = ((0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010))
+
+
+def same(a: torch.Tensor, b: torch.Tensor) -> bool:
+    a, b = a.cpu(), b.cpu()
+    if a.dtype != b.dtype or a.shape != b.shape:
+        return False
+    view = {torch.float32: torch.int32, torch.bfloat16: torch.int16, torch.float16: torch.int16}[a.dtype]
+    return torch.equal(a.contiguous().view(view), b.contiguous().view(view))
+
+
+def to_bytes(out: torch.Tensor) -> np.ndarray:
+    """ToTensor-only output [B,C,H,W] -> uint8 [B,H,W,C] (v / 255 is injective on bytes)."""
+    return (out.float().cpu() * 255.0).round().to(torch.uint8).permute(0, 2, 3, 1).numpy()
+
+
+def test_reference_cifar_compose_golden(golden):
+    """The reference's training transform (resnet.py:96-103), run as its own T.Compose under
+    torch.manual_seed(42) when the fixture was made, against ONE launch with replayed draws."""
+    g = golden("augment_torchvision.npz")
+    if (str(g["cpu_capability"]).upper() == "DEFAULT") != (not _torchrng.fused_multiply_add()):
+        pytest.skip("fixture was drawn by the other variant of torch's uniform_ kernel")
+    spec = TransformSpec(crop=32, padding=4, padding_mode="reflect", flip_p=0.5, rotation=15, rand_augment=True,
+                         mean=CIFAR[0], std=CIFAR[1])
+    bt = BatchTransform(spec, device="cuda", seed=int(g["cifar_seed"]))
+    before = N.lib().tb_launch_count()
+    out = bt(torch.from_numpy(g["cifar_input"]).cuda())
+    torch.cuda.synchronize()
+    assert N.lib().tb_launch_count() - before == 1
+    assert same(out, torch.from_numpy(g["cifar_output"]))
+
+
+def test_every_operation_alone_golden(golden):
+    g = golden("augment_torchvision.npz")
+    imgs = [g["op_image0"], g["op_image1"]]
+    off = g["op_offsets"]
+    for k, img in enumerate(imgs):
+        H, W, C = img.shape
+        rows = [i for i in range(len(g["op_names"])) if g["op_image"][i] == k]
+        ops = [[(str(g["op_names"][i]), float(g["op_magnitudes"][i]))] for i in rows]
+        batch = torch.from_numpy(np.repeat(img[None], len(rows), 0)).cuda()
+        bt = BatchTransform(TransformSpec(rand_augment=(1, 9, 31)), device="cuda")
+        out = to_bytes(bt(batch, params=(None, None, None, ops)))
+        for j, i in enumerate(rows):
+            want = g["op_outputs"][off[i]:off[i + 1]].reshape(img.shape)
+            assert np.array_equal(out[j], want), (ops[j], k)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_fuzz_chains_vs_torchvision(seed):
+    """Random sizes (odd plane sizes take the scalar store path), channels, paddings, dtypes and
+    operation lists of 0-5 operations over the whole vocabulary, with every magnitude bin."""
+    rng = np.random.default_rng(500 + seed)
+    names = list(AO.RAND_AUGMENT_OPS) + ["RandomRotation", "Invert"]
+    for trial in range(6):
+        C = 1 if rng.integers(0, 4) == 0 else 3
+        H, W = (int(v) for v in rng.integers(4, 44, 2))
+        pad = int(rng.integers(0, 4))
+        mode = ["constant", "reflect", "edge", "symmetric"][int(rng.integers(0, 4))]
+        th, tw = int(rng.integers(3, H + 2 * pad + 1)), int(rng.integers(3, W + 2 * pad + 1))
+        dtype = [torch.float32, torch.bfloat16, torch.float16][int(rng.integers(0, 3))]
+        B = int(rng.integers(1, 40))
+        batch = rng.integers(0, 256, (B, H, W, C), dtype=np.uint8)
+        if trial % 2:
+            batch = (batch // int(rng.integers(2, 6)) + int(rng.integers(0, 100))).astype(np.uint8)
+        top = rng.integers(0, H + 2 * pad - th + 1, B).astype(np.int32)
+        left = rng.integers(0, W + 2 * pad - tw + 1, B).astype(np.int32)
+        flip = rng.integers(0, 2, B).astype(np.uint8)
+        ops = []
+        for b in range(B):
+            mags = A.rand_augment_magnitudes(th, tw, int(rng.integers(0, 31)))
+            mine = []
+            for _ in range(int(rng.integers(0, 6))):
+                name = names[int(rng.integers(0, len(names)))]
+                m = float(np.float32(rng.uniform(-180, 180))) if name == "RandomRotation" else mags.get(name, 0.0)
+                if name not in ("Posterize", "Solarize", "RandomRotation") and rng.integers(0, 2):
+                    m = -m
+                mine.append((name, m))
+            ops.append(mine)
+        spec = TransformSpec(crop=(th, tw), padding=pad, padding_mode=mode, flip_p=0.5, rotation=180, rand_augment=True,
+                             mean=CIFAR[0][:C], std=CIFAR[1][:C], dtype=dtype)
+        got = BatchTransform(spec, device="cuda")(torch.from_numpy(batch).cuda(), params=(top, left, flip, ops))
+        want = TO.transform_batch(batch, crop_top=top, crop_left=left, out_size=(th, tw), flip=flip, ops=ops, padding=pad,
+                                  padding_mode=mode, mean=CIFAR[0][:C], std=CIFAR[1][:C], dtype=dtype)
+        assert same(got, want), (seed, trial, H, W, C, th, tw, pad, mode, dtype)
+
+
+def test_full_cifar_batches_replayed_vs_torchvision():
+    """BASELINE config C1's batch (256 x 32x32x3) through the whole training transform, three
+    consecutive batches from one seed; the oracle draws with torchvision's own code."""
+    rng = np.random.default_rng(9)
+    spec = TransformSpec(crop=32, padding=4, padding_mode="reflect", flip_p=0.5, rotation=15, rand_augment=True,
+                         mean=CIFAR[0], std=CIFAR[1], dtype=torch.bfloat16)
+    bt = BatchTransform(spec, device="cuda", seed=1234)
+    top, left, flip, ops = AO.draw_augment(1234, 3 * 256, 32, 32, 32, 32, 4, 0.5, 15)
+    for step in range(3):
+        batch = rng.integers(0, 256, (256, 32, 32, 3), dtype=np.uint8)
+        got = bt(torch.from_numpy(batch).cuda())
+        sl = slice(step * 256, (step + 1) * 256)
+        want = TO.transform_batch(batch, crop_top=top[sl], crop_left=left[sl], out_size=(32, 32), flip=flip[sl], ops=ops[sl],
+                                  padding=4, padding_mode="reflect", mean=CIFAR[0], std=CIFAR[1], dtype=torch.bfloat16)
+        assert same(got, want), step
+
+
+def test_larger_images_and_limits():
+    rng = np.random.default_rng(2)
+    batch = rng.integers(0, 256, (3, 150, 170, 3), dtype=np.uint8)          # 2 x 76.5 KB of shared memory
+    ops = [[("Rotate", -30.0), ("Sharpness", 0.81), ("Equalize", 0.0)], [("ShearX", 0.3), ("Contrast", -0.9), ("AutoContrast", 0.0)],
+           [("TranslateY", -50.0), ("Color", 0.9), ("Solarize", 10.0)]]
+    spec = TransformSpec(rand_augment=True, mean=CIFAR[0], std=CIFAR[1])
+    got = BatchTransform(spec, device="cuda")(torch.from_numpy(batch).cuda(), params=(None, None, None, ops))
+    assert same(got, TO.transform_batch(batch, ops=ops, mean=CIFAR[0], std=CIFAR[1]))
+    with pytest.raises(NotImplementedError, match="shared memory"):
+        BatchTransform(spec, device="cuda")(torch.zeros((1, 224, 224, 3), dtype=torch.uint8, device="cuda"),
+                                            params=(None, None, None, [[("Invert", 0.0)]]))
+    with pytest.raises(ValueError, match="not in"):
+        BatchTransform(spec, device="cuda")(torch.zeros((1, 8, 8, 4), dtype=torch.uint8, device="cuda"),
+                                            params=(None, None, None, [[("Invert", 0.0)]]))
+    with pytest.raises(ValueError, match="seed"):
+        BatchTransform(spec, device="cuda")(torch.zeros((1, 8, 8, 3), dtype=torch.uint8, device="cuda"))
+    with pytest.raises(NotImplementedError):
+        TransformSpec(resize=64, rand_augment=True)
+    # an empty batch and an empty operation list are fine
+    empty = BatchTransform(spec, device="cuda")(torch.zeros((0, 8, 8, 3), dtype=torch.uint8, device="cuda"), params=(None, None, None, []))
+    assert tuple(empty.shape) == (0, 3, 8, 8)
+    plain = BatchTransform(spec, device="cuda")(torch.from_numpy(batch[:1]).cuda(), params=(None, None, None, [[]]))
+    assert same(plain, TO.transform_batch(batch[:1], mean=CIFAR[0], std=CIFAR[1]))

@@ -145,6 +145,37 @@ def rrc_case(name, B, iters, flags=0):
                       "frac_measured": gbs / PEAK, "alg_bytes_per_image": alg / B}), flush=True)
 
 
+def augment_case(name, B, iters, host_params=False):
+    """The reference's CIFAR training transform (resnet.py:96-103): RandomCrop(32, 4, reflect), flip,
+    RandomRotation(15), RandAugment(), normalise -> fp32; records pre-encoded on the device
+    (kernel time) or drawn + encoded + uploaded every step (host_params)."""
+    if CASE and CASE not in name:
+        return
+    import time
+    from torchbooster_b200 import augment as A
+    dev = torch.device("cuda", 0)
+    spec = TransformSpec(crop=32, padding=4, padding_mode="reflect", flip_p=.5, rotation=15, rand_augment=True,
+                         mean=CIFAR[0], std=CIFAR[1])
+    bt = BatchTransform(spec, device=dev, seed=42)
+    nbuf = 24
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    srcs = [torch.randint(0, 256, (B, 32, 32, 3), dtype=torch.uint8, device=dev, generator=gen) for _ in range(nbuf)]
+    t, l, f, rec = bt.draw_params(B, 32, 32)
+    prm = tuple(torch.from_numpy(a).to(dev) for a in (t, l, f, rec))
+    out = [torch.empty((B, 3, 32, 32), dtype=torch.float32, device=dev) for _ in range(2)]
+    if host_params:
+        ms = time_loop(lambda i: bt(srcs[i % nbuf], out=out[i & 1]), iters)
+        t0 = time.perf_counter()
+        for _ in range(20):
+            bt.draw_params(B, 32, 32)
+        host_ms = (time.perf_counter() - t0) / 20 * 1e3
+    else:
+        ms, host_ms = time_loop(lambda i: bt(srcs[i % nbuf], params=prm, out=out[i & 1]), iters), None
+    gbs = 15360 * B / (ms * 1e-3) / 1e9
+    print(json.dumps({"case": name, "B": B, "ms": ms, "images_per_s": B / (ms * 1e-3), "alg_GBps": gbs,
+                      "frac_measured": gbs / PEAK, "host_draw_encode_ms": host_ms}), flush=True)
+
+
 def loader_case(name, n_images, batch, threads, prefetch=2, in_place=False):
     """LMDB (tmpfs) -> BatchLoader background gather into pinned slots -> zero-copy C2 transform."""
     if CASE and CASE not in name:
@@ -250,6 +281,11 @@ def main():
             for per in (1, 2, 4, 7, 14):
                 rrc_case(f"rrc_c2_b512_per{per}", 512, 100, flags=per << 16)
                 rrc_case(f"rrc_c2_b2048_per{per}", 2048, 30, flags=per << 16)
+    if want("aug"):
+        for bsz in (256, 2048, 16384):
+            augment_case(f"aug_cifar_b{bsz}", bsz, 200 if bsz < 10000 else 50)
+        augment_case("aug_cifar_b256_host_params", 256, 100, host_params=True)
+        augment_case("aug_cifar_b2048_host_params", 2048, 30, host_params=True)
     if want("streams"):
         for ns in (1, 2, 3):
             two_stream_case(f"c2_abi_{ns}stream", 512, 400, ns)

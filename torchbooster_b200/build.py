@@ -16,7 +16,7 @@ CSRC = ROOT / "csrc"
 LIB_DIR = ROOT / "lib"
 LIB_PATH = LIB_DIR / "libtorchbooster_b200.so"
 
-SOURCES = ["tb_abi.cu", "tb_lut.cu", "tb_transform.cu", "tb_resize.cu", "tb_metrics.cu", "tb_lmdb.cpp"]
+SOURCES = ["tb_abi.cu", "tb_lut.cu", "tb_transform.cu", "tb_resize.cu", "tb_augment.cu", "tb_metrics.cu", "tb_lmdb.cpp", "tb_augment_host.cpp"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -26,6 +26,8 @@ NVCC_FLAGS = [
 ]
 # translation units whose float arithmetic must not be contracted into FMAs
 NO_FMAD = {"tb_lut.cu"}
+# host translation units that restate CPython float expressions: no contraction on the host either
+NO_CONTRACT = {"tb_augment_host.cpp"}
 
 
 def _nvcc() -> str:
@@ -59,6 +61,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         cmd = [nvcc, *NVCC_FLAGS, "-c", str(path), "-o", str(obj)]
         if src in NO_FMAD:
             cmd.insert(1, "-fmad=false")
+        if src in NO_CONTRACT:
+            cmd[1:1] = ["-Xcompiler", "-ffp-contract=off"]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd), file=sys.stderr)

@@ -1,0 +1,323 @@
+// Image-resident augmentation chain (sm_100a): pad -> crop -> flip -> [per-sample operation list]
+// -> table lookup -> cast, uint8 NHWC -> NCHW, ONE launch per batch.
+//
+// Replaces the middle of the reference's CIFAR pipeline
+// (examples/img_cls/resnet/resnet.py:96-103: RandomCrop, RandomHorizontalFlip, RandomRotation(15),
+// RandAugment(), ToTensor, Normalize), which torchvision runs per sample on PIL images: every
+// stage there is a full pass over the image through Pillow's C code plus Python object churn.
+// Here one CTA owns one image.  The cropped / flipped image is gathered from global memory ONCE
+// into shared memory (planar, the layout of the output), every operation of that sample's list
+// runs out of shared memory (two buffers, ping-pong for the operations that move pixels), and
+// the result leaves through the per-channel table as coalesced planar stores.  Global traffic is
+// the algorithmic minimum: source bytes in, output elements out.
+//
+// The arithmetic of each operation is Pillow 12's, bit for bit (oracle/augment_oracle.py):
+//   AFFINE        nearest neighbour in 16.16 fixed point (Geometry.c affine_fixed): rotations,
+//                 shears, integer translations; outside = 0
+//   BRIGHTNESS / COLOR / CONTRAST / SHARPNESS
+//                 ImagingBlend(degenerate, image, alpha) = deg + alpha * (image - deg) in float32
+//                 (two roundings, no FMA), truncated, clipped; degenerate = black / grey value
+//                 (19595 R + 38470 G + 7471 B + 0x8000) >> 16 / grey mean / 3x3 SMOOTH
+//   POSTERIZE, SOLARIZE, INVERT   byte maps
+//   AUTOCONTRAST, EQUALIZE        per-band histogram -> table (ImageOps), float64 where Python is
+#include "tb_common.cuh"
+
+namespace {
+
+constexpr int kAugThreads = 256;      // == histogram bins: thread t owns bin t
+
+struct AugParams {
+    const uint8_t* src;
+    int B, H, W, C;
+    int64_t bs, pitch;
+    void* dst;
+    int out_h, out_w;
+    const int32_t* top;
+    const int32_t* left;
+    const uint8_t* flip;
+    int pad_y, pad_x, pad_mode;
+    const int32_t* ops;
+    int n_ops;
+    const void* lut;
+    int plane;          // out_h * out_w
+    int buf_bytes;      // C * plane rounded up to 16
+};
+
+__device__ __forceinline__ int aug_fold(int i, int n, int mode, bool& inside) {
+    if ((unsigned)i < (unsigned)n) return i;
+    if (mode == TB_PAD_REFLECT)
+        i = i < 0 ? -i : 2 * (n - 1) - i;
+    else if (mode == TB_PAD_SYMMETRIC)
+        i = i < 0 ? -i - 1 : 2 * n - 1 - i;
+    else if (mode == TB_PAD_EDGE)
+        i = i < 0 ? 0 : n - 1;
+    else
+        i = -1;
+    if ((unsigned)i >= (unsigned)n) {
+        inside = false;
+        return 0;
+    }
+    return i;
+}
+
+// ImagingBlend: float32 multiply, float32 add (separately rounded), truncation; the clip is a
+// no-op for alpha in [0, 1], where Pillow does not clip.
+__device__ __forceinline__ uint8_t aug_blend(int deg, int v, float alpha) {
+    const float t = __fadd_rn((float)deg, __fmul_rn(alpha, (float)(v - deg)));
+    return t <= 0.0f ? 0 : (t >= 255.0f ? 255 : (uint8_t)(int)t);
+}
+
+__device__ __forceinline__ int aug_grey(int r, int g, int b) { return (r * 19595 + g * 38470 + b * 7471 + 0x8000) >> 16; }
+
+template <typename T>
+__global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ int s_hist[3 * 256];
+    __shared__ uint8_t s_tab[3 * 256];
+    __shared__ int s_lo[3], s_hi[3], s_sum, s_warp[kAugThreads / 32];
+
+    uint8_t* cur = smem;
+    uint8_t* alt = smem + p.buf_bytes;
+    T* s_lut = (T*)(smem + 2 * p.buf_bytes);
+
+    tb_grid_dependency_wait();
+    const int tid = threadIdx.x;
+    const int b = blockIdx.x;
+    const int C = p.C, plane = p.plane, W = p.out_w, H = p.out_h;
+    const int total = C * plane;
+
+    {
+        const T* __restrict__ glut = (const T*)p.lut;
+        for (int i = tid; i < C * 256; i += kAugThreads) s_lut[i] = glut[i];
+    }
+    // ---- gather: pad / crop / flip, interleaved source -> planar shared --------------------
+    {
+        const int top = (p.top ? p.top[b] : 0) - p.pad_y;
+        const int left = (p.left ? p.left[b] : 0) - p.pad_x;
+        const bool flip = p.flip ? (p.flip[b] != 0) : false;
+        const uint8_t* __restrict__ img = p.src + (int64_t)b * p.bs;
+        for (int q = tid; q < plane; q += kAugThreads) {
+            const int y = q / W, x = q - y * W;
+            const int xs = flip ? W - 1 - x : x;
+            bool inside = true;
+            const int u = aug_fold(top + y, p.H, p.pad_mode, inside);
+            const int v = aug_fold(left + xs, p.W, p.pad_mode, inside);
+            const uint8_t* __restrict__ s = img + (int64_t)u * p.pitch + (int64_t)v * C;
+            for (int c = 0; c < C; ++c) cur[c * plane + q] = inside ? s[c] : (uint8_t)0;
+        }
+    }
+    __syncthreads();
+
+    // ---- the sample's operations ------------------------------------------------------------
+    const int32_t* __restrict__ rec = p.ops + (int64_t)b * p.n_ops * 8;
+    for (int o = 0; o < p.n_ops; ++o, rec += 8) {
+        const int kind = rec[0];
+        const int r1 = rec[1];
+        const float alpha = __int_as_float(r1);
+        switch (kind) {
+        case TB_AUG_AFFINE: {
+            const uint32_t a0 = rec[1], a1 = rec[2], a2 = rec[3], a3 = rec[4], a4 = rec[5], a5 = rec[6];
+            for (int q = tid; q < plane; q += kAugThreads) {
+                const int y = q / W, x = q - y * W;
+                const int xin = (int)(a2 + (uint32_t)x * a0 + (uint32_t)y * a1) >> 16;
+                const int yin = (int)(a5 + (uint32_t)x * a3 + (uint32_t)y * a4) >> 16;
+                const bool ok = (unsigned)xin < (unsigned)W && (unsigned)yin < (unsigned)H;
+                const int s = ok ? yin * W + xin : 0;
+                for (int c = 0; c < C; ++c) alt[c * plane + q] = ok ? cur[c * plane + s] : (uint8_t)0;
+            }
+            uint8_t* t = cur; cur = alt; alt = t;
+            break;
+        }
+        case TB_AUG_BRIGHTNESS:
+            for (int i = tid; i < total; i += kAugThreads) cur[i] = aug_blend(0, cur[i], alpha);
+            break;
+        case TB_AUG_COLOR:
+            if (C == 3)
+                for (int q = tid; q < plane; q += kAugThreads) {
+                    const int r = cur[q], g = cur[plane + q], bl = cur[2 * plane + q];
+                    const int l = aug_grey(r, g, bl);
+                    cur[q] = aug_blend(l, r, alpha);
+                    cur[plane + q] = aug_blend(l, g, alpha);
+                    cur[2 * plane + q] = aug_blend(l, bl, alpha);
+                }
+            break;
+        case TB_AUG_CONTRAST: {
+            if (tid == 0) s_sum = 0;
+            __syncthreads();
+            int part = 0;
+            for (int q = tid; q < plane; q += kAugThreads)
+                part += C == 3 ? aug_grey(cur[q], cur[plane + q], cur[2 * plane + q]) : (int)cur[q];
+            part = __reduce_add_sync(0xffffffffu, part);
+            if ((tid & 31) == 0) atomicAdd(&s_sum, part);
+            __syncthreads();
+            // int(sum / count + 0.5), Python float64
+            const int mean = (int)__dadd_rn(__ddiv_rn((double)s_sum, (double)plane), 0.5);
+            for (int i = tid; i < total; i += kAugThreads) cur[i] = aug_blend(mean, cur[i], alpha);
+            break;
+        }
+        case TB_AUG_SHARPNESS: {
+            const float k1 = __fdiv_rn(1.0f, 13.0f), k5 = __fdiv_rn(5.0f, 13.0f);
+            for (int q = tid; q < plane; q += kAugThreads) {
+                const int y = q / W, x = q - y * W;
+                const bool interior = x >= 1 && x < W - 1 && y >= 1 && y < H - 1;
+                for (int c = 0; c < C; ++c) {
+                    const uint8_t* __restrict__ im = cur + c * plane + q;
+                    const int v = im[0];
+                    int deg = v;
+                    if (interior) {
+                        float ss = 0.5f;
+#pragma unroll
+                        for (int dy = 1; dy >= -1; --dy) {
+                            const uint8_t* __restrict__ row = im + dy * W;
+                            const float mid = dy == 0 ? k5 : k1;
+                            const float part = __fadd_rn(__fadd_rn(__fmul_rn((float)row[-1], k1), __fmul_rn((float)row[0], mid)),
+                                                         __fmul_rn((float)row[1], k1));
+                            ss = __fadd_rn(ss, part);
+                        }
+                        deg = ss <= 0.0f ? 0 : (ss >= 255.0f ? 255 : (int)ss);
+                    }
+                    alt[c * plane + q] = aug_blend(deg, v, alpha);
+                }
+            }
+            uint8_t* t = cur; cur = alt; alt = t;
+            break;
+        }
+        case TB_AUG_POSTERIZE:
+            for (int i = tid; i < total; i += kAugThreads) cur[i] = cur[i] & (uint8_t)r1;
+            break;
+        case TB_AUG_SOLARIZE:
+            for (int i = tid; i < total; i += kAugThreads) {
+                const int v = cur[i];
+                cur[i] = (uint8_t)(v < r1 ? v : 255 - v);
+            }
+            break;
+        case TB_AUG_INVERT:
+            for (int i = tid; i < total; i += kAugThreads) cur[i] = (uint8_t)(255 - cur[i]);
+            break;
+        case TB_AUG_AUTOCONTRAST:
+        case TB_AUG_EQUALIZE: {
+            for (int i = tid; i < C * 256; i += kAugThreads) s_hist[i] = 0;
+            if (tid < 3) { s_lo[tid] = 256; s_hi[tid] = -1; }
+            __syncthreads();
+            for (int i = tid; i < total; i += kAugThreads) atomicAdd(&s_hist[(i / plane) * 256 + cur[i]], 1);
+            __syncthreads();
+            for (int c = 0; c < C; ++c)
+                if (s_hist[c * 256 + tid]) { atomicMin(&s_lo[c], tid); atomicMax(&s_hi[c], tid); }
+            __syncthreads();
+            for (int c = 0; c < C; ++c) {
+                const int lo = s_lo[c], hi = s_hi[c];
+                int entry = tid;
+                if (kind == TB_AUG_AUTOCONTRAST) {
+                    if (hi > lo) {      // ImageOps.autocontrast: scale = 255.0 / (hi - lo); offset = -lo * scale
+                        const double scale = __ddiv_rn(255.0, (double)(hi - lo));
+                        const double offset = __dmul_rn((double)(-lo), scale);
+                        const double v = __dadd_rn(__dmul_rn((double)tid, scale), offset);
+                        const int iv = (int)v;
+                        entry = iv < 0 ? 0 : (iv > 255 ? 255 : iv);
+                    }
+                } else {
+                    // ImageOps.equalize: step = (pixels - last non-empty bin) // 255;
+                    // table[i] = (step // 2 + sum of bins below i) // step
+                    const int h = s_hist[c * 256 + tid];
+                    int incl = h;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const int n = __shfl_up_sync(0xffffffffu, incl, d);
+                        if ((tid & 31) >= d) incl += n;
+                    }
+                    __syncthreads();        // s_warp free again (previous channel read it)
+                    if ((tid & 31) == 31) s_warp[tid >> 5] = incl;
+                    __syncthreads();
+                    int below = incl - h;
+                    for (int w = 0; w < (tid >> 5); ++w) below += s_warp[w];
+                    const int step = hi > lo ? (plane - s_hist[c * 256 + hi]) / 255 : 0;
+                    if (step > 0) {
+                        const int n = (step / 2 + below) / step;
+                        entry = n > 255 ? 255 : n;
+                    }
+                }
+                s_tab[c * 256 + tid] = (uint8_t)entry;
+            }
+            __syncthreads();
+            for (int i = tid; i < total; i += kAugThreads) cur[i] = s_tab[(i / plane) * 256 + cur[i]];
+            break;
+        }
+        default:        // TB_AUG_IDENTITY and unknown codes
+            break;
+        }
+        __syncthreads();
+    }
+
+    // ---- table lookup, cast, planar store ---------------------------------------------------
+    tb_launch_dependents();
+    T* __restrict__ d = (T*)p.dst + (int64_t)b * total;
+    if (sizeof(T) == 4 ? ((total & 3) == 0 && (((uintptr_t)p.dst) & 15) == 0)
+                       : ((total & 7) == 0 && (((uintptr_t)p.dst) & 15) == 0)) {
+        constexpr int PX = 16 / sizeof(T);
+        for (int i = tid * PX; i < total; i += kAugThreads * PX) {
+            __align__(16) T v[PX];
+#pragma unroll
+            for (int k = 0; k < PX; ++k) v[k] = s_lut[((i + k) / plane) * 256 + cur[i + k]];
+            tb_st_cs_v4(d + i, *(const uint4*)v);
+        }
+    } else {
+        for (int i = tid; i < total; i += kAugThreads) d[i] = s_lut[(i / plane) * 256 + cur[i]];
+    }
+}
+
+template <typename T>
+int launch_augment(const AugParams& p, size_t smem, cudaStream_t s) {
+    if (smem > 48 * 1024)
+        TB_CUDA(cudaFuncSetAttribute(tb_augment_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tb_augment_kernel<T><<<p.B, kAugThreads, smem, s>>>(p);
+    TB_LAUNCH_CHECK("tb_augment_kernel");
+    return TB_OK;
+}
+
+}  // namespace
+
+extern "C" int tb_augment_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride,
+                                          int64_t src_row_pitch, void* dst, int dst_dtype, int out_h, int out_w,
+                                          const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
+                                          int pad_y, int pad_x, int pad_mode, const int32_t* ops, int n_ops,
+                                          const void* lut, int flags, tb_stream_t stream) {
+    (void)flags;
+    TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_augment: bad source shape B=%d H=%d W=%d", B, H, W);
+    TB_REQUIRE(C == 1 || C == 3, "tb_augment: C=%d not in {1,3} (PIL modes L and RGB)", C);
+    TB_REQUIRE(out_h >= 1 && out_w >= 1, "tb_augment: bad output size %dx%d", out_h, out_w);
+    TB_REQUIRE(out_h < 32768 && out_w < 32768, "tb_augment: output beyond the 16.16 fixed-point range");
+    TB_REQUIRE(tb_dtype_size(dst_dtype) != 0, "tb_augment: unknown dst_dtype %d", dst_dtype);
+    TB_REQUIRE(pad_mode >= TB_PAD_NONE && pad_mode <= TB_PAD_SYMMETRIC, "tb_augment: unknown pad_mode %d", pad_mode);
+    TB_REQUIRE(pad_y >= 0 && pad_x >= 0, "tb_augment: negative padding");
+    if (pad_mode == TB_PAD_REFLECT)
+        TB_REQUIRE(pad_y <= H - 1 && pad_x <= W - 1, "tb_augment: reflect padding must be smaller than the image");
+    if (pad_mode == TB_PAD_SYMMETRIC)
+        TB_REQUIRE(pad_y <= H && pad_x <= W, "tb_augment: symmetric padding must not exceed the image");
+    TB_REQUIRE(src_row_pitch >= (int64_t)W * C, "tb_augment: src_row_pitch %lld < W*C", (long long)src_row_pitch);
+    TB_REQUIRE(src_batch_stride >= 0, "tb_augment: negative src_batch_stride");
+    TB_REQUIRE(n_ops >= 0 && n_ops <= TB_AUG_MAX_OPS, "tb_augment: n_ops=%d not in [0,%d]", n_ops, TB_AUG_MAX_OPS);
+    if (B == 0) return TB_OK;
+    TB_REQUIRE(src && dst && lut, "tb_augment: NULL src/dst/lut");
+    TB_REQUIRE(ops || n_ops == 0, "tb_augment: NULL ops");
+    TB_REQUIRE(((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_augment: dst misaligned for its dtype");
+
+    TbDevice dev;
+    int rc = tb_device(&dev);
+    if (rc) return rc;
+
+    AugParams p;
+    p.src = src; p.B = B; p.H = H; p.W = W; p.C = C; p.bs = src_batch_stride; p.pitch = src_row_pitch;
+    p.dst = dst; p.out_h = out_h; p.out_w = out_w; p.top = crop_top; p.left = crop_left; p.flip = flip;
+    p.pad_y = pad_y; p.pad_x = pad_x; p.pad_mode = pad_mode; p.ops = ops; p.n_ops = n_ops; p.lut = lut;
+    const int64_t plane = (int64_t)out_h * out_w;
+    const int64_t buf = (plane * C + 15) & ~(int64_t)15;
+    const int64_t smem = 2 * buf + (int64_t)C * 256 * tb_dtype_size(dst_dtype);
+    // the image lives in shared memory, twice (operations that move pixels write the other copy)
+    if (smem + 8 * 1024 > dev.max_smem_optin)
+        return tb_fail(TB_ENOTSUP, "tb_augment: a %dx%dx%d image does not fit in shared memory twice (%lld of %d bytes)",
+                       out_h, out_w, C, (long long)smem, dev.max_smem_optin - 8 * 1024);
+    p.plane = (int)plane;
+    p.buf_bytes = (int)buf;
+    cudaStream_t s = (cudaStream_t)stream;
+    return dst_dtype == TB_F32 ? launch_augment<float>(p, (size_t)smem, s) : launch_augment<uint16_t>(p, (size_t)smem, s);
+}

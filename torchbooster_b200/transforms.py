@@ -21,6 +21,8 @@ import numpy as np
 import torch
 
 from . import _native as N
+from . import _torchrng
+from . import augment as _augment
 
 IntPair = Union[int, Tuple[int, int]]
 
@@ -38,7 +40,8 @@ class TransformSpec:
     """What the pipeline does, in the reference's vocabulary.
 
     Order: ``Resize`` -> ``CenterCrop`` -> ``RandomCrop(size, padding, padding_mode)`` ->
-    ``RandomHorizontalFlip(p)`` -> ``ToTensor`` -> ``Normalize(mean, std)`` -> ``1 - X`` -> cast.
+    ``RandomHorizontalFlip(p)`` -> ``RandomRotation(rotation)`` -> ``RandAugment(*rand_augment)`` ->
+    ``ToTensor`` -> ``Normalize(mean, std)`` -> ``1 - X`` -> cast.
 
     resize        ``T.Resize`` argument: int (short side) or (h, w); Pillow antialiased bilinear.
     center_crop   ``T.CenterCrop`` size (zero fill when larger than the image).
@@ -49,6 +52,10 @@ class TransformSpec:
     padding       ``T.RandomCrop`` padding: int or (left/right, top/bottom).
     padding_mode  "constant" (fill 0) | "reflect" | "edge" | "symmetric".
     flip_p        ``T.RandomHorizontalFlip`` probability; ``None`` = transform not in the pipeline.
+    rotation      ``T.RandomRotation`` degrees (number or (min, max)); nearest, no expand, fill 0.
+    rand_augment  ``T.RandAugment`` as ``(num_ops, magnitude, num_magnitude_bins)``, ``True`` = its defaults
+                  ``(2, 9, 31)`` (``resnet.py:99-100``).  Both apply to crop / flip pipelines; the per-sample
+                  operations come from ``params`` (a fourth element) or the replayed generator.
     mean, std     ``T.Normalize``; ``None`` = ToTensor only.
     one_minus     the ``1.0 - X`` of ``examples/img_gen/gan/gan.py:99``.
     dtype         output dtype: float32 (the reference), bfloat16 or float16 (RNE of the fp32 value).
@@ -60,6 +67,8 @@ class TransformSpec:
     padding: IntPair = 0
     padding_mode: str = "constant"
     flip_p: Optional[float] = None
+    rotation: Union[None, float, Tuple[float, float]] = None
+    rand_augment: Union[None, bool, Tuple[int, int, int]] = None
     resize: Optional[IntPair] = None
     center_crop: Optional[IntPair] = None
     mean: Optional[Sequence[float]] = None
@@ -80,7 +89,22 @@ class TransformSpec:
         if self.random_resized_crop is not None and (self.resize is not None or self.center_crop is not None or
                                                      self.crop is not None or _pair(self.padding) != (0, 0)):
             raise ValueError("random_resized_crop excludes resize, center_crop, crop and padding")
+        if self.augments and (self.resize is not None or self.center_crop is not None or
+                              self.random_resized_crop is not None):
+            raise NotImplementedError("rotation / rand_augment are built for crop / flip pipelines")
+        if self.rand_augment not in (None, True, False) and len(tuple(self.rand_augment)) != 3:
+            raise ValueError("rand_augment is True or (num_ops, magnitude, num_magnitude_bins)")
         N.dtype_code(self.dtype)
+
+    @property
+    def augments(self) -> bool:
+        return self.rotation is not None or bool(self.rand_augment)
+
+    @property
+    def rand_augment_args(self) -> Optional[Tuple[int, int, int]]:
+        if not self.rand_augment:
+            return None
+        return (2, 9, 31) if self.rand_augment is True else tuple(int(v) for v in self.rand_augment)
 
 
 def resized_output_size(h: int, w: int, size: IntPair) -> Tuple[int, int]:
@@ -141,7 +165,8 @@ class ResizedCropParams:
     (``torchvision/transforms/transforms.py`` RandomResizedCrop.get_params: up to ten attempts of
     ``area * uniform(scale)``, ``exp(uniform(log ratio))``, then two ``randint``; central fallback).
 
-    ``torch.empty(1).uniform_(a, b)`` spends one 32-bit word: ``fl32(fl32((w & (2**24 - 1)) * 2**-24 * fl32(b - a)) + a)``.
+    ``torch.empty(1).uniform_(a, b)`` spends one 32-bit word: ``x * fl32(b - a) + a`` with ``x = (w & (2**24 - 1)) * 2**-24``,
+    fused or not as torch's CPU kernel on this host does it (``_torchrng.uniform``).
     The number of words per sample varies with the rejection loop, so words are drawn in blocks
     and the unused tail is kept for the next batch; the per-word candidates (area, aspect) are
     computed vectorised, the accept / reject walk is sequential.
@@ -163,8 +188,7 @@ class ResizedCropParams:
 
     @staticmethod
     def _uniform(words: np.ndarray, a: np.float32, b: np.float32) -> np.ndarray:
-        x = (words & np.uint64(0xFFFFFF)).astype(np.float32) * np.float32(2.0 ** -24)
-        return (x * np.float32(b - a)).astype(np.float32) + np.float32(a)
+        return _torchrng.uniform(words, float(a), float(b))
 
     def draw(self, batch: int, height: int, width: int, flip_p: Optional[float] = None):
         """Returns numpy ``(box int32[B,4] = top, left, h, w ; flip uint8[B])``."""
@@ -214,6 +238,8 @@ class BatchTransform:
             self._rng = None
         elif spec.random_resized_crop is not None:
             self._rng = ResizedCropParams(seed, spec.rrc_scale, spec.rrc_ratio)
+        elif spec.augments:
+            self._rng = _augment.AugmentParams(seed, spec.rotation, spec.rand_augment_args)
         else:
             self._rng = CropFlipParams(seed)
         self._param_host = None
@@ -292,13 +318,16 @@ class BatchTransform:
         return dict(rs=(rs_h, rs_w), off=(off_y, off_x), cur=(cur_h, cur_w), pad=(px, py), crop=crop,
                     out=(out_h, out_w))
 
-    def draw_params(self, batch: int, h: int, w: int):
-        """Next ``(top, left, flip)`` from the replayed torch generator (needs ``seed=``)."""
+    def draw_params(self, batch: int, h: int, w: int, channels: int = 3):
+        """Next ``(top, left, flip)`` -- ``(box, flip)`` for random_resized_crop, ``(top, left, flip, ops)``
+        with rotation / rand_augment -- from the replayed torch generator (needs ``seed=``)."""
         if self._rng is None:
             raise RuntimeError("BatchTransform was built without a seed; pass params= explicitly")
         if self.spec.random_resized_crop is not None:
             return self._rng.draw(batch, h, w, self.spec.flip_p)
         g = self.geometry(h, w)
+        if self.spec.augments:
+            return self._rng.draw_records(batch, g["cur"][0], g["cur"][1], channels, g["crop"], g["pad"], self.spec.flip_p)
         return self._rng.draw(batch, g["cur"][0], g["cur"][1], g["crop"], g["pad"], self.spec.flip_p)
 
     def _params_to_device(self, params, batch: int):
@@ -315,6 +344,20 @@ class BatchTransform:
         dev = host.to(self.device, non_blocking=True)
         self._param_host = host  # keep the pinned source alive until the copy has run
         return dev[:4 * batch].view(torch.int32), dev[4 * batch:8 * batch].view(torch.int32), dev[8 * batch:]
+
+    def _ops_to_device(self, ops, batch: int, h: int, w: int, channels: int) -> torch.Tensor:
+        """(name, magnitude) lists, or already encoded int32 ``[B, n_ops, 8]`` records -> device tensor."""
+        if isinstance(ops, torch.Tensor) and ops.is_cuda:
+            rec = ops.to(device=self.device, dtype=torch.int32).contiguous()
+        else:
+            arr = ops if isinstance(ops, (np.ndarray, torch.Tensor)) else _augment.encode_ops(ops, h, w, channels)
+            arr = np.ascontiguousarray(np.asarray(arr, dtype=np.int32))
+            host = torch.from_numpy(arr).pin_memory()
+            self._ops_host = host               # pinned source stays alive until the copy has run
+            rec = host.to(self.device, non_blocking=True)
+        if rec.dim() != 3 or rec.shape[0] != batch or rec.shape[2] != _augment.OP_WORDS:
+            raise ValueError(f"ops must be [B={batch}, n_ops, {_augment.OP_WORDS}] int32 records; got {tuple(rec.shape)}")
+        return rec
 
     def _boxes_to_device(self, params, batch: int):
         box, flip = params
@@ -337,7 +380,7 @@ class BatchTransform:
         LMDB map registered with ``LMDBReader.cuda_register``): the kernel reads them in place.
         Crop / flip pipelines only."""
         sp = self.spec
-        if sp.resize is not None or sp.center_crop is not None or sp.random_resized_crop is not None:
+        if sp.resize is not None or sp.center_crop is not None or sp.random_resized_crop is not None or sp.augments:
             raise NotImplementedError("from_records supports crop / flip / normalise pipelines")
         H, W, Cn = (int(v) for v in shape)
         off = np.ascontiguousarray(np.asarray(offsets, dtype=np.int64)) if not isinstance(offsets, torch.Tensor) else None
@@ -377,7 +420,7 @@ class BatchTransform:
         sp = self.spec
         if not batch.is_cuda:
             in_place = (self.zero_copy and batch.is_pinned() and sp.resize is None and sp.center_crop is None and
-                        sp.random_resized_crop is None)
+                        sp.random_resized_crop is None and not sp.augments)
             if not in_place:
                 batch = batch.to(self.device, non_blocking=True)
         elif batch.device != self.device:
@@ -388,13 +431,18 @@ class BatchTransform:
         g = self.geometry(H, W)
         out_h, out_w = g["out"]
         rrc = sp.random_resized_crop is not None
-        if params is None and self._rng is not None and (rrc or g["crop"] is not None or sp.flip_p is not None):
-            params = self.draw_params(B, H, W)
-        top = left = flip = box = None
+        if params is None and self._rng is not None and (rrc or sp.augments or g["crop"] is not None or sp.flip_p is not None):
+            params = self.draw_params(B, H, W, Cn)
+        top = left = flip = box = ops = None
         if rrc:
             if params is None:
                 raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
             box, flip = self._boxes_to_device(params, B)
+        elif sp.augments:
+            if params is None or len(params) != 4:
+                raise ValueError("rotation / rand_augment need params=(top, left, flip, ops) or a seed")
+            ops = self._ops_to_device(params[3], B, out_h, out_w, Cn)
+            top, left, flip = self._params_to_device(params[:3], B)
         elif params is not None:
             top, left, flip = self._params_to_device(params, B)
         if out is None:
@@ -414,6 +462,13 @@ class BatchTransform:
                 rc = L.tb_resized_crop_bilinear_u8_nhwc_to_nchw(
                     batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1), box.data_ptr(),
                     out.data_ptr(), N.dtype_code(sp.dtype), out_h, out_w, ptr(flip), lut.data_ptr(), self.flags, stream)
+            elif ops is not None:
+                mode = N.PAD_MODES[sp.padding_mode] if (px or py) else N.PAD_MODES["none"]
+                rc = L.tb_augment_u8_nhwc_to_nchw(
+                    batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1),
+                    out.data_ptr(), N.dtype_code(sp.dtype), out_h, out_w,
+                    ptr(top), ptr(left), ptr(flip), py, px, mode, ops.data_ptr(), int(ops.shape[1]),
+                    lut.data_ptr(), self.flags, stream)
             elif sp.resize is None and g["off"] == (0, 0) and sp.center_crop is None:
                 mode = N.PAD_MODES[sp.padding_mode] if (px or py) else N.PAD_MODES["none"]
                 rc = L.tb_transform_u8_nhwc_to_nchw(
