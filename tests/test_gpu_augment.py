@@ -39,6 +39,7 @@ def test_reference_cifar_compose_golden(golden):
     spec = TransformSpec(crop=32, padding=4, padding_mode="reflect", flip_p=0.5, rotation=15, rand_augment=True,
                          mean=CIFAR[0], std=CIFAR[1])
     bt = BatchTransform(spec, device="cuda", seed=int(g["cifar_seed"]))
+    bt.lut(3)                                       # the table is built once per spec, not per batch
     before = N.lib().tb_launch_count()
     out = bt(torch.from_numpy(g["cifar_input"]).cuda())
     torch.cuda.synchronize()
@@ -118,6 +119,22 @@ def test_full_cifar_batches_replayed_vs_torchvision():
         assert same(got, want), step
 
 
+def test_mnist_rand_augment_replayed():
+    """lenet.py:95: T.Compose([T.RandAugment(), T.ToTensor()]) on 28x28 grey images -- no crop, flip or
+    rotation in the pipeline, so only RandAugment draws; two batches from one seed."""
+    import torchvision.transforms as T
+    from PIL import Image
+    rng = np.random.default_rng(4)
+    bt = BatchTransform(TransformSpec(rand_augment=True), device="cuda", seed=99)
+    compose = T.Compose([T.RandAugment(), T.ToTensor()])
+    torch.manual_seed(99)
+    for _ in range(2):
+        batch = rng.integers(0, 256, (128, 28, 28, 1), dtype=np.uint8)
+        batch[batch < 140] = 0                                  # digit-like: mostly black
+        want = torch.stack([compose(Image.fromarray(batch[b, :, :, 0])) for b in range(batch.shape[0])])
+        assert same(bt(torch.from_numpy(batch).cuda()), want)
+
+
 def test_larger_images_and_limits():
     rng = np.random.default_rng(2)
     batch = rng.integers(0, 256, (3, 150, 170, 3), dtype=np.uint8)          # 2 x 76.5 KB of shared memory
@@ -130,8 +147,8 @@ def test_larger_images_and_limits():
         BatchTransform(spec, device="cuda")(torch.zeros((1, 224, 224, 3), dtype=torch.uint8, device="cuda"),
                                             params=(None, None, None, [[("Invert", 0.0)]]))
     with pytest.raises(ValueError, match="not in"):
-        BatchTransform(spec, device="cuda")(torch.zeros((1, 8, 8, 4), dtype=torch.uint8, device="cuda"),
-                                            params=(None, None, None, [[("Invert", 0.0)]]))
+        BatchTransform(TransformSpec(rand_augment=True), device="cuda")(
+            torch.zeros((1, 8, 8, 4), dtype=torch.uint8, device="cuda"), params=(None, None, None, [[("Invert", 0.0)]]))
     with pytest.raises(ValueError, match="seed"):
         BatchTransform(spec, device="cuda")(torch.zeros((1, 8, 8, 3), dtype=torch.uint8, device="cuda"))
     with pytest.raises(NotImplementedError):

@@ -172,8 +172,22 @@ def augment_case(name, B, iters, host_params=False):
     else:
         ms, host_ms = time_loop(lambda i: bt(srcs[i % nbuf], params=prm, out=out[i & 1]), iters), None
     gbs = 15360 * B / (ms * 1e-3) / 1e9
+    cpu = None
+    if host_params and B <= 256:
+        # the reference's own Compose (resnet.py:96-103), one process, on this box's CPU
+        import torchvision.transforms as T
+        from PIL import Image
+        compose = T.Compose([T.RandomCrop(32, 4, padding_mode="reflect"), T.RandomHorizontalFlip(), T.RandomRotation(15),
+                             T.RandAugment(), T.ToTensor(), T.Normalize(CIFAR[0], CIFAR[1], inplace=True)])
+        pil = [Image.fromarray(a) for a in srcs[0].cpu().numpy()]
+        torch.stack([compose(im) for im in pil[:64]])
+        t0 = time.perf_counter()
+        for _ in range(4):
+            torch.stack([compose(im) for im in pil])
+        cpu = 4 * len(pil) / (time.perf_counter() - t0)
     print(json.dumps({"case": name, "B": B, "ms": ms, "images_per_s": B / (ms * 1e-3), "alg_GBps": gbs,
-                      "frac_measured": gbs / PEAK, "host_draw_encode_ms": host_ms}), flush=True)
+                      "frac_measured": gbs / PEAK, "host_draw_encode_ms": host_ms, "cpu_torchvision_1proc_images_per_s": cpu}),
+          flush=True)
 
 
 def loader_case(name, n_images, batch, threads, prefetch=2, in_place=False):

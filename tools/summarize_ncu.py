@@ -90,8 +90,15 @@ def main():
         t = summarize_report(src / "prof_rs.ncu-rep", OUT / f"{tag}_ncu_resize.txt", "resize kernel, C4 workload (batch 256)")
         for name, v in t.items():
             traffic["c4_b256"] = sum(v) / len(v)
+    if (src / "prof_aug.ncu-rep").exists():
+        t = summarize_report(src / "prof_aug.ncu-rep", OUT / f"{tag}_ncu_augment.txt",
+                             "augment kernel, CIFAR training transform (resnet.py:96-103), batch 2048")
+        for name, v in t.items():
+            traffic["aug_cifar_b2048"] = sum(v) / len(v)
     if traffic:
-        (OUT / "traffic.json").write_text(json.dumps(traffic, indent=1) + "\n")
+        old = json.loads((OUT / "traffic.json").read_text()) if (OUT / "traffic.json").exists() else {}
+        old.update(traffic)
+        (OUT / "traffic.json").write_text(json.dumps(old, indent=1) + "\n")
     for f in ("bench_full.json", "bench_ref.json", "configs.jsonl"):
         if (src / f).exists():
             (OUT / f"{tag}_{f}").write_text((src / f).read_text())

@@ -75,6 +75,7 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
     __shared__ int s_hist[3 * 256];
     __shared__ uint8_t s_tab[3 * 256];
     __shared__ int s_lo[3], s_hi[3], s_sum, s_warp[kAugThreads / 32];
+    __shared__ int32_t s_ops[TB_AUG_MAX_OPS * 8];
 
     uint8_t* cur = smem;
     uint8_t* alt = smem + p.buf_bytes;
@@ -89,6 +90,7 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
     {
         const T* __restrict__ glut = (const T*)p.lut;
         for (int i = tid; i < C * 256; i += kAugThreads) s_lut[i] = glut[i];
+        if (tid < p.n_ops * 8) s_ops[tid] = p.ops[(int64_t)b * p.n_ops * 8 + tid];      // one round trip for the whole list
     }
     // ---- gather: pad / crop / flip, interleaved source -> planar shared --------------------
     {
@@ -109,7 +111,7 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
     __syncthreads();
 
     // ---- the sample's operations ------------------------------------------------------------
-    const int32_t* __restrict__ rec = p.ops + (int64_t)b * p.n_ops * 8;
+    const int32_t* rec = s_ops;
     for (int o = 0; o < p.n_ops; ++o, rec += 8) {
         const int kind = rec[0];
         const int r1 = rec[1];
