@@ -99,9 +99,18 @@ def main():
         old = json.loads((OUT / "traffic.json").read_text()) if (OUT / "traffic.json").exists() else {}
         old.update(traffic)
         (OUT / "traffic.json").write_text(json.dumps(old, indent=1) + "\n")
-    for f in ("bench_full.json", "bench_ref.json", "configs.jsonl"):
+    for f in ("bench_full.json", "bench_ref.json"):
         if (src / f).exists():
             (OUT / f"{tag}_{f}").write_text((src / f).read_text())
+    if (src / "configs.jsonl").exists():        # merge by case name: a partial run must not drop the other cases
+        dst = OUT / f"{tag}_configs.jsonl"
+        rows = OrderedDict()
+        for path in (dst, src / "configs.jsonl"):
+            if path.exists():
+                for line in path.read_text().splitlines():
+                    if line.strip():
+                        rows[json.loads(line)["case"]] = line
+        dst.write_text("\n".join(rows.values()) + "\n")
 
 
 if __name__ == "__main__":
