@@ -63,6 +63,11 @@ extern "C" {
 #define TB_AUG_INVERT       10
 #define TB_AUG_MAX_OPS      8
 
+/* tb_to_image_u8 modes */
+#define TB_IMAGE_PLAIN   0   /* Normalize -> ToPILImage */
+#define TB_IMAGE_CLAMP   1   /* Normalize -> x.clamp(0, 1) -> ToPILImage            (adain.py:168-171) */
+#define TB_IMAGE_STRETCH 2   /* Normalize -> (x - x.min()) / (x.max() - x.min()) -> ToPILImage  (online.py:169-174) */
+
 #define TB_FLAG_FORCE_GENERIC 1  /* tests: skip the streaming path, use the one-gather-per-pixel kernel */
 #define TB_FLAG_FORCE_STREAM  2  /* tests: take the streaming path even where the gather kernel is the better launch */
 #define TB_FLAG_NO_PDL        4  /* launch without programmatic stream serialization */
@@ -221,6 +226,21 @@ TB_API int64_t tb_augment_params_walk(
     int has_rotation, float rot_lo, float rot_span, int fused, int height, int width,
     int n_ops, int n_choices, const int32_t* op_table, const uint8_t* op_signed,
     int32_t* top, int32_t* left, uint8_t* flip, int32_t* records);
+
+/*
+ * Model output -> displayable image: float32 [images][C][H][W] -> uint8 [images][H][W][C], replacing
+ * the reference's `utransform` = T.Compose([T.Normalize(mean=-mean/std, std=1.0/std), clamp | hdr,
+ * T.ToPILImage()]) (examples/img_stt/adain/adain.py:168-171, online/online.py:169-174,
+ * offline/offline.py:108-111): (x - mean[c]) / std[c] in float32 (IEEE sub, div), the clamp or the
+ * min-max stretch, * 255, truncation; the same operations in the same order as torchvision, so the
+ * bytes are identical.
+ *   mean, std : HOST float[C], the T.Normalize arguments as float32 (NULL, NULL = no Normalize)
+ *   minmax    : DEVICE float[C][2], per-channel (min, max) of src, for TB_IMAGE_STRETCH only.
+ *               tb_channel_minmax ACCUMULATES into it (the caller initialises it to +inf, -inf).
+ */
+TB_API int tb_channel_minmax(const float* src, int64_t images, int C, int64_t plane, float* minmax, tb_stream_t stream);
+TB_API int tb_to_image_u8(const float* src, int64_t images, int C, int H, int W, const float* mean, const float* std,
+                          int mode, const float* minmax, uint8_t* dst, tb_stream_t stream);
 
 /*
  * One pass over a logits matrix: top-1 and top-k correct counts and confusion-matrix bins.

@@ -125,3 +125,20 @@ def index_map_sample(img: np.ndarray, lut: np.ndarray, *, top: int, left: int, o
     for c in range(C):
         out[c] = lut[c][px[..., c]]
     return out
+
+
+def to_image(x: torch.Tensor, mean=None, std=None, mode=None) -> np.ndarray:
+    """The reference's ``utransform`` (``examples/img_stt/adain/adain.py:168-171``; ``online.py:169-174`` and
+    ``offline.py:108-111`` with the min-max stretch), literally: ``T.Compose([T.Normalize(mean, std),
+    T.Lambda(clamp | hdr), T.ToPILImage()])`` on one ``[C,H,W]`` float tensor -> ``[H,W,C]`` uint8."""
+    import torchvision.transforms as T
+    stages = []
+    if mean is not None:
+        stages.append(T.Normalize(mean=mean, std=std))
+    if mode == "clamp":
+        stages.append(T.Lambda(lambda t: t.clamp(0, 1)))
+    elif mode == "stretch":
+        stages.append(T.Lambda(lambda t: (t - t.min()) / (t.max() - t.min())))
+    stages.append(T.ToPILImage())
+    arr = np.asarray(T.Compose(stages)(x.detach().cpu()))
+    return arr.reshape(x.shape[1], x.shape[2], x.shape[0]).copy()

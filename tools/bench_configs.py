@@ -190,6 +190,23 @@ def augment_case(name, B, iters, host_params=False):
           flush=True)
 
 
+def to_image_case(name, B, H, W, mode, iters):
+    """utransform (adain.py:171 / online.py:174): fp32 NCHW -> uint8 NHWC; 12 B read (+ 12 B for the
+    stretch's extrema pass) + 3 B written per pixel."""
+    if CASE and CASE not in name:
+        return
+    from torchbooster_b200.transforms import ToImage
+    dev = torch.device("cuda", 0)
+    nbuf = max(3, -(-4 * L2 // (B * H * W * 12)))
+    xs = [torch.randn((B, 3, H, W), device=dev) for _ in range(nbuf)]
+    ti = ToImage.inverse_of(IMAGENET[0], IMAGENET[1], mode)
+    ms = time_loop(lambda i: ti(xs[i % nbuf]), iters)
+    alg = B * H * W * (15 + (12 if mode == "stretch" else 0))
+    gbs = alg / (ms * 1e-3) / 1e9
+    print(json.dumps({"case": name, "B": B, "ms": ms, "images_per_s": B / (ms * 1e-3), "alg_GBps": gbs,
+                      "frac_measured": gbs / PEAK}), flush=True)
+
+
 def loader_case(name, n_images, batch, threads, prefetch=2, in_place=False):
     """LMDB (tmpfs) -> BatchLoader background gather into pinned slots -> zero-copy C2 transform."""
     if CASE and CASE not in name:
@@ -300,6 +317,10 @@ def main():
             augment_case(f"aug_cifar_b{bsz}", bsz, 200 if bsz < 10000 else 50)
         augment_case("aug_cifar_b256_host_params", 256, 100, host_params=True)
         augment_case("aug_cifar_b2048_host_params", 2048, 30, host_params=True)
+    if want("image"):
+        to_image_case("to_image_clamp_b32_256", 32, 256, 256, "clamp", 200)
+        to_image_case("to_image_clamp_b256_256", 256, 256, 256, "clamp", 100)
+        to_image_case("to_image_stretch_b256_256", 256, 256, 256, "stretch", 100)
     if want("streams"):
         for ns in (1, 2, 3):
             two_stream_case(f"c2_abi_{ns}stream", 512, 400, ns)

@@ -16,7 +16,7 @@ CSRC = ROOT / "csrc"
 LIB_DIR = ROOT / "lib"
 LIB_PATH = LIB_DIR / "libtorchbooster_b200.so"
 
-SOURCES = ["tb_abi.cu", "tb_lut.cu", "tb_transform.cu", "tb_resize.cu", "tb_augment.cu", "tb_metrics.cu", "tb_lmdb.cpp", "tb_augment_host.cpp"]
+SOURCES = ["tb_abi.cu", "tb_lut.cu", "tb_transform.cu", "tb_resize.cu", "tb_augment.cu", "tb_image.cu", "tb_metrics.cu", "tb_lmdb.cpp", "tb_augment_host.cpp"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -25,7 +25,7 @@ NVCC_FLAGS = [
     "-cudart", "static",
 ]
 # translation units whose float arithmetic must not be contracted into FMAs
-NO_FMAD = {"tb_lut.cu"}
+NO_FMAD = {"tb_lut.cu", "tb_image.cu"}
 # host translation units that restate CPython float expressions: no contraction on the host either
 NO_CONTRACT = {"tb_augment_host.cpp"}
 

@@ -1,0 +1,152 @@
+// Model output back to a displayable image: Normalize(mean', std') -> clamp(0, 1) | min-max stretch
+// -> ToPILImage, float32 NCHW -> uint8 NHWC, on the device.
+//
+// Replaces the `utransform` of the reference's style-transfer examples
+// (examples/img_stt/adain/adain.py:168-171: T.Normalize(mean=-mean/std, std=1.0/std), clamp(0, 1),
+// T.ToPILImage(); examples/img_stt/online/online.py:169-174 and offline/offline.py:108-111 use the
+// stretch hdr(x) = (x - x.min()) / (x.max() - x.min()) instead of the clamp).  torchvision's chain
+// is tensor.sub(mean).div(std) in float32 (_functional_tensor.py:905-928), the Lambda, then
+// pic.mul(255).byte() and a CHW -> HWC transpose (functional.py to_pil_image): five passes over
+// the tensor.  Here: one pass (plus one reduction pass for the stretch), every float operation the
+// same IEEE round-to-nearest operation in the same order, so the bytes are identical.
+//
+// The stretch needs the extrema of the NORMALISED tensor.  (x - m) / s with s > 0 is monotone in x
+// under IEEE rounding, so they are the images of the per-channel extrema of the input:
+// tb_channel_minmax accumulates those (atomics on the ordered-integer view of the floats).
+#include "tb_common.cuh"
+
+namespace {
+
+struct ImgParams {
+    const float* src;
+    uint8_t* dst;
+    int64_t images;     // B
+    int C;
+    int64_t plane;      // H * W
+    float mean[4], std[4];
+    int mode;
+    const float* minmax;    // device [C][2]: per-channel min, max of src (TB_IMAGE_STRETCH)
+};
+
+__device__ __forceinline__ void atomic_min_float(float* addr, float v) {
+    if (v >= 0.0f) atomicMin((int*)addr, __float_as_int(v));
+    else atomicMax((unsigned int*)addr, __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_float(float* addr, float v) {
+    if (v >= 0.0f) atomicMax((int*)addr, __float_as_int(v));
+    else atomicMin((unsigned int*)addr, __float_as_uint(v));
+}
+
+__global__ void __launch_bounds__(256) tb_channel_minmax_kernel(const float* __restrict__ src, int64_t images, int C,
+                                                                 int64_t plane, int chunks, float* minmax) {
+    tb_grid_dependency_wait();
+    const int64_t bc = blockIdx.x / chunks;          // (image, channel) plane
+    const int chunk = blockIdx.x - (int)(bc * chunks);
+    const int c = (int)(bc % C);
+    const float* __restrict__ pl = src + bc * plane;
+    const int64_t per = (plane + chunks - 1) / chunks;
+    const int64_t lo = chunk * per, hi = min(plane, lo + per);
+    float mn = __int_as_float(0x7f800000), mx = __int_as_float(0xff800000);
+    for (int64_t i = lo + threadIdx.x; i < hi; i += 256) {
+        const float v = __ldg(pl + i);
+        mn = fminf(mn, v);
+        mx = fmaxf(mx, v);
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, d));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+    }
+    if ((threadIdx.x & 31) == 0 && lo < hi) {
+        atomic_min_float(minmax + 2 * c, mn);
+        atomic_max_float(minmax + 2 * c + 1, mx);
+    }
+    (void)images;
+}
+
+__device__ __forceinline__ float normalised(float x, float m, float s) { return __fdiv_rn(__fsub_rn(x, m), s); }
+
+template <int C>
+__global__ void __launch_bounds__(256) tb_to_image_kernel(ImgParams p) {
+    tb_grid_dependency_wait();
+    float lo = 0.0f, span = 1.0f;
+    if (p.mode == TB_IMAGE_STRETCH) {
+        // x.min() / x.max() of the normalised tensor (see the header of this file)
+        float hi = __int_as_float(0xff800000);
+        lo = __int_as_float(0x7f800000);
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            lo = fminf(lo, normalised(p.minmax[2 * c], p.mean[c], p.std[c]));
+            hi = fmaxf(hi, normalised(p.minmax[2 * c + 1], p.mean[c], p.std[c]));
+        }
+        span = __fsub_rn(hi, lo);
+    }
+    const int64_t total = p.images * p.plane;
+    for (int64_t q = (int64_t)blockIdx.x * 256 + threadIdx.x; q < total; q += (int64_t)gridDim.x * 256) {
+        const int64_t b = q / p.plane;
+        const float* __restrict__ s = p.src + (b * C) * p.plane + (q - b * p.plane);
+        uint8_t out[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            float y = normalised(__ldg(s + c * p.plane), p.mean[c], p.std[c]);
+            if (p.mode == TB_IMAGE_CLAMP) y = fminf(fmaxf(y, 0.0f), 1.0f);           // x.clamp(0, 1)
+            else if (p.mode == TB_IMAGE_STRETCH) y = __fdiv_rn(__fsub_rn(y, lo), span);
+            // pic.mul(255).byte(): truncation; out-of-range values wrap like the C cast of the int value
+            out[c] = (uint8_t)(int)__fmul_rn(y, 255.0f);
+        }
+        uint8_t* d = p.dst + q * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c) d[c] = out[c];
+    }
+}
+
+}  // namespace
+
+extern "C" int tb_channel_minmax(const float* src, int64_t images, int C, int64_t plane, float* minmax, tb_stream_t stream) {
+    TB_REQUIRE(images >= 0 && C >= 1 && C <= 4 && plane >= 1, "tb_channel_minmax: bad shape");
+    if (images == 0) return TB_OK;
+    TB_REQUIRE(src && minmax, "tb_channel_minmax: NULL argument");
+    TbDevice dev;
+    int rc = tb_device(&dev);
+    if (rc) return rc;
+    const int64_t planes = images * C;
+    int chunks = (int)((plane + 16383) / 16384);
+    while ((int64_t)chunks * planes < 4 * dev.sm_count && chunks * 1024 < plane) chunks *= 2;
+    TB_REQUIRE(planes * chunks < ((int64_t)1 << 31), "tb_channel_minmax: grid too large");
+    tb_channel_minmax_kernel<<<(unsigned)(planes * chunks), 256, 0, (cudaStream_t)stream>>>(src, images, C, plane, chunks, minmax);
+    TB_LAUNCH_CHECK("tb_channel_minmax_kernel");
+    return TB_OK;
+}
+
+extern "C" int tb_to_image_u8(const float* src, int64_t images, int C, int H, int W, const float* mean, const float* std,
+                              int mode, const float* minmax, uint8_t* dst, tb_stream_t stream) {
+    TB_REQUIRE(images >= 0 && H >= 1 && W >= 1, "tb_to_image_u8: bad shape");
+    TB_REQUIRE(C == 1 || C == 3 || C == 4, "tb_to_image_u8: C=%d is not a PIL mode (1, 3 or 4 channels)", C);
+    TB_REQUIRE(mode >= TB_IMAGE_PLAIN && mode <= TB_IMAGE_STRETCH, "tb_to_image_u8: unknown mode %d", mode);
+    TB_REQUIRE((mean == nullptr) == (std == nullptr), "tb_to_image_u8: mean and std come together");
+    if (images == 0) return TB_OK;
+    TB_REQUIRE(src && dst, "tb_to_image_u8: NULL src/dst");
+    TB_REQUIRE(mode != TB_IMAGE_STRETCH || minmax, "tb_to_image_u8: the stretch needs the per-channel extrema (tb_channel_minmax)");
+    ImgParams p;
+    p.src = src; p.dst = dst; p.images = images; p.C = C; p.plane = (int64_t)H * W; p.mode = mode; p.minmax = minmax;
+    for (int c = 0; c < 4; ++c) { p.mean[c] = 0.0f; p.std[c] = 1.0f; }
+    for (int c = 0; c < C && mean; ++c) {
+        // torchvision raises for a zero std (_functional_tensor.py:923-924); the stretch relies on std > 0
+        TB_REQUIRE(std[c] != 0.0f, "tb_to_image_u8: std evaluated to zero, leading to division by zero");
+        TB_REQUIRE(mode != TB_IMAGE_STRETCH || std[c] > 0.0f, "tb_to_image_u8: the stretch needs std > 0");
+        p.mean[c] = mean[c];
+        p.std[c] = std[c];
+    }
+    TbDevice dev;
+    int rc = tb_device(&dev);
+    if (rc) return rc;
+    const int64_t total = images * p.plane;
+    const int64_t want = (total + 255) / 256, cap = (int64_t)dev.sm_count * 16;
+    const int64_t blocks = want < cap ? want : cap;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (C == 1) tb_to_image_kernel<1><<<(unsigned)blocks, 256, 0, s>>>(p);
+    else if (C == 3) tb_to_image_kernel<3><<<(unsigned)blocks, 256, 0, s>>>(p);
+    else tb_to_image_kernel<4><<<(unsigned)blocks, 256, 0, s>>>(p);
+    TB_LAUNCH_CHECK("tb_to_image_kernel");
+    return TB_OK;
+}

@@ -487,3 +487,66 @@ class BatchTransform:
                     ptr(top), ptr(left), ptr(flip), off_y - py, off_x - px, lut.data_ptr(), self.flags, stream)
         N.check(rc)
         return out
+
+
+class ToImage:
+    """The reference's ``utransform``: ``T.Compose([T.Normalize(mean, std), clamp | hdr, T.ToPILImage()])``
+    (``examples/img_stt/adain/adain.py:168-171``, ``online/online.py:169-174``, ``offline/offline.py:108-111``)
+    for a float32 CUDA tensor ``[C,H,W]`` or ``[B,C,H,W]`` -> uint8 ``[H,W,C]`` / ``[B,H,W,C]`` on the GPU,
+    byte-identical to torchvision's chain.
+
+    mode  ``None`` (Normalize + ToPILImage), ``"clamp"`` (``x.clamp(0, 1)``) or ``"stretch"``
+          (``(x - x.min()) / (x.max() - x.min())`` over the whole tensor).
+    mean, std are the ``T.Normalize`` arguments; ``ToImage.inverse_of(mean, std)`` builds the reference's
+    ``mean=-mean / std, std=1.0 / std`` in float64 numpy as its examples do.
+    """
+
+    MODES = {None: 0, "plain": 0, "clamp": 1, "stretch": 2, "hdr": 2}
+
+    def __init__(self, mean=None, std=None, mode: Optional[str] = "clamp"):
+        if (mean is None) != (std is None):
+            raise ValueError("mean and std must be given together")
+        if mode not in self.MODES:
+            raise ValueError(f"mode must be one of {sorted(k for k in self.MODES if k)} or None")
+        self.mode = self.MODES[mode]
+        # F.normalize: torch.as_tensor(mean, dtype=tensor.dtype) -- float32 of the given numbers
+        self.mean = None if mean is None else np.atleast_1d(np.asarray(mean, dtype=np.float64)).astype(np.float32)
+        self.std = None if std is None else np.atleast_1d(np.asarray(std, dtype=np.float64)).astype(np.float32)
+
+    @classmethod
+    def inverse_of(cls, mean, std, mode: Optional[str] = "clamp") -> "ToImage":
+        mean, std = np.asarray(mean, dtype=np.float64), np.asarray(std, dtype=np.float64)
+        return cls(-mean / std, 1.0 / std, mode)
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        N.require_cuda(x, "x")
+        if x.dtype != torch.float32 or x.dim() not in (3, 4):
+            raise TypeError(f"x must be float32 [C,H,W] or [B,C,H,W]; got {x.dtype} {tuple(x.shape)}")
+        single = x.dim() == 3
+        xb = (x.unsqueeze(0) if single else x).contiguous()
+        B, Cn, H, W = xb.shape
+        mean = std = None
+        if self.mean is not None:
+            mean = np.ascontiguousarray(np.broadcast_to(self.mean, (Cn,)) if self.mean.shape[0] == 1 else self.mean)
+            std = np.ascontiguousarray(np.broadcast_to(self.std, (Cn,)) if self.std.shape[0] == 1 else self.std)
+            if mean.shape[0] != Cn or std.shape[0] != Cn:
+                raise ValueError(f"mean/std have {mean.shape[0]}/{std.shape[0]} entries for {Cn} channels")
+        out = torch.empty((B, H, W, Cn), dtype=torch.uint8, device=x.device)
+        L = N.lib()
+        with torch.cuda.device(x.device):
+            stream = N.current_stream_ptr(x.device)
+            minmax = None
+            if self.mode == 2:
+                minmax = torch.tensor([[float("inf"), float("-inf")]] * Cn, dtype=torch.float32, device=x.device)
+                N.check(L.tb_channel_minmax(xb.data_ptr(), B, Cn, H * W, minmax.data_ptr(), stream))
+            N.check(L.tb_to_image_u8(xb.data_ptr(), B, Cn, H, W, None if mean is None else mean.ctypes.data,
+                                     None if std is None else std.ctypes.data, self.mode,
+                                     None if minmax is None else minmax.data_ptr(), out.data_ptr(), stream))
+        return out[0] if single else out
+
+    @staticmethod
+    def to_pil(image: torch.Tensor):
+        """uint8 ``[H,W,C]`` tensor -> ``PIL.Image`` (what ``T.ToPILImage`` returns)."""
+        from PIL import Image
+        arr = image.cpu().numpy()
+        return Image.fromarray(arr[:, :, 0] if arr.shape[2] == 1 else arr)
