@@ -67,6 +67,7 @@ extern "C" {
 #define TB_IMAGE_PLAIN   0   /* Normalize -> ToPILImage */
 #define TB_IMAGE_CLAMP   1   /* Normalize -> x.clamp(0, 1) -> ToPILImage            (adain.py:168-171) */
 #define TB_IMAGE_STRETCH 2   /* Normalize -> (x - x.min()) / (x.max() - x.min()) -> ToPILImage  (online.py:169-174) */
+#define TB_IMAGE_STATIC_MAX_CHANNELS 4   /* channels the fixed extrema array of tb_to_image_stretch_u8_static holds */
 
 #define TB_FLAG_FORCE_GENERIC 1  /* tests: skip the streaming path, use the one-gather-per-pixel kernel */
 #define TB_FLAG_FORCE_STREAM  2  /* tests: take the streaming path even where the gather kernel is the better launch */
@@ -241,6 +242,20 @@ TB_API int64_t tb_augment_params_walk(
 TB_API int tb_channel_minmax(const float* src, int64_t images, int C, int64_t plane, float* minmax, tb_stream_t stream);
 TB_API int tb_to_image_u8(const float* src, int64_t images, int C, int H, int W, const float* mean, const float* std,
                           int mode, const float* minmax, uint8_t* dst, tb_stream_t stream);
+
+/*
+ * tb_channel_minmax + tb_to_image_u8(TB_IMAGE_STRETCH) in one call that allocates nothing, here or
+ * in the caller: the per-channel extrema between the two passes live in a fixed device array of
+ * this library (TB_IMAGE_STATIC_MAX_CHANNELS x 2 floats; C beyond that is rejected with
+ * TB_EINVAL), reset to (+inf, -inf) on the stream at the start of every call.  No reference
+ * counterpart (the reference's tensors come from torch's allocator); same bytes as the two-call
+ * form.  The array is ONE per device: calls that overlap in time on the same device (different
+ * streams or threads) race on it -- keep them on one stream or serialise them.  The array's
+ * address is looked up once per device, on the first call for that device; make that first call
+ * before any stream capture begins.
+ */
+TB_API int tb_to_image_stretch_u8_static(const float* src, int64_t images, int C, int H, int W, const float* mean,
+                                         const float* std, uint8_t* dst, tb_stream_t stream);
 
 /*
  * One pass over a logits matrix: top-1 and top-k correct counts and confusion-matrix bins.

@@ -45,6 +45,7 @@ SIGNATURES = {
                                       _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp]),
     "tb_channel_minmax": (_i32, [_vp, _i64, _i32, _i64, _vp, _vp]),
     "tb_to_image_u8": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp]),
+    "tb_to_image_stretch_u8_static": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "tb_metrics_update": (_i32, [_vp, _i32, _i64, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
     "tb_running_sum_update": (_i32, [_vp, _i32, _i64, _vp, _vp]),
     "tb_lmdb_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),

@@ -150,3 +150,55 @@ extern "C" int tb_to_image_u8(const float* src, int64_t images, int C, int H, in
     TB_LAUNCH_CHECK("tb_to_image_kernel");
     return TB_OK;
 }
+
+// ----------------------------------------------------------------------------------------------
+// The stretch without any allocation by anyone: the per-channel extrema live in a fixed array in
+// device memory that belongs to this library.
+// ----------------------------------------------------------------------------------------------
+namespace {
+
+static __device__ __align__(256) float g_stretch_extrema[TB_IMAGE_STATIC_MAX_CHANNELS * 2];
+
+// (min, max) slots back to the identities of min / max
+__global__ void tb_reset_extrema_kernel(float* minmax, int C) {
+    tb_grid_dependency_wait();
+    const int i = threadIdx.x;
+    if (i < 2 * C) minmax[i] = __int_as_float((i & 1) ? 0xff800000 : 0x7f800000);
+}
+
+constexpr int kMaxDevices = 64;
+float* g_extrema_addr[kMaxDevices];
+
+// Address of this device's copy of g_stretch_extrema, looked up once per device.
+int stretch_extrema(float** out) {
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_REQUIRE(dev >= 0 && dev < kMaxDevices, "tb_to_image_stretch_u8_static: device ordinal %d beyond %d", dev, kMaxDevices);
+    float* a = __atomic_load_n(&g_extrema_addr[dev], __ATOMIC_ACQUIRE);
+    if (!a) {
+        void* sym = nullptr;
+        TB_CUDA(cudaGetSymbolAddress(&sym, g_stretch_extrema));
+        a = (float*)sym;
+        __atomic_store_n(&g_extrema_addr[dev], a, __ATOMIC_RELEASE);       // racing first calls store the same address
+    }
+    *out = a;
+    return TB_OK;
+}
+
+}  // namespace
+
+extern "C" int tb_to_image_stretch_u8_static(const float* src, int64_t images, int C, int H, int W, const float* mean,
+                                             const float* std, uint8_t* dst, tb_stream_t stream) {
+    TB_REQUIRE(C >= 1 && C <= TB_IMAGE_STATIC_MAX_CHANNELS, "tb_to_image_stretch_u8_static: C=%d beyond the %d channels the fixed array holds",
+               C, TB_IMAGE_STATIC_MAX_CHANNELS);
+    TB_REQUIRE(images >= 0 && H >= 1 && W >= 1, "tb_to_image_stretch_u8_static: bad shape");
+    float* extrema = nullptr;
+    int rc = stretch_extrema(&extrema);
+    if (rc) return rc;
+    if (images == 0) return TB_OK;
+    tb_reset_extrema_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(extrema, C);
+    TB_LAUNCH_CHECK("tb_reset_extrema_kernel");
+    rc = tb_channel_minmax(src, images, C, (int64_t)H * W, extrema, stream);
+    if (rc) return rc;
+    return tb_to_image_u8(src, images, C, H, W, mean, std, TB_IMAGE_STRETCH, extrema, dst, stream);
+}
