@@ -89,6 +89,31 @@ def test_batch_loader_feeds_transform(tmp_path):
     assert torch.cat(ys).cpu().tolist() == [i % 7 for i in order]
 
 
+def test_batch_loader_runs_the_cifar_training_transform(tmp_path):
+    """resnet.py:96-110 end to end: LMDB records -> BatchLoader -> crop / flip / rotation / RandAugment /
+    normalise in one launch per batch, draws replayed from one seed across batches (the last one ragged)."""
+    from oracle import augment_oracle as AO
+    from torchbooster_b200.loader import BatchLoader
+    rng = np.random.default_rng(12)
+    n = 200
+    imgs = rng.integers(0, 256, (n, 32, 32, 3), dtype=np.uint8)
+    write_image_lmdb(str(tmp_path / "db"), imgs, labels=np.arange(n) % 10)
+    reader = LMDBReader(str(tmp_path / "db"))
+    spec = TransformSpec(crop=32, padding=4, padding_mode="reflect", flip_p=.5, rotation=15, rand_augment=True,
+                         mean=CIFAR[0], std=CIFAR[1])
+    order = rng.permutation(n)
+    loader = BatchLoader(reader, (32, 32, 3), batch_size=64, sampler=order.tolist(), labels=reader.read_labels(),
+                         transform=BatchTransform(spec, device="cuda", seed=77))
+    outs = [(x.clone(), y.clone()) for x, y in loader]
+    torch.cuda.synchronize()
+    assert [x.shape[0] for x, _ in outs] == [64, 64, 64, 8]
+    top, left, flip, ops = AO.draw_augment(77, n, 32, 32, 32, 32, 4, 0.5, 15)
+    want = TO.transform_batch(imgs[order], crop_top=top, crop_left=left, out_size=(32, 32), flip=flip, ops=ops, padding=4,
+                              padding_mode="reflect", mean=CIFAR[0], std=CIFAR[1])
+    assert torch.equal(torch.cat([x for x, _ in outs]).cpu(), want)
+    assert torch.cat([y for _, y in outs]).cpu().tolist() == [int(i) % 10 for i in order]
+
+
 def test_in_place_records_equal_gathered(tmp_path):
     """The registered-map route (kernel reads LMDB records where they lie) gives the same bits as
     the gather route, for the streaming kernel and the gather kernel."""

@@ -207,8 +207,9 @@ def to_image_case(name, B, H, W, mode, iters):
                       "frac_measured": gbs / PEAK}), flush=True)
 
 
-def loader_case(name, n_images, batch, threads, prefetch=2, in_place=False):
-    """LMDB (tmpfs) -> BatchLoader background gather into pinned slots -> zero-copy C2 transform."""
+def loader_case(name, n_images, batch, threads, prefetch=2, in_place=False, cifar_aug=False):
+    """LMDB (tmpfs) -> BatchLoader background gather into pinned slots -> zero-copy C2 transform
+    (cifar_aug: 32x32 records through the reference's whole CIFAR training transform instead)."""
     if CASE and CASE not in name:
         return
     import os
@@ -221,19 +222,23 @@ def loader_case(name, n_images, batch, threads, prefetch=2, in_place=False):
     root = tempfile.mkdtemp(dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
     try:
         rng = np.random.default_rng(0)
-        imgs = rng.integers(0, 256, (n_images, 256, 256, 3), dtype=np.uint8)
+        side = 32 if cifar_aug else 256
+        imgs = rng.integers(0, 256, (n_images, side, side, 3), dtype=np.uint8)
         t0 = time.perf_counter()
         write_image_lmdb(os.path.join(root, "db"), imgs, labels=np.arange(n_images) % 1000)
         t_write = time.perf_counter() - t0
         del imgs
         reader = LMDBReader(os.path.join(root, "db"))
         spec = TransformSpec(crop=224, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
+        if cifar_aug:
+            spec = TransformSpec(crop=32, padding=4, padding_mode="reflect", flip_p=.5, rotation=15, rand_augment=True,
+                                 mean=CIFAR[0], std=CIFAR[1])
         bt = BatchTransform(spec, device=dev, seed=1)
         labels = reader.read_labels()
         order = np.random.default_rng(1).permutation(n_images).tolist()
         best = None
         for _ in range(3):
-            loader = BatchLoader(reader, (256, 256, 3), batch, sampler=order, transform=bt, labels=labels, drop_last=True,
+            loader = BatchLoader(reader, (side, side, 3), batch, sampler=order, transform=bt, labels=labels, drop_last=True,
                                  prefetch=prefetch, threads=threads, in_place=in_place)
             torch.cuda.synchronize()
             t0 = time.perf_counter()
@@ -244,7 +249,7 @@ def loader_case(name, n_images, batch, threads, prefetch=2, in_place=False):
             dt = time.perf_counter() - t0
             best = dt if best is None else min(best, dt)
         print(json.dumps({"case": name, "images": cnt, "batch": batch, "threads": threads, "images_per_s": cnt / best,
-                          "host_gather_GBps": cnt * 196608 / best / 1e9, "lmdb_write_s": t_write}), flush=True)
+                          "host_gather_GBps": cnt * side * side * 3 / best / 1e9, "lmdb_write_s": t_write}), flush=True)
     finally:
         shutil.rmtree(root, ignore_errors=True)
 
@@ -305,6 +310,8 @@ def main():
         for th in (8, 16):
             loader_case(f"loader_c2_threads{th}", 4096, 512, th)
         loader_case("loader_c2_in_place", 4096, 512, 8, in_place=True)
+        loader_case("loader_cifar_aug_b256", 50000, 256, 8, cifar_aug=True)
+        loader_case("loader_cifar_aug_b2048", 50000, 2048, 8, cifar_aug=True)
     if want("rrc"):
         rrc_case("rrc_c2_b512", 512, 100)
         rrc_case("rrc_c2_b2048", 2048, 30)
