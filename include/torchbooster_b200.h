@@ -199,8 +199,10 @@ TB_API int tb_resized_crop_bilinear_u8_nhwc_to_nchw(
  * ImageEnhance / ImageOps); every operation reproduces Pillow's result bit for bit.
  *   ops : DEVICE int32 [B][n_ops][8], records of TB_AUG_* (torchbooster_b200/augment.py encodes
  *         (name, magnitude) pairs); unknown codes are skipped.  Fill is 0, expand is False.
- * C in {1,3}; 2 * C * out_h * out_w bytes (+ table) must fit in shared memory (TB_ENOTSUP
- * otherwise; up to about 190 x 190 RGB).
+ * C in {1,3}.  Images larger than about 24 KB are owned by a thread-block cluster of 2, 4 or 8
+ * CTAs (distributed shared memory); 2 * C * out_h * out_w bytes must fit in the shared memory of 8
+ * SMs and C * out_h * out_w < 2^20 (TB_ENOTSUP otherwise; 512 x 512 RGB fits).
+ * flags: bits 8-11 force a cluster size (development knob).
  */
 TB_API int tb_augment_u8_nhwc_to_nchw(
     const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride, int64_t src_row_pitch,

@@ -119,6 +119,54 @@ def test_full_cifar_batches_replayed_vs_torchvision():
         assert same(got, want), step
 
 
+ALL_OPS = [("Rotate", 21.0), ("Sharpness", -0.63), ("Equalize", 0.0), ("ShearX", -0.21), ("Contrast", 0.45), ("AutoContrast", 0.0),
+           ("TranslateY", 31.0), ("Color", -0.9), ("Solarize", 102.0), ("ShearY", 0.3), ("Brightness", 0.27), ("Posterize", 5.0),
+           ("TranslateX", -17.0), ("Invert", 0.0), ("RandomRotation", -163.5), ("Identity", 0.0)]
+
+
+@pytest.mark.parametrize("H,W,C,crop,dtype", [(256, 256, 3, 224, torch.bfloat16),       # ImageNet crop: cluster of 2
+                                              (256, 256, 3, None, torch.float32),      # online.py's size: cluster of 2
+                                              (300, 333, 1, (299, 331), torch.float32),  # grey, odd sizes: cluster of 1
+                                              (512, 512, 3, None, torch.float16)])     # cluster of 8
+def test_images_owned_by_a_cluster(H, W, C, crop, dtype):
+    """Images that do not fit in one SM's shared memory twice are spread over a thread-block cluster
+    (distributed shared memory); every operation, chained, against torchvision."""
+    rng = np.random.default_rng(H + W)
+    B = 5
+    batch = rng.integers(0, 256, (B, H, W, C), dtype=np.uint8)
+    batch[1] = (batch[1] // 3 + 50).astype(np.uint8)
+    th, tw = (H, W) if crop is None else ((crop, crop) if np.isscalar(crop) else crop)
+    top = rng.integers(0, H - th + 1, B).astype(np.int32)
+    left = rng.integers(0, W - tw + 1, B).astype(np.int32)
+    flip = rng.integers(0, 2, B).astype(np.uint8)
+    ops = [[ALL_OPS[(3 * b + j) % len(ALL_OPS)] for j in range(4)] for b in range(B)]
+    ops[4] = ALL_OPS[12:16] + ALL_OPS[0:3]
+    spec = TransformSpec(crop=None if crop is None else (th, tw), flip_p=0.5, rand_augment=True, mean=CIFAR[0][:C], std=CIFAR[1][:C],
+                         dtype=dtype)
+    got = BatchTransform(spec, device="cuda")(torch.from_numpy(batch).cuda(), params=(top, left, flip, ops))
+    want = TO.transform_batch(batch, crop_top=top, crop_left=left, out_size=(th, tw), flip=flip, ops=ops, mean=CIFAR[0][:C],
+                              std=CIFAR[1][:C], dtype=dtype)
+    assert same(got, want)
+
+
+@pytest.mark.parametrize("cluster", [2, 4, 8])
+def test_forced_cluster_sizes_on_small_images(cluster):
+    """The development knob (flags bits 8-11) runs small images through the cluster path: odd chunk
+    boundaries, every operation, scalar and vector store paths."""
+    rng = np.random.default_rng(cluster)
+    for (H, W, C) in ((32, 32, 3), (19, 23, 3), (28, 28, 1), (5, 7, 3)):
+        B = 9
+        batch = rng.integers(0, 256, (B, H, W, C), dtype=np.uint8)
+        flip = rng.integers(0, 2, B).astype(np.uint8)
+        ops = [[ALL_OPS[(5 * b + j) % len(ALL_OPS)] for j in range(5)] for b in range(B)]
+        spec = TransformSpec(flip_p=0.5, rand_augment=True, mean=CIFAR[0][:C], std=CIFAR[1][:C])
+        bt = BatchTransform(spec, device="cuda")
+        bt.flags = cluster << 8
+        got = bt(torch.from_numpy(batch).cuda(), params=(None, None, flip, ops))
+        want = TO.transform_batch(batch, flip=flip, ops=ops, mean=CIFAR[0][:C], std=CIFAR[1][:C])
+        assert same(got, want), (H, W, C)
+
+
 def test_mnist_rand_augment_replayed():
     """lenet.py:95: T.Compose([T.RandAugment(), T.ToTensor()]) on 28x28 grey images -- no crop, flip or
     rotation in the pipeline, so only RandAugment draws; two batches from one seed."""
@@ -144,7 +192,7 @@ def test_larger_images_and_limits():
     got = BatchTransform(spec, device="cuda")(torch.from_numpy(batch).cuda(), params=(None, None, None, ops))
     assert same(got, TO.transform_batch(batch, ops=ops, mean=CIFAR[0], std=CIFAR[1]))
     with pytest.raises(NotImplementedError, match="shared memory"):
-        BatchTransform(spec, device="cuda")(torch.zeros((1, 224, 224, 3), dtype=torch.uint8, device="cuda"),
+        BatchTransform(spec, device="cuda")(torch.zeros((1, 600, 600, 3), dtype=torch.uint8, device="cuda"),
                                             params=(None, None, None, [[("Invert", 0.0)]]))
     with pytest.raises(ValueError, match="not in"):
         BatchTransform(TransformSpec(rand_augment=True), device="cuda")(

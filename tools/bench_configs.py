@@ -145,6 +145,26 @@ def rrc_case(name, B, iters, flags=0):
                       "frac_measured": gbs / PEAK, "alg_bytes_per_image": alg / B}), flush=True)
 
 
+def augment_imagenet_case(name, B, iters, flags=0):
+    """RandomCrop(224) of 256x256 + flip + RandAugment() + normalise -> bf16: each image is owned by a
+    cluster of 2 CTAs (distributed shared memory)."""
+    if CASE and CASE not in name:
+        return
+    dev = torch.device("cuda", 0)
+    spec = TransformSpec(crop=224, flip_p=.5, rand_augment=True, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
+    bt = BatchTransform(spec, device=dev, seed=42)
+    bt.flags = flags
+    nbuf = 6
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    srcs = [torch.randint(0, 256, (B, 256, 256, 3), dtype=torch.uint8, device=dev, generator=gen) for _ in range(nbuf)]
+    prm = tuple(torch.from_numpy(a).to(dev) for a in bt.draw_params(B, 256, 256))
+    out = [torch.empty((B, 3, 224, 224), dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    ms = time_loop(lambda i: bt(srcs[i % nbuf], params=prm, out=out[i & 1]), iters)
+    gbs = 224 * 224 * 9 * B / (ms * 1e-3) / 1e9
+    print(json.dumps({"case": name, "B": B, "ms": ms, "images_per_s": B / (ms * 1e-3), "alg_GBps": gbs,
+                      "frac_measured": gbs / PEAK}), flush=True)
+
+
 def augment_case(name, B, iters, host_params=False):
     """The reference's CIFAR training transform (resnet.py:96-103): RandomCrop(32, 4, reflect), flip,
     RandomRotation(15), RandAugment(), normalise -> fp32; records pre-encoded on the device
@@ -322,6 +342,9 @@ def main():
     if want("aug"):
         for bsz in (256, 2048, 16384):
             augment_case(f"aug_cifar_b{bsz}", bsz, 200 if bsz < 10000 else 50)
+        augment_imagenet_case("aug_imagenet224_b512", 512, 30)
+        for cl in (2, 4, 8):
+            augment_imagenet_case(f"aug_imagenet224_b512_cluster{cl}", 512, 30, flags=cl << 8)
         augment_case("aug_cifar_b256_host_params", 256, 100, host_params=True)
         augment_case("aug_cifar_b2048_host_params", 2048, 30, host_params=True)
     if want("image"):

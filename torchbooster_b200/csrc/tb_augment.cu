@@ -9,7 +9,11 @@
 // into shared memory (planar, the layout of the output), every operation of that sample's list
 // runs out of shared memory (two buffers, ping-pong for the operations that move pixels), and
 // the result leaves through the per-channel table as coalesced planar stores.  Global traffic is
-// the algorithmic minimum: source bytes in, output elements out.
+// the algorithmic minimum: source bytes in, output elements out.  An image too large for one SM
+// (ImageNet-sized crops) is owned by a thread-block CLUSTER of 2, 4 or 8 CTAs instead: the two
+// buffers are cut into equal chunks across the cluster's shared memories and every thread reaches
+// any pixel through distributed shared memory; histograms and sums are kept per CTA and added up
+// by each CTA from its peers.
 //
 // The arithmetic of each operation is Pillow 12's, bit for bit (oracle/augment_oracle.py):
 //   AFFINE        nearest neighbour in 16.16 fixed point (Geometry.c affine_fixed): rotations,
@@ -20,11 +24,16 @@
 //                 (19595 R + 38470 G + 7471 B + 0x8000) >> 16 / grey mean / 3x3 SMOOTH
 //   POSTERIZE, SOLARIZE, INVERT   byte maps
 //   AUTOCONTRAST, EQUALIZE        per-band histogram -> table (ImageOps), float64 where Python is
+#include <cooperative_groups.h>
+
 #include "tb_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
 constexpr int kAugThreads = 256;      // == histogram bins: thread t owns bin t
+constexpr int kAugChunk = 24 * 1024;
 
 struct AugParams {
     const uint8_t* src;
@@ -40,7 +49,8 @@ struct AugParams {
     int n_ops;
     const void* lut;
     int plane;          // out_h * out_w
-    int buf_bytes;      // C * plane rounded up to 16
+    int buf_bytes;      // bytes of one image buffer held by one CTA (multiple of 16): the whole image, or its chunk
+    uint64_t magic;     // ceil(2^40 / buf_bytes) (cluster launches)
 };
 
 __device__ __forceinline__ int aug_fold(int i, int n, int mode, bool& inside) {
@@ -67,23 +77,85 @@ __device__ __forceinline__ uint8_t aug_blend(int deg, int v, float alpha) {
     return t <= 0.0f ? 0 : (t >= 255.0f ? 255 : (uint8_t)(int)t);
 }
 
+// channel of planar element i (C <= 3; elements past the image count as the last channel)
+__device__ __forceinline__ int aug_channel(int i, int plane) { return (i >= plane) + (i >= 2 * plane); }
+
 __device__ __forceinline__ int aug_grey(int r, int g, int b) { return (r * 19595 + g * 38470 + b * 7471 + 0x8000) >> 16; }
 
-template <typename T>
+// A planar image buffer in shared memory: whole in this CTA (CL = false), or -- for images that do
+// not fit in one SM's shared memory twice -- cut into equal chunks over the CTAs of a thread-block
+// cluster and reached through distributed shared memory (CL = true): element i lives in CTA
+// i / chunk of the cluster at the same local offset in every CTA.
+template <bool CL>
+struct AugBuf;
+template <>
+struct AugBuf<false> {
+    uint8_t* base;
+    __device__ __forceinline__ int ld(int i) const { return base[i]; }
+    __device__ __forceinline__ void st(int i, uint8_t v) const { base[i] = v; }
+    __device__ __forceinline__ uint32_t* word(int i) const { return (uint32_t*)(base + i); }     // i % 4 == 0
+};
+template <>
+struct AugBuf<true> {
+    uint8_t* base;
+    uint32_t chunk;
+    uint64_t magic;     // ceil(2^40 / chunk): i / chunk == (i * magic) >> 40 for every i < 2^20
+    __device__ __forceinline__ uint8_t* at(int i) const {
+        const uint32_t r = (uint32_t)(((uint64_t)(uint32_t)i * magic) >> 40);
+        return cg::this_cluster().map_shared_rank(base, r) + ((uint32_t)i - r * chunk);
+    }
+    __device__ __forceinline__ int ld(int i) const { return *at(i); }
+    __device__ __forceinline__ void st(int i, uint8_t v) const { *at(i) = v; }
+    __device__ __forceinline__ uint32_t* word(int i) const { return (uint32_t*)at(i); }     // chunks are multiples of 16
+};
+
+// Byte-wise map over a buffer, four bytes per access (the padding bytes after the image ride along).
+template <bool CL, typename F>
+__device__ __forceinline__ void aug_map(const AugBuf<CL>& buf, int total, int gt, int gn, F f) {
+    for (int i = gt * 4; i < total; i += gn * 4) {
+        uint32_t* w = buf.word(i);
+        const uint32_t v = *w;
+        *w = (uint32_t)f(i, (int)(v & 0xffu)) | ((uint32_t)f(i + 1, (int)((v >> 8) & 0xffu)) << 8) |
+             ((uint32_t)f(i + 2, (int)((v >> 16) & 0xffu)) << 16) | ((uint32_t)f(i + 3, (int)(v >> 24)) << 24);
+    }
+}
+
+template <bool CL>
+__device__ __forceinline__ void aug_sync() {
+    if constexpr (CL) cg::this_cluster().sync();
+    else __syncthreads();
+}
+// value of a per-CTA shared variable in CTA r of the cluster
+template <bool CL>
+__device__ __forceinline__ int aug_peer(int* var, int r) {
+    if constexpr (CL) return *cg::this_cluster().map_shared_rank(var, r);
+    else return *var;
+}
+
+template <typename T, bool CL>
 __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int s_hist[3 * 256];
+    __shared__ int s_hist[3 * 256];     // this CTA's share of the histogram
+    __shared__ int s_full[3 * 256];     // the image's histogram
     __shared__ uint8_t s_tab[3 * 256];
     __shared__ int s_lo[3], s_hi[3], s_sum, s_warp[kAugThreads / 32];
     __shared__ int32_t s_ops[TB_AUG_MAX_OPS * 8];
 
-    uint8_t* cur = smem;
-    uint8_t* alt = smem + p.buf_bytes;
+    const int S = CL ? (int)cg::this_cluster().num_blocks() : 1;        // CTAs that share the image
+    const int rank = CL ? (int)cg::this_cluster().block_rank() : 0;
+    AugBuf<CL> cur, alt;
+    cur.base = smem;
+    alt.base = smem + p.buf_bytes;
+    if constexpr (CL) {
+        cur.chunk = alt.chunk = (uint32_t)p.buf_bytes;
+        cur.magic = alt.magic = p.magic;
+    }
     T* s_lut = (T*)(smem + 2 * p.buf_bytes);
 
     tb_grid_dependency_wait();
     const int tid = threadIdx.x;
-    const int b = blockIdx.x;
+    const int b = blockIdx.x / S;
+    const int gt = rank * kAugThreads + tid, gn = S * kAugThreads;      // this thread among the image's threads
     const int C = p.C, plane = p.plane, W = p.out_w, H = p.out_h;
     const int total = C * plane;
 
@@ -92,23 +164,24 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
         for (int i = tid; i < C * 256; i += kAugThreads) s_lut[i] = glut[i];
         if (tid < p.n_ops * 8) s_ops[tid] = p.ops[(int64_t)b * p.n_ops * 8 + tid];      // one round trip for the whole list
     }
+    if constexpr (CL) cg::this_cluster().sync();        // every CTA of the cluster is resident before its memory is written
     // ---- gather: pad / crop / flip, interleaved source -> planar shared --------------------
     {
         const int top = (p.top ? p.top[b] : 0) - p.pad_y;
         const int left = (p.left ? p.left[b] : 0) - p.pad_x;
         const bool flip = p.flip ? (p.flip[b] != 0) : false;
         const uint8_t* __restrict__ img = p.src + (int64_t)b * p.bs;
-        for (int q = tid; q < plane; q += kAugThreads) {
+        for (int q = gt; q < plane; q += gn) {
             const int y = q / W, x = q - y * W;
             const int xs = flip ? W - 1 - x : x;
             bool inside = true;
             const int u = aug_fold(top + y, p.H, p.pad_mode, inside);
             const int v = aug_fold(left + xs, p.W, p.pad_mode, inside);
             const uint8_t* __restrict__ s = img + (int64_t)u * p.pitch + (int64_t)v * C;
-            for (int c = 0; c < C; ++c) cur[c * plane + q] = inside ? s[c] : (uint8_t)0;
+            for (int c = 0; c < C; ++c) cur.st(c * plane + q, inside ? s[c] : (uint8_t)0);
         }
     }
-    __syncthreads();
+    aug_sync<CL>();
 
     // ---- the sample's operations ------------------------------------------------------------
     const int32_t* rec = s_ops;
@@ -119,92 +192,101 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
         switch (kind) {
         case TB_AUG_AFFINE: {
             const uint32_t a0 = rec[1], a1 = rec[2], a2 = rec[3], a3 = rec[4], a4 = rec[5], a5 = rec[6];
-            for (int q = tid; q < plane; q += kAugThreads) {
+            for (int q = gt; q < plane; q += gn) {
                 const int y = q / W, x = q - y * W;
                 const int xin = (int)(a2 + (uint32_t)x * a0 + (uint32_t)y * a1) >> 16;
                 const int yin = (int)(a5 + (uint32_t)x * a3 + (uint32_t)y * a4) >> 16;
                 const bool ok = (unsigned)xin < (unsigned)W && (unsigned)yin < (unsigned)H;
                 const int s = ok ? yin * W + xin : 0;
-                for (int c = 0; c < C; ++c) alt[c * plane + q] = ok ? cur[c * plane + s] : (uint8_t)0;
+                for (int c = 0; c < C; ++c) alt.st(c * plane + q, ok ? (uint8_t)cur.ld(c * plane + s) : (uint8_t)0);
             }
-            uint8_t* t = cur; cur = alt; alt = t;
+            const AugBuf<CL> t = cur; cur = alt; alt = t;
             break;
         }
         case TB_AUG_BRIGHTNESS:
-            for (int i = tid; i < total; i += kAugThreads) cur[i] = aug_blend(0, cur[i], alpha);
+            aug_map<CL>(cur, total, gt, gn, [=](int, int v) { return aug_blend(0, v, alpha); });
             break;
         case TB_AUG_COLOR:
             if (C == 3)
-                for (int q = tid; q < plane; q += kAugThreads) {
-                    const int r = cur[q], g = cur[plane + q], bl = cur[2 * plane + q];
+                for (int q = gt; q < plane; q += gn) {
+                    const int r = cur.ld(q), g = cur.ld(plane + q), bl = cur.ld(2 * plane + q);
                     const int l = aug_grey(r, g, bl);
-                    cur[q] = aug_blend(l, r, alpha);
-                    cur[plane + q] = aug_blend(l, g, alpha);
-                    cur[2 * plane + q] = aug_blend(l, bl, alpha);
+                    cur.st(q, aug_blend(l, r, alpha));
+                    cur.st(plane + q, aug_blend(l, g, alpha));
+                    cur.st(2 * plane + q, aug_blend(l, bl, alpha));
                 }
             break;
         case TB_AUG_CONTRAST: {
             if (tid == 0) s_sum = 0;
             __syncthreads();
             int part = 0;
-            for (int q = tid; q < plane; q += kAugThreads)
-                part += C == 3 ? aug_grey(cur[q], cur[plane + q], cur[2 * plane + q]) : (int)cur[q];
+            for (int q = gt; q < plane; q += gn)
+                part += C == 3 ? aug_grey(cur.ld(q), cur.ld(plane + q), cur.ld(2 * plane + q)) : cur.ld(q);
             part = __reduce_add_sync(0xffffffffu, part);
             if ((tid & 31) == 0) atomicAdd(&s_sum, part);
-            __syncthreads();
+            aug_sync<CL>();
+            int sum = 0;
+            for (int r = 0; r < S; ++r) sum += aug_peer<CL>(&s_sum, r);
             // int(sum / count + 0.5), Python float64
-            const int mean = (int)__dadd_rn(__ddiv_rn((double)s_sum, (double)plane), 0.5);
-            for (int i = tid; i < total; i += kAugThreads) cur[i] = aug_blend(mean, cur[i], alpha);
+            const int mean = (int)__dadd_rn(__ddiv_rn((double)sum, (double)plane), 0.5);
+            aug_map<CL>(cur, total, gt, gn, [=](int, int v) { return aug_blend(mean, v, alpha); });
             break;
         }
         case TB_AUG_SHARPNESS: {
             const float k1 = __fdiv_rn(1.0f, 13.0f), k5 = __fdiv_rn(5.0f, 13.0f);
-            for (int q = tid; q < plane; q += kAugThreads) {
+            for (int q = gt; q < plane; q += gn) {
                 const int y = q / W, x = q - y * W;
                 const bool interior = x >= 1 && x < W - 1 && y >= 1 && y < H - 1;
                 for (int c = 0; c < C; ++c) {
-                    const uint8_t* __restrict__ im = cur + c * plane + q;
-                    const int v = im[0];
+                    const int at = c * plane + q;
+                    const int v = cur.ld(at);
                     int deg = v;
                     if (interior) {
                         float ss = 0.5f;
 #pragma unroll
                         for (int dy = 1; dy >= -1; --dy) {
-                            const uint8_t* __restrict__ row = im + dy * W;
+                            const int row = at + dy * W;
                             const float mid = dy == 0 ? k5 : k1;
-                            const float part = __fadd_rn(__fadd_rn(__fmul_rn((float)row[-1], k1), __fmul_rn((float)row[0], mid)),
-                                                         __fmul_rn((float)row[1], k1));
+                            const float part = __fadd_rn(__fadd_rn(__fmul_rn((float)cur.ld(row - 1), k1),
+                                                                   __fmul_rn((float)(dy == 0 ? v : cur.ld(row)), mid)),
+                                                         __fmul_rn((float)cur.ld(row + 1), k1));
                             ss = __fadd_rn(ss, part);
                         }
                         deg = ss <= 0.0f ? 0 : (ss >= 255.0f ? 255 : (int)ss);
                     }
-                    alt[c * plane + q] = aug_blend(deg, v, alpha);
+                    alt.st(at, aug_blend(deg, v, alpha));
                 }
             }
-            uint8_t* t = cur; cur = alt; alt = t;
+            const AugBuf<CL> t = cur; cur = alt; alt = t;
             break;
         }
         case TB_AUG_POSTERIZE:
-            for (int i = tid; i < total; i += kAugThreads) cur[i] = cur[i] & (uint8_t)r1;
+            aug_map<CL>(cur, total, gt, gn, [=](int, int v) { return (uint8_t)(v & r1); });
             break;
         case TB_AUG_SOLARIZE:
-            for (int i = tid; i < total; i += kAugThreads) {
-                const int v = cur[i];
-                cur[i] = (uint8_t)(v < r1 ? v : 255 - v);
-            }
+            aug_map<CL>(cur, total, gt, gn, [=](int, int v) { return (uint8_t)(v < r1 ? v : 255 - v); });
             break;
         case TB_AUG_INVERT:
-            for (int i = tid; i < total; i += kAugThreads) cur[i] = (uint8_t)(255 - cur[i]);
+            aug_map<CL>(cur, total, gt, gn, [=](int, int v) { return (uint8_t)(255 - v); });
             break;
         case TB_AUG_AUTOCONTRAST:
         case TB_AUG_EQUALIZE: {
             for (int i = tid; i < C * 256; i += kAugThreads) s_hist[i] = 0;
             if (tid < 3) { s_lo[tid] = 256; s_hi[tid] = -1; }
             __syncthreads();
-            for (int i = tid; i < total; i += kAugThreads) atomicAdd(&s_hist[(i / plane) * 256 + cur[i]], 1);
-            __syncthreads();
-            for (int c = 0; c < C; ++c)
-                if (s_hist[c * 256 + tid]) { atomicMin(&s_lo[c], tid); atomicMax(&s_hi[c], tid); }
+            for (int i = gt * 4; i < total; i += gn * 4) {
+                const uint32_t v = *cur.word(i);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (i + k < total) atomicAdd(&s_hist[aug_channel(i + k, plane) * 256 + ((v >> (8 * k)) & 0xffu)], 1);
+            }
+            aug_sync<CL>();
+            for (int c = 0; c < C; ++c) {       // every CTA adds the shares up for itself
+                int n = 0;
+                for (int r = 0; r < S; ++r) n += aug_peer<CL>(&s_hist[c * 256 + tid], r);
+                s_full[c * 256 + tid] = n;
+                if (n) { atomicMin(&s_lo[c], tid); atomicMax(&s_hi[c], tid); }
+            }
             __syncthreads();
             for (int c = 0; c < C; ++c) {
                 const int lo = s_lo[c], hi = s_hi[c];
@@ -220,7 +302,7 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
                 } else {
                     // ImageOps.equalize: step = (pixels - last non-empty bin) // 255;
                     // table[i] = (step // 2 + sum of bins below i) // step
-                    const int h = s_hist[c * 256 + tid];
+                    const int h = s_full[c * 256 + tid];
                     int incl = h;
 #pragma unroll
                     for (int d = 1; d < 32; d <<= 1) {
@@ -232,7 +314,7 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
                     __syncthreads();
                     int below = incl - h;
                     for (int w = 0; w < (tid >> 5); ++w) below += s_warp[w];
-                    const int step = hi > lo ? (plane - s_hist[c * 256 + hi]) / 255 : 0;
+                    const int step = hi > lo ? (plane - s_full[c * 256 + hi]) / 255 : 0;
                     if (step > 0) {
                         const int n = (step / 2 + below) / step;
                         entry = n > 255 ? 255 : n;
@@ -241,13 +323,13 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
                 s_tab[c * 256 + tid] = (uint8_t)entry;
             }
             __syncthreads();
-            for (int i = tid; i < total; i += kAugThreads) cur[i] = s_tab[(i / plane) * 256 + cur[i]];
+            aug_map<CL>(cur, total, gt, gn, [&](int i, int v) { return s_tab[aug_channel(i, plane) * 256 + v]; });
             break;
         }
         default:        // TB_AUG_IDENTITY and unknown codes
             break;
         }
-        __syncthreads();
+        aug_sync<CL>();     // also keeps s_sum / s_hist alive until every CTA of the cluster has read them
     }
 
     // ---- table lookup, cast, planar store ---------------------------------------------------
@@ -256,22 +338,44 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
     if (sizeof(T) == 4 ? ((total & 3) == 0 && (((uintptr_t)p.dst) & 15) == 0)
                        : ((total & 7) == 0 && (((uintptr_t)p.dst) & 15) == 0)) {
         constexpr int PX = 16 / sizeof(T);
-        for (int i = tid * PX; i < total; i += kAugThreads * PX) {
+        for (int i = gt * PX; i < total; i += gn * PX) {
             __align__(16) T v[PX];
 #pragma unroll
-            for (int k = 0; k < PX; ++k) v[k] = s_lut[((i + k) / plane) * 256 + cur[i + k]];
+            for (int k = 0; k < PX; k += 4) {
+                const uint32_t w = *cur.word(i + k);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[k + j] = s_lut[aug_channel(i + k + j, plane) * 256 + ((w >> (8 * j)) & 0xffu)];
+            }
             tb_st_cs_v4(d + i, *(const uint4*)v);
         }
     } else {
-        for (int i = tid; i < total; i += kAugThreads) d[i] = s_lut[(i / plane) * 256 + cur[i]];
+        for (int i = gt; i < total; i += gn) d[i] = s_lut[aug_channel(i, plane) * 256 + cur.ld(i)];
     }
+    if constexpr (CL) cg::this_cluster().sync();        // no CTA leaves while its memory may still be read
 }
 
 template <typename T>
-int launch_augment(const AugParams& p, size_t smem, cudaStream_t s) {
-    if (smem > 48 * 1024)
-        TB_CUDA(cudaFuncSetAttribute(tb_augment_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    tb_augment_kernel<T><<<p.B, kAugThreads, smem, s>>>(p);
+int launch_augment(const AugParams& p, int cluster, size_t smem, cudaStream_t s) {
+    if (cluster == 1) {
+        if (smem > 48 * 1024)
+            TB_CUDA(cudaFuncSetAttribute(tb_augment_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        tb_augment_kernel<T, false><<<p.B, kAugThreads, smem, s>>>(p);
+    } else {
+        TB_CUDA(cudaFuncSetAttribute(tb_augment_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)p.B * cluster);
+        cfg.blockDim = dim3(kAugThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)cluster;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        TB_CUDA(cudaLaunchKernelEx(&cfg, tb_augment_kernel<T, true>, p));
+    }
     TB_LAUNCH_CHECK("tb_augment_kernel");
     return TB_OK;
 }
@@ -283,7 +387,6 @@ extern "C" int tb_augment_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int 
                                           const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
                                           int pad_y, int pad_x, int pad_mode, const int32_t* ops, int n_ops,
                                           const void* lut, int flags, tb_stream_t stream) {
-    (void)flags;
     TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_augment: bad source shape B=%d H=%d W=%d", B, H, W);
     TB_REQUIRE(C == 1 || C == 3, "tb_augment: C=%d not in {1,3} (PIL modes L and RGB)", C);
     TB_REQUIRE(out_h >= 1 && out_w >= 1, "tb_augment: bad output size %dx%d", out_h, out_w);
@@ -312,14 +415,31 @@ extern "C" int tb_augment_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int 
     p.dst = dst; p.out_h = out_h; p.out_w = out_w; p.top = crop_top; p.left = crop_left; p.flip = flip;
     p.pad_y = pad_y; p.pad_x = pad_x; p.pad_mode = pad_mode; p.ops = ops; p.n_ops = n_ops; p.lut = lut;
     const int64_t plane = (int64_t)out_h * out_w;
-    const int64_t buf = (plane * C + 15) & ~(int64_t)15;
-    const int64_t smem = 2 * buf + (int64_t)C * 256 * tb_dtype_size(dst_dtype);
-    // the image lives in shared memory, twice (operations that move pixels write the other copy)
-    if (smem + 8 * 1024 > dev.max_smem_optin)
-        return tb_fail(TB_ENOTSUP, "tb_augment: a %dx%dx%d image does not fit in shared memory twice (%lld of %d bytes)",
-                       out_h, out_w, C, (long long)smem, dev.max_smem_optin - 8 * 1024);
+    // The image lives in shared memory, twice (operations that move pixels write the other copy):
+    // in one CTA when it fits, else spread over a cluster of 2, 4 or 8 CTAs (distributed shared memory).
+    const int64_t reserve = 10 * 1024;      // static shared memory of the kernel + the system's share
+    int cluster = (flags >> 8) & 0xf;       // development knob: force a cluster size
+    int64_t buf = 0, smem = 0;
+    // Small chunks win: shared memory per CTA decides how many warps an SM holds (224 x 224 RGB:
+    // 2 CTAs of 150 KB = 8 warps per SM, 8 CTAs of 38 KB = 40), so an image takes the smallest
+    // cluster whose chunks are at most kAugChunk bytes, or 8 CTAs.
+    const bool forced = cluster != 0;
+    for (int c = forced ? cluster : 1; c <= 8; c *= 2) {
+        buf = (((plane * C + c - 1) / c) + 15) & ~(int64_t)15;
+        smem = 2 * buf + (int64_t)C * 256 * tb_dtype_size(dst_dtype);
+        const bool fits = smem + reserve <= dev.max_smem_optin;
+        if (forced) { if (!fits) cluster = 0; break; }
+        if (fits && (c == 8 || buf <= kAugChunk)) { cluster = c; break; }
+    }
+    if (cluster == 0 || smem + reserve > dev.max_smem_optin || plane * C >= ((int64_t)1 << 20))
+        return tb_fail(TB_ENOTSUP, "tb_augment: a %dx%dx%d image does not fit twice in the shared memory of a cluster of 8 SMs",
+                       out_h, out_w, C);
+    TB_REQUIRE(cluster == 1 || cluster == 2 || cluster == 4 || cluster == 8, "tb_augment: cluster size %d", cluster);
+    TB_REQUIRE((int64_t)B * cluster < ((int64_t)1 << 31), "tb_augment: grid too large");
     p.plane = (int)plane;
     p.buf_bytes = (int)buf;
+    p.magic = ((((uint64_t)1) << 40) + (uint64_t)buf - 1) / (uint64_t)buf;
     cudaStream_t s = (cudaStream_t)stream;
-    return dst_dtype == TB_F32 ? launch_augment<float>(p, (size_t)smem, s) : launch_augment<uint16_t>(p, (size_t)smem, s);
+    return dst_dtype == TB_F32 ? launch_augment<float>(p, cluster, (size_t)smem, s)
+                               : launch_augment<uint16_t>(p, cluster, (size_t)smem, s);
 }
