@@ -34,6 +34,7 @@ extern "C" {
 #define TB_F32  0
 #define TB_BF16 1
 #define TB_F16  2
+#define TB_U8   3   /* tb_resized_crop_bilinear_u8_nhwc_to_nchw only: bytes out (lut = uint8 [C][256]), the hand-off to tb_augment */
 
 /* padding modes of torchvision F.pad (torchvision/transforms/_functional_pil.py:147-223) */
 #define TB_PAD_NONE      0  /* no padding declared; reads outside the image still give 0 */
@@ -72,6 +73,7 @@ extern "C" {
 #define TB_FLAG_FORCE_GENERIC 1  /* tests: skip the streaming path, use the one-gather-per-pixel kernel */
 #define TB_FLAG_FORCE_STREAM  2  /* tests: take the streaming path even where the gather kernel is the better launch */
 #define TB_FLAG_NO_PDL        4  /* launch without programmatic stream serialization */
+#define TB_FLAG_SRC_PLANAR    8  /* tb_augment: the source is uint8 [B][C][H][W] (src_row_pitch = bytes per row of one plane) */
 
 typedef struct CUstream_st* tb_stream_t;   /* == cudaStream_t */
 
@@ -210,6 +212,17 @@ TB_API int tb_augment_u8_nhwc_to_nchw(
     const int32_t* crop_top, const int32_t* crop_left, const uint8_t* flip,
     int pad_y, int pad_x, int pad_mode, const int32_t* ops, int n_ops,
     const void* lut, int flags, tb_stream_t stream);
+
+/*
+ * Nearest-neighbour affine of whole uint8 images, NHWC -> NHWC (dense), one TB_AUG_AFFINE /
+ * TB_AUG_IDENTITY record per sample (records[b][8], as in tb_augment): T.RandomRotation at the HEAD
+ * of a pipeline, before a resized crop (examples/img_stt/online/online.py:173:
+ * T.RandomRotation(180), T.RandomResizedCrop(size), T.RandAugment()), where the image is too large
+ * to live in shared memory.  Pillow's 16.16 fixed-point rule, outside = 0.  C in [1,4].
+ */
+TB_API int tb_affine_nearest_u8_nhwc(
+    const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride, int64_t src_row_pitch,
+    const int32_t* records, uint8_t* dst, tb_stream_t stream);
 
 /*
  * Host helpers of tb_augment (no GPU work).  tb_augment_rotation_records: angles (degrees) ->

@@ -34,6 +34,7 @@ def transform_sample(
     resized_crop: Optional[Sequence[int]] = None,   # (top, left, h, w, out_h, out_w): T.RandomResizedCrop.forward
     flip: bool = False,
     ops=None,                                       # [(name, magnitude)]: RandomRotation / RandAugment operations
+    pre_ops=None,                                   # the same, applied to the source image first (online.py:173)
     mean=None,
     std=None,
     one_minus: bool = False,
@@ -49,6 +50,9 @@ def transform_sample(
     (``_functional_tensor.py:905-928``).
     """
     pil = _to_pil(img)
+    if pre_ops:
+        from .augment_oracle import apply_ops_pil
+        pil = apply_ops_pil(pil, pre_ops)
     if resize is not None:
         pil = F.resize(pil, resize)
     if center_crop is not None:
@@ -74,7 +78,7 @@ def transform_sample(
 
 
 def transform_batch(batch: np.ndarray, *, crop_top=None, crop_left=None, out_size=None,
-                    flip=None, boxes=None, ops=None, **kw) -> torch.Tensor:
+                    flip=None, boxes=None, ops=None, pre_ops=None, **kw) -> torch.Tensor:
     """``[B,H,W,C]`` uint8 -> ``[B,C,h,w]``; default collate = ``torch.stack``."""
     if isinstance(batch, torch.Tensor):
         batch = batch.cpu().numpy()
@@ -87,7 +91,8 @@ def transform_batch(batch: np.ndarray, *, crop_top=None, crop_left=None, out_siz
         rc = None
         if boxes is not None:
             rc = tuple(int(v) for v in boxes[b]) + (int(out_size[0]), int(out_size[1]))
-        out.append(transform_sample(batch[b], crop=crop, resized_crop=rc, flip=f, ops=None if ops is None else ops[b], **kw))
+        out.append(transform_sample(batch[b], crop=crop, resized_crop=rc, flip=f, ops=None if ops is None else ops[b],
+                                    pre_ops=None if pre_ops is None else pre_ops[b], **kw))
     return torch.stack(out)
 
 

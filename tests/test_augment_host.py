@@ -152,3 +152,34 @@ def test_reference_cifar_compose_golden(golden):
     assert torch.equal(got, torch.from_numpy(g["cifar_output"]))
     restated = np.stack([AO.restated_ops(AO.apply_ops(batch[b], []), []) for b in range(2)])     # smoke of the empty list
     assert np.array_equal(restated, batch[:2])
+
+
+IMAGENET = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+
+
+@pytest.mark.parametrize("pre,flip_p,rot,ra", [(180, None, None, (2, 9, 31)),      # online.py:173
+                                                (None, 0.5, None, (2, 9, 31)), (30, 0.5, 15, None), (None, None, 10, (1, 20, 31))])
+def test_chain_replay_equals_the_compose(pre, flip_p, rot, ra):
+    """ChainParams against the literal T.Compose around T.RandomResizedCrop under torch.manual_seed:
+    same draws <=> same images (both sides end in torchvision's functional ops)."""
+    import torchvision.transforms as T
+    from PIL import Image
+    rng = np.random.default_rng(21)
+    batch = rng.integers(0, 256, (10, 60, 80, 3), dtype=np.uint8)
+    stages = ([T.RandomRotation(pre)] if pre is not None else []) + [T.RandomResizedCrop(32)] + \
+        ([T.RandomHorizontalFlip(flip_p)] if flip_p is not None else []) + ([T.RandomRotation(rot)] if rot is not None else []) + \
+        ([T.RandAugment(*ra)] if ra is not None else []) + [T.ToTensor(), T.Normalize(IMAGENET[0], IMAGENET[1])]
+    compose = T.Compose(stages)
+    state = torch.get_rng_state()
+    try:
+        torch.manual_seed(314)
+        want = torch.stack([compose(Image.fromarray(batch[b])) for b in range(10)])
+    finally:
+        torch.set_rng_state(state)
+    cp = A.ChainParams(314, pre_rotation=pre, rotation=rot, rand_augment=ra)
+    box, flip, ops, pre_ops = cp.draw(6, 60, 80, 32, 32, flip_p)
+    box2, flip2, ops2, pre2 = cp.draw(4, 60, 80, 32, 32, flip_p)
+    join = lambda a, b: None if a is None else a + b
+    got = TO.transform_batch(batch, boxes=np.concatenate([box, box2]), out_size=(32, 32), flip=np.concatenate([flip, flip2]),
+                             ops=join(ops, ops2), pre_ops=join(pre_ops, pre2), mean=IMAGENET[0], std=IMAGENET[1])
+    assert torch.equal(got, want)

@@ -206,3 +206,30 @@ def test_larger_images_and_limits():
     assert tuple(empty.shape) == (0, 3, 8, 8)
     plain = BatchTransform(spec, device="cuda")(torch.from_numpy(batch[:1]).cuda(), params=(None, None, None, [[]]))
     assert same(plain, TO.transform_batch(batch[:1], mean=CIFAR[0], std=CIFAR[1]))
+
+
+IMAGENET = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+
+
+@pytest.mark.parametrize("pre,flip_p,rot,ra,dtype", [(180, None, None, True, torch.float32),        # online.py:173
+                                                      (None, 0.5, None, True, torch.bfloat16), (45, 0.5, 15, None, torch.float32),
+                                                      (180, None, None, None, torch.float16)])
+def test_resized_crop_chains_vs_the_compose(pre, flip_p, rot, ra, dtype):
+    """T.RandomRotation(180) -> T.RandomResizedCrop(size) -> T.RandAugment() -> ToTensor -> Normalize
+    (examples/img_stt/online/online.py:173) and its variants: the literal Compose under
+    torch.manual_seed against the chained launches with replayed draws."""
+    import torchvision.transforms as T
+    from PIL import Image
+    rng = np.random.default_rng(5)
+    B, H, W, size = 8, 120, 160, 96
+    batch = rng.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+    stages = ([T.RandomRotation(pre)] if pre is not None else []) + [T.RandomResizedCrop(size)] + \
+        ([T.RandomHorizontalFlip(flip_p)] if flip_p is not None else []) + ([T.RandomRotation(rot)] if rot is not None else []) + \
+        ([T.RandAugment()] if ra else []) + [T.ToTensor(), T.Normalize(IMAGENET[0], IMAGENET[1])]
+    compose = T.Compose(stages)
+    torch.manual_seed(2718)
+    want = torch.stack([compose(Image.fromarray(batch[b])) for b in range(B)]).to(dtype)
+    spec = TransformSpec(random_resized_crop=size, pre_rotation=pre, flip_p=flip_p, rotation=rot, rand_augment=ra,
+                         mean=IMAGENET[0], std=IMAGENET[1], dtype=dtype)
+    got = BatchTransform(spec, device="cuda", seed=2718)(torch.from_numpy(batch).cuda())
+    assert same(got, want)

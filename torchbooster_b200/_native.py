@@ -14,10 +14,10 @@ _lock = threading.Lock()
 _lib = None
 
 TB_OK, TB_EINVAL, TB_ENOTSUP, TB_ENOENT = 0, -22, -95, -2
-TB_F32, TB_BF16, TB_F16 = 0, 1, 2
+TB_F32, TB_BF16, TB_F16, TB_U8 = 0, 1, 2, 3
 PAD_MODES = {"none": 0, "constant": 1, "reflect": 2, "edge": 3, "symmetric": 4}
 LUT_TO_TENSOR, LUT_NORMALIZE, LUT_ONE_MINUS, LUT_NORMALIZE_ONE_MINUS = 0, 1, 2, 3
-FLAG_FORCE_GENERIC, FLAG_FORCE_STREAM, FLAG_NO_PDL = 1, 2, 4
+FLAG_FORCE_GENERIC, FLAG_FORCE_STREAM, FLAG_NO_PDL, FLAG_SRC_PLANAR = 1, 2, 4, 8
 
 _i32, _i64, _vp = C.c_int, C.c_int64, C.c_void_p
 
@@ -40,6 +40,7 @@ SIGNATURES = {
                                                         _vp, _vp, _i32, _vp]),
     "tb_augment_u8_nhwc_to_nchw": (_i32, [_vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp, _i32, _i32, _i32, _vp, _vp, _vp,
                                           _i32, _i32, _i32, _vp, _i32, _vp, _i32, _vp]),
+    "tb_affine_nearest_u8_nhwc": (_i32, [_vp, _i32, _i32, _i32, _i32, _i64, _i64, _vp, _vp, _vp]),
     "tb_augment_rotation_records": (_i32, [_vp, _i64, _i32, _i32, _vp]),
     "tb_augment_params_walk": (_i64, [_vp, _i64, _i64, _i32, _i32, C.c_double, _i32, C.c_float, C.c_float, _i32, _i32, _i32,
                                       _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp]),

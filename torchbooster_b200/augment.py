@@ -271,3 +271,81 @@ class AugmentParams:
             ops.append(mine)
         self._words = words[pos:]
         return top, left, flip, ops
+
+
+class ChainParams:
+    """Replay for pipelines built around ``T.RandomResizedCrop`` -- per sample, in this order:
+    ``RandomRotation(pre_rotation)`` -> ``RandomResizedCrop.get_params`` -> ``RandomHorizontalFlip`` ->
+    ``RandomRotation(rotation)`` -> ``RandAugment`` (``examples/img_stt/online/online.py:173`` is
+    pre_rotation=180, the resized crop, RandAugment).  Stages that are absent draw nothing.  A plain
+    sequential walk in Python: these pipelines run at batch sizes (8 in ``online.yml``) where that is free.
+    """
+
+    def __init__(self, seed: int, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0), pre_rotation=None, rotation=None,
+                 rand_augment: Optional[Tuple[int, int, int]] = None) -> None:
+        self._rs = np.random.RandomState(int(seed) & 0xFFFFFFFF)
+        self.scale = (float(scale[0]), float(scale[1]))
+        self.ratio = (float(ratio[0]), float(ratio[1]))
+        lr = torch.log(torch.tensor(self.ratio))                    # float32, as torchvision computes it
+        self._log_ratio = (float(lr[0].item()), float(lr[1].item()))
+        span = lambda d: None if d is None else ((-float(d), float(d)) if np.isscalar(d) else (float(d[0]), float(d[1])))
+        self.pre_rotation, self.rotation = span(pre_rotation), span(rotation)
+        self.rand_augment = None if rand_augment is None else tuple(int(v) for v in rand_augment)
+        self._words: List[int] = []
+
+    def _word(self) -> int:
+        if not self._words:
+            self._words = self._rs.randint(0, 2 ** 32, size=4096, dtype=np.uint64).tolist()[::-1]
+        return self._words.pop()
+
+    def _uniform(self, lo: float, hi: float) -> float:
+        return float(_torchrng.uniform(np.array([self._word()], np.uint64), lo, hi)[0])
+
+    def _box(self, height: int, width: int):
+        area = height * width
+        for _ in range(10):
+            target_area = area * self._uniform(*self.scale)
+            aspect = float(torch.exp(torch.tensor(np.float32(self._uniform(*self._log_ratio)))).item())
+            w = int(round(math.sqrt(target_area * aspect)))
+            h = int(round(math.sqrt(target_area / aspect)))
+            if 0 < w <= width and 0 < h <= height:
+                i = self._word() % (height - h + 1)
+                j = self._word() % (width - w + 1)
+                return i, j, h, w
+        in_ratio = float(width) / float(height)
+        if in_ratio < min(self.ratio):
+            w = width
+            h = int(round(w / min(self.ratio)))
+        elif in_ratio > max(self.ratio):
+            h = height
+            w = int(round(h * max(self.ratio)))
+        else:
+            w, h = width, height
+        return (height - h) // 2, (width - w) // 2, h, w
+
+    def draw(self, batch: int, height: int, width: int, out_h: int, out_w: int, flip_p: Optional[float] = None):
+        """Returns ``(box int32[B,4], flip uint8[B], ops, pre)``: ``ops[b]`` the (name, magnitude) list applied to
+        the resized crop, ``pre[b]`` the one applied to the source image (``None`` when the stage is absent)."""
+        box, flip = np.zeros((batch, 4), np.int32), np.zeros(batch, np.uint8)
+        pre = [] if self.pre_rotation is not None else None
+        ops = [] if (self.rotation is not None or self.rand_augment is not None) else None
+        n_ops, magnitude, bins = self.rand_augment if self.rand_augment is not None else (0, 0, 0)
+        mags = rand_augment_magnitudes(out_h, out_w, magnitude, bins) if n_ops else {}
+        for b in range(batch):
+            if pre is not None:
+                pre.append([("RandomRotation", self._uniform(*self.pre_rotation))])
+            box[b] = self._box(height, width)
+            if flip_p is not None:
+                flip[b] = _torchrng.unit_float32(np.array([self._word()], np.uint64))[0] < np.float32(flip_p)
+            if ops is not None:
+                mine: List[Op] = []
+                if self.rotation is not None:
+                    mine.append(("RandomRotation", self._uniform(*self.rotation)))
+                for _ in range(n_ops):
+                    name, signed = RAND_AUGMENT_SPACE[self._word() % len(RAND_AUGMENT_SPACE)]
+                    m = mags[name]
+                    if signed and self._word() % 2:
+                        m *= -1.0
+                    mine.append((name, m))
+                ops.append(mine)
+        return box, flip, ops, pre

@@ -48,6 +48,7 @@ struct AugParams {
     const int32_t* ops;
     int n_ops;
     const void* lut;
+    int64_t px_stride, ch_stride;   // source bytes between pixels of a row / between channels of a pixel
     int plane;          // out_h * out_w
     int buf_bytes;      // bytes of one image buffer held by one CTA (multiple of 16): the whole image, or its chunk
     uint64_t magic;     // ceil(2^40 / buf_bytes) (cluster launches)
@@ -177,8 +178,8 @@ __global__ void __launch_bounds__(kAugThreads) tb_augment_kernel(AugParams p) {
             bool inside = true;
             const int u = aug_fold(top + y, p.H, p.pad_mode, inside);
             const int v = aug_fold(left + xs, p.W, p.pad_mode, inside);
-            const uint8_t* __restrict__ s = img + (int64_t)u * p.pitch + (int64_t)v * C;
-            for (int c = 0; c < C; ++c) cur.st(c * plane + q, inside ? s[c] : (uint8_t)0);
+            const uint8_t* __restrict__ s = img + (int64_t)u * p.pitch + (int64_t)v * p.px_stride;
+            for (int c = 0; c < C; ++c) cur.st(c * plane + q, inside ? s[c * p.ch_stride] : (uint8_t)0);
         }
     }
     aug_sync<CL>();
@@ -380,7 +381,44 @@ int launch_augment(const AugParams& p, int cluster, size_t smem, cudaStream_t s)
     return TB_OK;
 }
 
+// Whole-image nearest affine, global -> global: one thread per output pixel.
+__global__ void __launch_bounds__(256) tb_affine_nearest_kernel(const uint8_t* __restrict__ src, int H, int W, int C, int64_t bs,
+                                                                int64_t pitch, const int32_t* __restrict__ records,
+                                                                uint8_t* __restrict__ dst, int blocks_per_image) {
+    tb_grid_dependency_wait();
+    const int b = blockIdx.x / blocks_per_image;
+    const int q = (blockIdx.x - b * blocks_per_image) * 256 + threadIdx.x;
+    if (q >= H * W) return;
+    const int32_t* rec = records + (int64_t)b * 8;
+    const int y = q / W, x = q - y * W;
+    int xin = x, yin = y;
+    if (rec[0] == TB_AUG_AFFINE) {
+        const uint32_t a0 = rec[1], a1 = rec[2], a2 = rec[3], a3 = rec[4], a4 = rec[5], a5 = rec[6];
+        xin = (int)(a2 + (uint32_t)x * a0 + (uint32_t)y * a1) >> 16;
+        yin = (int)(a5 + (uint32_t)x * a3 + (uint32_t)y * a4) >> 16;
+    }
+    const bool ok = (unsigned)xin < (unsigned)W && (unsigned)yin < (unsigned)H;
+    const uint8_t* s = src + (int64_t)b * bs + (int64_t)(ok ? yin : 0) * pitch + (int64_t)(ok ? xin : 0) * C;
+    uint8_t* d = dst + ((int64_t)b * H * W + q) * C;
+    for (int c = 0; c < C; ++c) d[c] = ok ? s[c] : (uint8_t)0;
+}
+
 }  // namespace
+
+extern "C" int tb_affine_nearest_u8_nhwc(const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride,
+                                         int64_t src_row_pitch, const int32_t* records, uint8_t* dst, tb_stream_t stream) {
+    TB_REQUIRE(B >= 0 && H >= 1 && W >= 1 && H < 32768 && W < 32768, "tb_affine_nearest: bad shape B=%d H=%d W=%d", B, H, W);
+    TB_REQUIRE(C >= 1 && C <= 4, "tb_affine_nearest: C=%d not in [1,4]", C);
+    TB_REQUIRE(src_row_pitch >= (int64_t)W * C && src_batch_stride >= 0, "tb_affine_nearest: bad strides");
+    if (B == 0) return TB_OK;
+    TB_REQUIRE(src && dst && records, "tb_affine_nearest: NULL argument");
+    const int64_t bpi = ((int64_t)H * W + 255) / 256;
+    TB_REQUIRE(bpi * B < ((int64_t)1 << 31), "tb_affine_nearest: grid too large");
+    tb_affine_nearest_kernel<<<(unsigned)(bpi * B), 256, 0, (cudaStream_t)stream>>>(src, H, W, C, src_batch_stride, src_row_pitch,
+                                                                                  records, dst, (int)bpi);
+    TB_LAUNCH_CHECK("tb_affine_nearest_kernel");
+    return TB_OK;
+}
 
 extern "C" int tb_augment_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride,
                                           int64_t src_row_pitch, void* dst, int dst_dtype, int out_h, int out_w,
@@ -398,7 +436,8 @@ extern "C" int tb_augment_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int 
         TB_REQUIRE(pad_y <= H - 1 && pad_x <= W - 1, "tb_augment: reflect padding must be smaller than the image");
     if (pad_mode == TB_PAD_SYMMETRIC)
         TB_REQUIRE(pad_y <= H && pad_x <= W, "tb_augment: symmetric padding must not exceed the image");
-    TB_REQUIRE(src_row_pitch >= (int64_t)W * C, "tb_augment: src_row_pitch %lld < W*C", (long long)src_row_pitch);
+    const bool planar = (flags & TB_FLAG_SRC_PLANAR) != 0;
+    TB_REQUIRE(src_row_pitch >= (int64_t)W * (planar ? 1 : C), "tb_augment: src_row_pitch %lld shorter than a row", (long long)src_row_pitch);
     TB_REQUIRE(src_batch_stride >= 0, "tb_augment: negative src_batch_stride");
     TB_REQUIRE(n_ops >= 0 && n_ops <= TB_AUG_MAX_OPS, "tb_augment: n_ops=%d not in [0,%d]", n_ops, TB_AUG_MAX_OPS);
     if (B == 0) return TB_OK;
@@ -414,6 +453,8 @@ extern "C" int tb_augment_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int 
     p.src = src; p.B = B; p.H = H; p.W = W; p.C = C; p.bs = src_batch_stride; p.pitch = src_row_pitch;
     p.dst = dst; p.out_h = out_h; p.out_w = out_w; p.top = crop_top; p.left = crop_left; p.flip = flip;
     p.pad_y = pad_y; p.pad_x = pad_x; p.pad_mode = pad_mode; p.ops = ops; p.n_ops = n_ops; p.lut = lut;
+    p.px_stride = planar ? 1 : C;
+    p.ch_stride = planar ? (int64_t)H * src_row_pitch : 1;
     const int64_t plane = (int64_t)out_h * out_w;
     // The image lives in shared memory, twice (operations that move pixels write the other copy):
     // in one CTA when it fits, else spread over a cluster of 2, 4 or 8 CTAs (distributed shared memory).

@@ -622,11 +622,11 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
     TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_resized_crop: bad source shape B=%d H=%d W=%d", B, H, W);
     TB_REQUIRE(C == 1 || C == 3, "tb_resized_crop: C=%d not supported (Pillow premultiplies alpha for RGBA); use C in {1,3}", C);
     TB_REQUIRE(out_h >= 1 && out_w >= 1, "tb_resized_crop: bad output size");
-    TB_REQUIRE(tb_dtype_size(dst_dtype) != 0, "tb_resized_crop: unknown dst_dtype %d", dst_dtype);
+    TB_REQUIRE(dst_dtype == TB_U8 || tb_dtype_size(dst_dtype) != 0, "tb_resized_crop: unknown dst_dtype %d", dst_dtype);
     TB_REQUIRE(src_row_pitch >= (int64_t)W * C && src_batch_stride >= 0, "tb_resized_crop: bad source strides");
     if (B == 0) return TB_OK;
     TB_REQUIRE(src && dst && lut && box, "tb_resized_crop: NULL src/dst/lut/box");
-    TB_REQUIRE(((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_resized_crop: dst misaligned for its dtype");
+    TB_REQUIRE(dst_dtype == TB_U8 || ((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_resized_crop: dst misaligned for its dtype");
     // every box is at most the whole image: a source within 4x of the output keeps every scale <= 4
     if ((int64_t)H > 4 * (int64_t)out_h || (int64_t)W > 4 * (int64_t)out_w)
         return tb_fail(TB_ENOTSUP, "tb_resized_crop: source %dx%d is more than four times the output %dx%d; "
@@ -670,6 +670,9 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resized_crop: grid too large");
     cudaStream_t s = (cudaStream_t)stream;
     const bool f32 = dst_dtype == TB_F32;
+    if (dst_dtype == TB_U8)     // bytes out: the resized crop hands a uint8 image on (to tb_augment)
+        return C == 3 ? launch_resize<uint8_t, 3>(p, smem, blocks, dev.max_smem_optin, true, nt, s)
+                      : launch_resize<uint8_t, 1>(p, smem, blocks, dev.max_smem_optin, true, nt, s);
     if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, true, nt, s)
                            : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, true, nt, s);
     return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, true, nt, s)

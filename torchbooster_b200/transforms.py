@@ -52,10 +52,13 @@ class TransformSpec:
     padding       ``T.RandomCrop`` padding: int or (left/right, top/bottom).
     padding_mode  "constant" (fill 0) | "reflect" | "edge" | "symmetric".
     flip_p        ``T.RandomHorizontalFlip`` probability; ``None`` = transform not in the pipeline.
+    pre_rotation  ``T.RandomRotation`` at the HEAD of a random_resized_crop pipeline (``online.py:173``:
+                  ``RandomRotation(180), RandomResizedCrop(size), RandAugment()``): the whole source is rotated.
     rotation      ``T.RandomRotation`` degrees (number or (min, max)); nearest, no expand, fill 0.
     rand_augment  ``T.RandAugment`` as ``(num_ops, magnitude, num_magnitude_bins)``, ``True`` = its defaults
-                  ``(2, 9, 31)`` (``resnet.py:99-100``).  Both apply to crop / flip pipelines; the per-sample
-                  operations come from ``params`` (a fourth element) or the replayed generator.
+                  ``(2, 9, 31)`` (``resnet.py:99-100``).  Both apply to crop / flip pipelines (one launch) and
+                  after a random_resized_crop (the crop hands a uint8 image to the augment kernel); the
+                  per-sample operations come from ``params`` or the replayed generator.
     mean, std     ``T.Normalize``; ``None`` = ToTensor only.
     one_minus     the ``1.0 - X`` of ``examples/img_gen/gan/gan.py:99``.
     dtype         output dtype: float32 (the reference), bfloat16 or float16 (RNE of the fp32 value).
@@ -67,6 +70,7 @@ class TransformSpec:
     padding: IntPair = 0
     padding_mode: str = "constant"
     flip_p: Optional[float] = None
+    pre_rotation: Union[None, float, Tuple[float, float]] = None
     rotation: Union[None, float, Tuple[float, float]] = None
     rand_augment: Union[None, bool, Tuple[int, int, int]] = None
     resize: Optional[IntPair] = None
@@ -89,9 +93,10 @@ class TransformSpec:
         if self.random_resized_crop is not None and (self.resize is not None or self.center_crop is not None or
                                                      self.crop is not None or _pair(self.padding) != (0, 0)):
             raise ValueError("random_resized_crop excludes resize, center_crop, crop and padding")
-        if self.augments and (self.resize is not None or self.center_crop is not None or
-                              self.random_resized_crop is not None):
-            raise NotImplementedError("rotation / rand_augment are built for crop / flip pipelines")
+        if self.augments and (self.resize is not None or self.center_crop is not None):
+            raise NotImplementedError("rotation / rand_augment are built for crop / flip and random_resized_crop pipelines")
+        if self.pre_rotation is not None and self.random_resized_crop is None:
+            raise NotImplementedError("pre_rotation is the head of a random_resized_crop pipeline (use rotation otherwise)")
         if self.rand_augment not in (None, True, False) and len(tuple(self.rand_augment)) != 3:
             raise ValueError("rand_augment is True or (num_ops, magnitude, num_magnitude_bins)")
         N.dtype_code(self.dtype)
@@ -236,6 +241,9 @@ class BatchTransform:
         self._taps = {}
         if seed is None:
             self._rng = None
+        elif spec.random_resized_crop is not None and (spec.augments or spec.pre_rotation is not None):
+            self._rng = _augment.ChainParams(seed, spec.rrc_scale, spec.rrc_ratio, spec.pre_rotation, spec.rotation,
+                                             spec.rand_augment_args)
         elif spec.random_resized_crop is not None:
             self._rng = ResizedCropParams(seed, spec.rrc_scale, spec.rrc_ratio)
         elif spec.augments:
@@ -323,6 +331,9 @@ class BatchTransform:
         with rotation / rand_augment -- from the replayed torch generator (needs ``seed=``)."""
         if self._rng is None:
             raise RuntimeError("BatchTransform was built without a seed; pass params= explicitly")
+        if isinstance(self._rng, _augment.ChainParams):
+            oh, ow = _pair(self.spec.random_resized_crop)
+            return self._rng.draw(batch, h, w, oh, ow, self.spec.flip_p)
         if self.spec.random_resized_crop is not None:
             return self._rng.draw(batch, h, w, self.spec.flip_p)
         g = self.geometry(h, w)
@@ -353,7 +364,7 @@ class BatchTransform:
             arr = ops if isinstance(ops, (np.ndarray, torch.Tensor)) else _augment.encode_ops(ops, h, w, channels)
             arr = np.ascontiguousarray(np.asarray(arr, dtype=np.int32))
             host = torch.from_numpy(arr).pin_memory()
-            self._ops_host = host               # pinned source stays alive until the copy has run
+            self._ops_hosts = (getattr(self, "_ops_hosts", []) + [host])[-4:]    # pinned sources stay alive until the copies have run
             rec = host.to(self.device, non_blocking=True)
         if rec.dim() != 3 or rec.shape[0] != batch or rec.shape[2] != _augment.OP_WORDS:
             raise ValueError(f"ops must be [B={batch}, n_ops, {_augment.OP_WORDS}] int32 records; got {tuple(rec.shape)}")
@@ -413,6 +424,53 @@ class BatchTransform:
         N.check(rc)
         return out
 
+    def _resized_crop_chain(self, batch: torch.Tensor, params, out: Optional[torch.Tensor]) -> torch.Tensor:
+        """[RandomRotation on the source ->] RandomResizedCrop [-> flip] [-> rotation / RandAugment on the crop] ->
+        table: up to three launches that hand uint8 images on (``online.py:173``)."""
+        sp = self.spec
+        B, H, W, Cn = batch.shape
+        out_h, out_w = _pair(sp.random_resized_crop)
+        box_flip, ops, pre = params[:2], params[2], params[3]
+        if (ops is None) != (not sp.augments) or (pre is None) != (sp.pre_rotation is None):
+            raise ValueError("params do not match the pipeline: ops / pre must be given exactly for the stages it has")
+        if out is None:
+            out = torch.empty((B, Cn, out_h, out_w), dtype=sp.dtype, device=self.device)
+        elif tuple(out.shape) != (B, Cn, out_h, out_w) or out.dtype != sp.dtype or not out.is_contiguous() or out.device != self.device:
+            raise ValueError(f"out must be a contiguous tensor of shape {(B, Cn, out_h, out_w)}, dtype {sp.dtype} on {self.device}")
+        if B == 0:
+            return out
+        L = N.lib()
+        lut = self.lut(Cn)
+        ptr = lambda t: None if t is None else t.data_ptr()
+        with torch.cuda.device(self.device):
+            stream = N.current_stream_ptr(self.device)
+            src = batch
+            if pre is not None:                                             # stage A: rotate the whole source image
+                rec = self._ops_to_device(pre, B, H, W, Cn)
+                if rec.shape[1] != 1:
+                    raise ValueError("pre holds exactly one operation per sample")
+                src = torch.empty((B, H, W, Cn), dtype=torch.uint8, device=self.device)
+                N.check(L.tb_affine_nearest_u8_nhwc(batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1),
+                                                    rec.data_ptr(), src.data_ptr(), stream))
+            box, flip = self._boxes_to_device(box_flip, B)
+            if ops is None:                                                 # stage B straight to the output
+                N.check(L.tb_resized_crop_bilinear_u8_nhwc_to_nchw(
+                    src.data_ptr(), B, H, W, Cn, src.stride(0), src.stride(1), box.data_ptr(), out.data_ptr(),
+                    N.dtype_code(sp.dtype), out_h, out_w, ptr(flip), lut.data_ptr(), self.flags, stream))
+                return out
+            if getattr(self, "_bytes_lut", None) is None or self._bytes_lut.shape[0] != Cn:
+                self._bytes_lut = torch.arange(256, dtype=torch.uint8, device=self.device).repeat(Cn, 1).contiguous()
+            crop = torch.empty((B, Cn, out_h, out_w), dtype=torch.uint8, device=self.device)      # stage B: bytes, planar
+            N.check(L.tb_resized_crop_bilinear_u8_nhwc_to_nchw(
+                src.data_ptr(), B, H, W, Cn, src.stride(0), src.stride(1), box.data_ptr(), crop.data_ptr(),
+                N.TB_U8, out_h, out_w, ptr(flip), self._bytes_lut.data_ptr(), self.flags, stream))
+            rec = self._ops_to_device(ops, B, out_h, out_w, Cn)             # stage C: operations on the crop, then the table
+            N.check(L.tb_augment_u8_nhwc_to_nchw(
+                crop.data_ptr(), B, out_h, out_w, Cn, Cn * out_h * out_w, out_w, out.data_ptr(), N.dtype_code(sp.dtype),
+                out_h, out_w, None, None, None, 0, 0, N.PAD_MODES["none"], rec.data_ptr(), int(rec.shape[1]),
+                lut.data_ptr(), N.FLAG_SRC_PLANAR, stream))
+        return out
+
     # -- the call --------------------------------------------------------------------------
     def __call__(self, batch: torch.Tensor, params=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         if batch.dtype != torch.uint8 or batch.dim() != 4:
@@ -434,6 +492,10 @@ class BatchTransform:
         if params is None and self._rng is not None and (rrc or sp.augments or g["crop"] is not None or sp.flip_p is not None):
             params = self.draw_params(B, H, W, Cn)
         top = left = flip = box = ops = None
+        if rrc and (sp.augments or sp.pre_rotation is not None):
+            if params is None or len(params) != 4:
+                raise ValueError("this pipeline needs params=(box[B,4], flip, ops, pre) or a seed")
+            return self._resized_crop_chain(batch, params, out)
         if rrc:
             if params is None:
                 raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
