@@ -239,6 +239,24 @@ def ncu_traffic(workload: str):
     return None
 
 
+def bind_to_gpu_node(index: int):
+    """Pins this process to the CPUs NVML lists as local to its GPU, before any pinned host buffer is
+    allocated: the buffers the kernel reads over PCIe then lie on the GPU's own NUMA node instead of
+    wherever the launcher happened to start the rank.  Returns the number of CPUs in the mask."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = torch.cuda.get_device_properties(index).uuid
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
 def run_ours(args, wl):
     from torchbooster_b200 import _native as N
     from torchbooster_b200.metrics import MetricState
@@ -253,6 +271,7 @@ def run_ours(args, wl):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    affinity = None if args.no_affinity else bind_to_gpu_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     L = N.lib()
@@ -487,7 +506,9 @@ def run_ours(args, wl):
                                   "output buffers), scoring on a third; all joined before the stop event",
                        "launch": (f"CUDA graph of {G} steps replayed {K // G} times + {K % G} eager steps"
                                   if graph is not None else "eager launches"),
-                       "variant": args.variant},
+                       "variant": args.variant,
+                       "cpu_affinity": (f"rank pinned to its GPU's {affinity} local CPUs (NVML) before pinned buffers are allocated"
+                                        if affinity else "not set")},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": ck, "per_rank": per_rank,
             "counts": {"n": counts["n"], "correct_1": counts["correct_1"], f"correct_{k}": counts[f"correct_{k}"]},
@@ -582,6 +603,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-affinity", action="store_true", help="do not pin the rank to its GPU's local CPUs")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
