@@ -45,17 +45,15 @@ def get_local_rank() -> int:
     """Rank inside this machine's group, 0 outside a process group."""
     if not _active():
         return 0
-    if not LOCAL_PROCESS_GROUP:
+    group = LOCAL_PROCESS_GROUP
+    if not group:                       # same complaint as the reference (distributed.py:36-37)
         raise ValueError("LOCAL_PROCESS_GROUP is None")
-    return dist.get_rank(group=LOCAL_PROCESS_GROUP)
+    return dist.get_rank(group=group)
 
 
 def gather(tensor: torch.Tensor, tensor_list: List[torch.Tensor] = None):
     """Gather ``tensor`` from every rank into ``tensor_list`` on rank 0 (``None`` elsewhere)."""
-    if is_primary():
-        dist.gather(tensor, tensor_list)
-    else:
-        dist.gather(tensor, dst=0)
+    dist.gather(tensor, gather_list=tensor_list if is_primary() else None, dst=0)
 
 
 def is_primary() -> bool:
@@ -101,21 +99,19 @@ def launch(
     args: tuple = (),
 ) -> None:
     """Run ``fn(*args)`` in-process for a world of one, else once per GPU via ``mp.spawn``."""
-    world_size = n_machine * n_gpu_per_machine
-    if world_size == 1:
+    ranks = n_machine * n_gpu_per_machine
+    if ranks == 1:                      # a world of one never spawns
         fn(*args)
-        return
+        return None
 
     logging.info("Launching in distributed mode")
     os.environ.setdefault("OMP_NUM_THREADS", "1")
-
     if dist_url == "auto":
-        if n_machine > 1:
-            raise ValueError("dist_url='auto' no supported in multi-machine jobs")
-        dist_url = f"tcp://127.0.0.1:{find_free_port()}"
-
-    mp.spawn(job, nprocs=n_gpu_per_machine,
-             args=(fn, world_size, n_gpu_per_machine, machine_rank, dist_url, args), daemon=False)
+        if n_machine != 1:
+            raise ValueError("dist_url='auto' no supported in multi-machine jobs")      # message of distributed.py:146-147
+        dist_url = "tcp://127.0.0.1:%d" % find_free_port()
+    spawn_args = (fn, ranks, n_gpu_per_machine, machine_rank, dist_url, args)
+    mp.spawn(job, nprocs=n_gpu_per_machine, args=spawn_args, daemon=False)
 
 
 def job(
@@ -130,31 +126,25 @@ def job(
     """Per-process entry: join the NCCL group, pin the GPU, build per-machine groups, run ``fn``."""
     global LOCAL_PROCESS_GROUP
 
+    per = n_gpu_per_machine
     if REQUIRE_CUDA and not torch.cuda.is_available():
-        raise OSError("CUDA is not available on this machine")
-
-    global_rank = machine_rank * n_gpu_per_machine + local_rank
+        raise OSError("CUDA is not available on this machine")           # distributed.py:168-169
     try:
-        dist.init_process_group(backend=BACKEND, init_method=dist_url, world_size=world_size, rank=global_rank)
+        dist.init_process_group(backend=BACKEND, init_method=dist_url, world_size=world_size,
+                                rank=machine_rank * per + local_rank)
     except Exception:
-        raise OSError("NCC groups failed to initialize")
-
+        raise OSError("NCC groups failed to initialize")                 # distributed.py:181-182 (sic)
     synchronize()
-
     if REQUIRE_CUDA:
-        available = torch.cuda.device_count()
-        if n_gpu_per_machine > available:
-            raise ValueError(f"Asked for {n_gpu_per_machine} gpus bu got {available} available")
+        have = torch.cuda.device_count()
+        if per > have:
+            raise ValueError(f"Asked for {per} gpus bu got {have} available")   # distributed.py:186-189 (sic)
         torch.cuda.set_device(local_rank)
-
     if LOCAL_PROCESS_GROUP is not None:
         raise ValueError("torch.distributed.LOCAL_PROCESS_GROUP is not None")
-
-    for i in range(world_size // n_gpu_per_machine):
-        group = dist.new_group(list(range(i * n_gpu_per_machine, (i + 1) * n_gpu_per_machine)))
-        if i == machine_rank:
-            LOCAL_PROCESS_GROUP = group
-
+    # every rank creates every machine's group (new_group is collective) and keeps its own
+    machines = [dist.new_group(list(range(m * per, m * per + per))) for m in range(world_size // per)]
+    LOCAL_PROCESS_GROUP = machines[machine_rank]
     fn(*args)
 
 
