@@ -35,6 +35,8 @@ def test_golden_pillow_resize(golden):
         assert same(out, ref), f"case {i}"
 
 
+BOTH_KERNELS = (0, 16)      # sliding-window kernel (default), TB_FLAG_TWO_PHASE
+
 CASES = [
     # B, H, W, C, resize, center_crop, dtype
     (2, 512, 512, 3, 256, 256, torch.float32),       # C4
@@ -59,8 +61,10 @@ def test_resize_grid_vs_oracle(B, H, W, C, resize, cc, dtype):
     batch = rng.integers(0, 256, (B, H, W, C), dtype=np.uint8)
     mean, std = (IMAGENET if C == 3 else ((.5,), (.5,)))
     want = TO.transform_batch(batch, resize=resize, center_crop=cc, mean=mean, std=std, dtype=dtype)
-    bt = BatchTransform(TransformSpec(resize=resize, center_crop=cc, mean=mean, std=std, dtype=dtype), device="cuda")
-    assert same(bt(torch.from_numpy(batch).cuda()), want)
+    for flags in BOTH_KERNELS:
+        bt = BatchTransform(TransformSpec(resize=resize, center_crop=cc, mean=mean, std=std, dtype=dtype), device="cuda")
+        bt.flags = flags
+        assert same(bt(torch.from_numpy(batch).cuda()), want), flags
 
 
 def test_resize_then_random_crop_flip():
@@ -70,9 +74,11 @@ def test_resize_then_random_crop_flip():
     top = np.array([0, 4, 8], np.int32); left = np.array([21, 0, 7], np.int32); flip = np.array([1, 1, 0], np.uint8)
     want = TO.transform_batch(batch, resize=48, crop_top=top, crop_left=left, out_size=(40, 43), flip=flip,
                               mean=IMAGENET[0], std=IMAGENET[1])
-    bt = BatchTransform(TransformSpec(resize=48, crop=(40, 43), flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1]),
-                        device="cuda")
-    assert same(bt(torch.from_numpy(batch).cuda(), params=(top, left, flip)), want)
+    for flags in BOTH_KERNELS:
+        bt = BatchTransform(TransformSpec(resize=48, crop=(40, 43), flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1]),
+                            device="cuda")
+        bt.flags = flags
+        assert same(bt(torch.from_numpy(batch).cuda(), params=(top, left, flip)), want), flags
 
 
 def test_resize_linearity_property_full_size():
@@ -126,7 +132,7 @@ def test_fuzz_resize_against_integer_oracle(seed):
             want.append(TO.index_map_sample(rs, lut.view(view).numpy(), top=int(top[b]), left=int(left[b]), out_h=th,
                                             out_w=tw, flip=bool(flip[b]), pad_y=pad, pad_x=pad, pad_mode="constant"))
         spec = TransformSpec(resize=(rs_h, rs_w), crop=(th, tw), padding=pad, flip_p=.5, mean=mean, std=std, dtype=dtype)
-        for flags in (0, 1):
+        for flags in (0, 1, 16):
             bt = BatchTransform(spec, device="cuda")
             bt.flags = flags
             got = bt(torch.from_numpy(batch).cuda(), params=(top, left, flip)).cpu().view(view).numpy()
@@ -156,9 +162,11 @@ def test_random_resized_crop_vs_torchvision(B, H, W, C, size, dtype):
     mean, std = (IMAGENET if C == 3 else ((.5,), (.5,)))
     out_size = (size, size) if isinstance(size, int) else size
     want = TO.transform_batch(batch, boxes=boxes, out_size=out_size, flip=flip, mean=mean, std=std, dtype=dtype)
-    bt = BatchTransform(TransformSpec(random_resized_crop=size, flip_p=.5, mean=mean, std=std, dtype=dtype),
-                        device="cuda", seed=77)
-    assert same(bt(torch.from_numpy(batch).cuda()), want)
+    for flags in BOTH_KERNELS:
+        bt = BatchTransform(TransformSpec(random_resized_crop=size, flip_p=.5, mean=mean, std=std, dtype=dtype),
+                            device="cuda", seed=77)
+        bt.flags = flags
+        assert same(bt(torch.from_numpy(batch).cuda()), want), flags
 
 
 def test_resized_crop_edge_boxes_and_limits():
@@ -169,12 +177,14 @@ def test_resized_crop_edge_boxes_and_limits():
     boxes = np.array([[0, 0, 64, 64], [10, 20, 1, 1], [5, 0, 1, 64], [0, 7, 64, 1], [16, 16, 32, 32], [63, 63, 1, 1]], np.int32)
     flip = np.array([0, 1, 0, 1, 1, 0], np.uint8)
     want = TO.transform_batch(batch, boxes=boxes, out_size=(S, S), flip=flip, mean=IMAGENET[0], std=IMAGENET[1])
-    bt = BatchTransform(TransformSpec(random_resized_crop=S, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1]), device="cuda")
-    assert same(bt(torch.from_numpy(batch).cuda(), params=(boxes, flip)), want)
-    # a box outside the image gives zeros (lut[0]) instead of reading out of bounds
-    bad = boxes.copy(); bad[0] = [60, 60, 10, 10]
-    out = bt(torch.from_numpy(batch).cuda(), params=(bad, flip))
-    assert same(out[1:], want[1:]) and bool((out[0] == bt.lut(3)[:, 0].view(3, 1, 1)).all())
+    for flags in BOTH_KERNELS:
+        bt = BatchTransform(TransformSpec(random_resized_crop=S, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1]), device="cuda")
+        bt.flags = flags
+        assert same(bt(torch.from_numpy(batch).cuda(), params=(boxes, flip)), want), flags
+        # a box outside the image gives zeros (lut[0]) instead of reading out of bounds
+        bad = boxes.copy(); bad[0] = [60, 60, 10, 10]
+        out = bt(torch.from_numpy(batch).cuda(), params=(bad, flip))
+        assert same(out[1:], want[1:]) and bool((out[0] == bt.lut(3)[:, 0].view(3, 1, 1)).all())
     # reductions beyond 4x are not built for per-sample boxes
     big = torch.zeros((1, 200, 200, 3), dtype=torch.uint8, device="cuda")
     with pytest.raises(NotImplementedError, match="four times"):

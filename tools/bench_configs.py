@@ -322,6 +322,11 @@ def main():
         c4 = dict(resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1])
         transform_case("c4_stt_b32", 32, 512, 512, c4, 1572864, 200, params=False)
         transform_case("c4_stt_b256", 256, 512, 512, c4, 1572864, 50, params=False)
+        transform_case("c4_stt_b32_two_phase", 32, 512, 512, c4, 1572864, 200, flags=16, params=False)
+        transform_case("c4_stt_b256_two_phase", 256, 512, 512, c4, 1572864, 50, flags=16, params=False)
+        for tr in (8, 16, 32):
+            transform_case(f"c4_stt_b256_tr{tr}", 256, 512, 512, c4, 1572864, 50, flags=tr << 24, params=False)
+            transform_case(f"c4_stt_b32_tr{tr}", 32, 512, 512, c4, 1572864, 200, flags=tr << 24, params=False)
         if a.quick:
             for per in (1, 2, 4, 8, 16):
                 transform_case(f"c4_stt_b256_per{per}", 256, 512, 512, c4, 1572864, 50, flags=per << 16, params=False)
@@ -335,6 +340,7 @@ def main():
     if want("rrc"):
         rrc_case("rrc_c2_b512", 512, 100)
         rrc_case("rrc_c2_b2048", 2048, 30)
+        rrc_case("rrc_c2_b512_two_phase", 512, 100, flags=16)
         if a.quick:
             for per in (1, 2, 4, 7, 14):
                 rrc_case(f"rrc_c2_b512_per{per}", 512, 100, flags=per << 16)

@@ -489,6 +489,228 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
 }
 
 
+// ----------------------------------------------------------------------------------------------
+// sliding-window variant of the fast path: NO shared-memory intermediate.
+//
+// A thread owns one output column and walks down the input rows of its strip.  For every input
+// row it runs the horizontal pass for its column (same DP4A chain) and pushes the uint8 result
+// into a per-channel register window holding the last NT rows -- exactly the NT samples the
+// vertical pass of the next output row needs, already packed for DP4A.  Whenever the window's
+// newest row is the last row an output row depends on (s_ytop), that output row is emitted:
+// vertical DP4A chain on the window registers, table lookup, coalesced store.  All threads of
+// the CTA see the same row schedule, so there is no divergence, no __syncthreads in the loop,
+// and none of the transposed stores / unaligned window loads of the two-phase kernel.
+// Works for every scale the NT taps cover, up- and down-scaling (an output row is emitted after
+// 0, 1 or several pushes).
+// ----------------------------------------------------------------------------------------------
+constexpr int kSlideMaxTR = 32;
+
+// v = *p when take, else v keeps its bits (no zeroing, no branch)
+__device__ __forceinline__ void tb_ldg_if(uint32_t& v, const uint32_t* p, bool take) {
+    asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)take));
+}
+
+template <typename T, int C, bool BOX, int NT>
+__global__ void __launch_bounds__(256) tb_resize_slide_kernel(RsParams p) {
+    constexpr int G = NT / 4;
+    constexpr int NQ = NT * C / 4;                   // aligned words of an NT-sample window after the shift
+    constexpr int UR = NT == 4 ? 4 : 2;              // input rows in flight per thread
+    __shared__ T s_lut[C * 256];
+    __shared__ uint32_t s_kyb[kSlideMaxTR][G][3];
+    __shared__ int s_ytop[kSlideMaxTR];              // last input row an output row needs; -1: outside the resized image
+    tb_grid_dependency_wait();
+    for (int i = threadIdx.x; i < C * 256; i += blockDim.x) s_lut[i] = ((const T*)p.lut)[i];
+
+    int t = blockIdx.x;
+    const int tx = t % p.tiles_x; t /= p.tiles_x;
+    const int ty = t % p.tiles_y;
+    const int b = t / p.tiles_y;
+    const int x0 = tx * p.TC, y0 = ty * p.TR;
+    const int nc = min(p.TC, p.out_w - x0), nr = min(p.TR, p.out_h - y0);
+    int box_top = 0, box_left = 0, in_h = p.H, in_w = p.W;
+    if constexpr (BOX) {
+        box_top = p.box[4 * b]; box_left = p.box[4 * b + 1]; in_h = p.box[4 * b + 2]; in_w = p.box[4 * b + 3];
+        // a box the host did not vouch for (outside the image, or too large for NT taps) yields zeros
+        if (box_top < 0 || box_left < 0 || in_h < 1 || in_w < 1 || box_top + in_h > p.H || box_left + in_w > p.W ||
+            in_h > (NT / 2) * p.rs_h || in_w > (NT / 2) * p.rs_w)
+            in_h = in_w = 0;
+    }
+    const int oy = BOX ? 0 : (p.top ? p.top[b] : 0) + p.off_y;
+    const int ox = BOX ? 0 : (p.left ? p.left[b] : 0) + p.off_x;
+    const bool flip = p.flip ? (p.flip[b] != 0) : false;
+
+    // ---- vertical taps of this strip's output rows
+    if ((int)threadIdx.x < nr) {
+        const int ry = oy + y0 + (int)threadIdx.x;
+        int top = -1;
+        if (ry >= 0 && ry < p.rs_h && in_h > 0) {
+            TapN<NT> tp;
+            if constexpr (BOX) {
+                tp = tb_bilinear_tap<NT>(in_h, p.rs_h, ry);
+            } else {
+                tp.xmin = p.by[2 * ry]; tp.n = p.by[2 * ry + 1];
+#pragma unroll
+                for (int j = 0; j < NT; ++j) tp.k[j] = (j < p.ksy && j < tp.n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+            }
+            tb_pack_taps<G>(tp.k, s_kyb[threadIdx.x]);
+            top = tp.xmin + NT - 1;
+        }
+        s_ytop[threadIdx.x] = top;
+    }
+    // ---- this thread's column: horizontal taps and source window
+    const bool active = (int)threadIdx.x < nc;
+    const int x = x0 + (int)threadIdx.x;
+    const int rx = ox + (flip ? p.out_w - 1 - x : x);
+    const bool colin = active && in_w > 0 && rx >= 0 && rx < p.rs_w;
+    // A column outside the resized image keeps all-zero taps: its horizontal results, its window
+    // and its outputs are then 0 without any special casing below.
+    uint32_t kbx[G][3];
+#pragma unroll
+    for (int g = 0; g < G; ++g) kbx[g][0] = kbx[g][1] = kbx[g][2] = 0;
+    int a1 = 0, nw1 = 1;
+    const int64_t pitch_w = p.pitch >> 2;
+    const uint32_t* wbase = reinterpret_cast<const uint32_t*>(p.src + (int64_t)b * p.bs);      // always a readable word
+    if (colin) {
+        TapN<NT> tp;
+        if constexpr (BOX) {
+            tp = tb_bilinear_tap<NT>(in_w, p.rs_w, rx);
+        } else {
+            tp.xmin = p.bx[2 * rx]; tp.n = p.bx[2 * rx + 1];
+#pragma unroll
+            for (int j = 0; j < NT; ++j) tp.k[j] = (j < p.ksx && j < tp.n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+        }
+        tb_pack_taps<G>(tp.k, kbx);
+        const int boff = (box_left + tp.xmin) * C;
+        a1 = boff & 3;
+        nw1 = (a1 + tp.n * C + 3) >> 2;                  // words that hold this window (1 .. NQ + 1)
+        wbase = reinterpret_cast<const uint32_t*>(p.src + (int64_t)b * p.bs + (boff - a1)) + (int64_t)box_top * pitch_w;
+    }
+    const int sh1 = a1 * 8;
+    const uint32_t pitch_b = (uint32_t)p.pitch;
+    const int64_t plane = (int64_t)p.out_h * p.out_w;
+    T* d[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) d[c] = (T*)p.dst + ((int64_t)b * C + c) * plane + (int64_t)y0 * p.out_w + x;
+    __syncthreads();
+
+    uint32_t win[C][G];
+#pragma unroll
+    for (int c = 0; c < C; ++c)
+#pragma unroll
+        for (int g = 0; g < G; ++g) win[c][g] = 0;
+
+    int yy = 0;
+    auto emit = [&](bool valid) {       // output row yy from the window (zeros when the row lies outside the resized image)
+        uint32_t e[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) e[c] = 0;
+        if (valid) {
+            uint32_t kb[G][3];
+#pragma unroll
+            for (int g = 0; g < G; ++g) { kb[g][0] = s_kyb[yy][g][0]; kb[g][1] = s_kyb[yy][g][1]; kb[g][2] = s_kyb[yy][g][2]; }
+#pragma unroll
+            for (int c = 0; c < C; ++c) e[c] = tb_dot<G>(win[c], kb);
+        }
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            if (active) *d[c] = s_lut[c * 256 + e[c]];
+            d[c] += p.out_w;
+        }
+        ++yy;
+    };
+
+    while (yy < nr && s_ytop[yy] < 0) emit(false);                // rows above the resized image (centre-crop padding)
+    if (yy < nr) {
+        int nv = nr;
+        while (s_ytop[nv - 1] < 0) --nv;                         // rows below it
+        const int first = s_ytop[yy] - (NT - 1), last = s_ytop[nv - 1];
+        // Rows past `last` (the batch's tail) or past the source (their taps are zero) re-read row
+        // `rlim`: every load stays inside the image and what it returns is never weighted.
+        const int rlim = min(last, in_h - 1);
+        int next_top = s_ytop[yy];
+        uint32_t w[UR][NQ + 1];
+#pragma unroll
+        for (int u = 0; u < UR; ++u)
+#pragma unroll
+            for (int i = 0; i <= NQ; ++i) w[u][i] = 0;
+        for (int r0 = first; r0 <= last; r0 += UR) {
+#pragma unroll
+            for (int u = 0; u < UR; ++u) {
+                // one 32 x 32 -> 64-bit multiply-add per row (the host keeps the pitch below 4 GiB)
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(
+                    reinterpret_cast<const char*>(wbase) + (uint64_t)(uint32_t)min(r0 + u, rlim) * pitch_b);
+                w[u][0] = __ldg(wp);
+#pragma unroll
+                for (int i = 1; i <= NQ; ++i) tb_ldg_if(w[u][i], wp + i, i < nw1);     // words past the window keep stale bits: zero taps
+            }
+#pragma unroll
+            for (int u = 0; u < UR; ++u) {
+                const int r = r0 + u;
+                if (r > last) break;
+                uint32_t q[NQ];
+#pragma unroll
+                for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[u][i], w[u][i + 1], sh1);
+                uint32_t h[C];
+                if (C == 3) {
+                    // samples of channel c sit at bytes c, c+3, c+6, c+9 of each 12-byte group of four pixels
+                    uint32_t p0[G], p1[G], p2[G];
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        p0[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0630), q[3 * g + 2], 0x5210);
+                        p1[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0741), q[3 * g + 2], 0x6210);
+                        p2[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0052), q[3 * g + 2], 0x7410);
+                    }
+                    h[0] = tb_dot<G>(p0, kbx);
+                    h[1 % C] = tb_dot<G>(p1, kbx);
+                    h[2 % C] = tb_dot<G>(p2, kbx);
+                } else {
+                    h[0] = tb_dot<G>(q, kbx);
+                }
+                // push: the window keeps rows r - NT + 1 .. r, oldest in byte 0
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+#pragma unroll
+                    for (int g = 0; g + 1 < G; ++g) win[c][g] = __funnelshift_r(win[c][g], win[c][g + 1], 8);
+                    win[c][G - 1] = (win[c][G - 1] >> 8) | (h[c] << 24);
+                }
+                while (next_top == r) {
+                    emit(true);
+                    next_top = yy < nv ? s_ytop[yy] : 0x7fffffff;
+                }
+            }
+        }
+        while (yy < nr) emit(false);
+    }
+}
+
+
+template <typename T, int C>
+int launch_slide(const RsParams& p, int64_t blocks, int threads, int nt, cudaStream_t s) {
+    if (p.box) {
+        if (nt == 4) tb_resize_slide_kernel<T, C, true, 4><<<(unsigned)blocks, threads, 0, s>>>(p);
+        else tb_resize_slide_kernel<T, C, true, 8><<<(unsigned)blocks, threads, 0, s>>>(p);
+    } else {
+        if (nt == 4) tb_resize_slide_kernel<T, C, false, 4><<<(unsigned)blocks, threads, 0, s>>>(p);
+        else tb_resize_slide_kernel<T, C, false, 8><<<(unsigned)blocks, threads, 0, s>>>(p);
+    }
+    TB_LAUNCH_CHECK("tb_resize_slide_kernel");
+    return TB_OK;
+}
+
+// Strip geometry of the sliding-window kernel: CTA = min(out_w, 256) columns x TR output rows.
+inline void slide_geometry(RsParams& p, int B, int sm_count, int flags, int64_t* blocks, int* threads) {
+    const int TC = p.out_w < 256 ? p.out_w : 256;
+    const int tiles_x = (p.out_w + TC - 1) / TC;
+    int TR = kSlideMaxTR;         // taller strips recompute fewer halo rows; keep >= 8 CTAs per SM in the grid
+    while (TR > 8 && (int64_t)B * tiles_x * ((p.out_h + TR - 1) / TR) < 8 * (int64_t)sm_count) TR >>= 1;
+    if ((flags >> 24) & 0xff) TR = (flags >> 24) & 0xff;      // development knob
+    if (TR > kSlideMaxTR) TR = kSlideMaxTR;
+    if (TR > p.out_h) TR = p.out_h;
+    p.TR = TR; p.TC = TC; p.tiles_x = tiles_x; p.tiles_y = (p.out_h + TR - 1) / TR;
+    *blocks = (int64_t)B * p.tiles_x * p.tiles_y;
+    *threads = ((TC + 31) / 32) * 32;
+}
+
 template <typename T, int C>
 int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, bool fast, int nt, cudaStream_t s) {
     static bool attr_set[64] = {};
@@ -562,6 +784,16 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     bool fast = !(flags & TB_FLAG_FORCE_GENERIC) && p.words_ok && rs_w != W && rs_h != H &&
                 (int64_t)W <= 4 * (int64_t)rs_w && (int64_t)H <= 4 * (int64_t)rs_h;
     const int nt = ((int64_t)W <= 2 * (int64_t)rs_w && (int64_t)H <= 2 * (int64_t)rs_h) ? 4 : 8;
+    if (fast && !(flags & TB_FLAG_TWO_PHASE) && src_row_pitch < ((int64_t)1 << 32)) {
+        int64_t blocks = 0;
+        int threads = 0;
+        slide_geometry(p, B, dev.sm_count, flags, &blocks, &threads);
+        TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize: grid too large");
+        cudaStream_t s = (cudaStream_t)stream;
+        if (dst_dtype == TB_F32)
+            return C == 3 ? launch_slide<float, 3>(p, blocks, threads, nt, s) : launch_slide<float, 1>(p, blocks, threads, nt, s);
+        return C == 3 ? launch_slide<uint16_t, 3>(p, blocks, threads, nt, s) : launch_slide<uint16_t, 1>(p, blocks, threads, nt, s);
+    }
     int TC = out_w < 256 ? out_w : 256;
     // taller tiles recompute fewer halo rows; keep at least ~4 CTAs per SM in the grid
     int TR = ((int64_t)B * ((out_h + 15) / 16) * ((out_w + TC - 1) / TC) >= 4 * (int64_t)dev.sm_count) ? 16 : 8;
@@ -643,6 +875,18 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
     p.rs_h = out_h; p.rs_w = out_w;
     p.dst = dst; p.out_h = out_h; p.out_w = out_w;
     p.flip = flip; p.lut = lut; p.box = box; p.words_ok = 1;
+    if (!(flags & TB_FLAG_TWO_PHASE) && src_row_pitch < ((int64_t)1 << 32)) {
+        int64_t blocks = 0;
+        int threads = 0;
+        slide_geometry(p, B, dev.sm_count, flags, &blocks, &threads);
+        TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resized_crop: grid too large");
+        cudaStream_t s = (cudaStream_t)stream;
+        if (dst_dtype == TB_U8)
+            return C == 3 ? launch_slide<uint8_t, 3>(p, blocks, threads, nt, s) : launch_slide<uint8_t, 1>(p, blocks, threads, nt, s);
+        if (dst_dtype == TB_F32)
+            return C == 3 ? launch_slide<float, 3>(p, blocks, threads, nt, s) : launch_slide<float, 1>(p, blocks, threads, nt, s);
+        return C == 3 ? launch_slide<uint16_t, 3>(p, blocks, threads, nt, s) : launch_slide<uint16_t, 1>(p, blocks, threads, nt, s);
+    }
     const int TC = out_w < 256 ? out_w : 256;
     int TR = ((int64_t)B * ((out_h + 15) / 16) * ((out_w + TC - 1) / TC) >= 4 * (int64_t)dev.sm_count) ? 16 : 8;
     // up to nt/2 input rows per output row + the tap overhang
