@@ -324,13 +324,12 @@ def main():
         transform_case("c4_stt_b256", 256, 512, 512, c4, 1572864, 50, params=False)
         transform_case("c4_stt_b32_two_phase", 32, 512, 512, c4, 1572864, 200, flags=16, params=False)
         transform_case("c4_stt_b256_two_phase", 256, 512, 512, c4, 1572864, 50, flags=16, params=False)
-        for tr in (8, 16, 32):
-            transform_case(f"c4_stt_b256_tr{tr}", 256, 512, 512, c4, 1572864, 50, flags=tr << 24, params=False)
-            transform_case(f"c4_stt_b32_tr{tr}", 32, 512, 512, c4, 1572864, 200, flags=tr << 24, params=False)
         if a.quick:
-            for per in (1, 2, 4, 8, 16):
-                transform_case(f"c4_stt_b256_per{per}", 256, 512, 512, c4, 1572864, 50, flags=per << 16, params=False)
-                transform_case(f"c4_stt_b32_per{per}", 32, 512, 512, c4, 1572864, 100, flags=per << 16, params=False)
+            for tr in (8, 16, 32):
+                for tc in (2, 4, 8):
+                    transform_case(f"c4_stt_b256_tr{tr}_tc{tc * 32}", 256, 512, 512, c4, 1572864, 50, flags=(tr << 24) | (tc << 16), params=False)
+                    transform_case(f"c4_stt_b32_tr{tr}_tc{tc * 32}", 32, 512, 512, c4, 1572864, 200, flags=(tr << 24) | (tc << 16), params=False)
+
     if want("loader"):
         for th in (8, 16):
             loader_case(f"loader_c2_threads{th}", 4096, 512, th)

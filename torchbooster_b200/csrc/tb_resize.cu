@@ -514,7 +514,7 @@ template <typename T, int C, bool BOX, int NT>
 __global__ void __launch_bounds__(256) tb_resize_slide_kernel(RsParams p) {
     constexpr int G = NT / 4;
     constexpr int NQ = NT * C / 4;                   // aligned words of an NT-sample window after the shift
-    constexpr int UR = NT == 4 ? 4 : 2;              // input rows in flight per thread
+    constexpr int UR = NT == 4 ? 4 : 2;              // input rows per register buffer (two buffers)
     __shared__ T s_lut[C * 256];
     __shared__ uint32_t s_kyb[kSlideMaxTR][G][3];
     __shared__ int s_ytop[kSlideMaxTR];              // last input row an output row needs; -1: outside the resized image
@@ -628,12 +628,14 @@ __global__ void __launch_bounds__(256) tb_resize_slide_kernel(RsParams p) {
         // `rlim`: every load stays inside the image and what it returns is never weighted.
         const int rlim = min(last, in_h - 1);
         int next_top = s_ytop[yy];
-        uint32_t w[UR][NQ + 1];
+        // Two register buffers of UR rows each: the loads of the next rows are in flight while the
+        // current ones are consumed, so a warp does not sit out a DRAM round trip per batch.
+        uint32_t wa[UR][NQ + 1], wb[UR][NQ + 1];
 #pragma unroll
         for (int u = 0; u < UR; ++u)
 #pragma unroll
-            for (int i = 0; i <= NQ; ++i) w[u][i] = 0;
-        for (int r0 = first; r0 <= last; r0 += UR) {
+            for (int i = 0; i <= NQ; ++i) wa[u][i] = wb[u][i] = 0;
+        auto load = [&](uint32_t (&w)[UR][NQ + 1], int r0) {
 #pragma unroll
             for (int u = 0; u < UR; ++u) {
                 // one 32 x 32 -> 64-bit multiply-add per row (the host keeps the pitch below 4 GiB)
@@ -643,41 +645,51 @@ __global__ void __launch_bounds__(256) tb_resize_slide_kernel(RsParams p) {
 #pragma unroll
                 for (int i = 1; i <= NQ; ++i) tb_ldg_if(w[u][i], wp + i, i < nw1);     // words past the window keep stale bits: zero taps
             }
+        };
+        auto consume = [&](const uint32_t (&w)[UR][NQ + 1], int r0) {
 #pragma unroll
             for (int u = 0; u < UR; ++u) {
                 const int r = r0 + u;
-                if (r > last) break;
-                uint32_t q[NQ];
+                if (r <= last) {
+                    uint32_t q[NQ];
 #pragma unroll
-                for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[u][i], w[u][i + 1], sh1);
-                uint32_t h[C];
-                if (C == 3) {
-                    // samples of channel c sit at bytes c, c+3, c+6, c+9 of each 12-byte group of four pixels
-                    uint32_t p0[G], p1[G], p2[G];
+                    for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[u][i], w[u][i + 1], sh1);
+                    uint32_t h[C];
+                    if (C == 3) {
+                        // samples of channel c sit at bytes c, c+3, c+6, c+9 of each 12-byte group of four pixels
+                        uint32_t p0[G], p1[G], p2[G];
 #pragma unroll
-                    for (int g = 0; g < G; ++g) {
-                        p0[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0630), q[3 * g + 2], 0x5210);
-                        p1[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0741), q[3 * g + 2], 0x6210);
-                        p2[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0052), q[3 * g + 2], 0x7410);
+                        for (int g = 0; g < G; ++g) {
+                            p0[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0630), q[3 * g + 2], 0x5210);
+                            p1[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0741), q[3 * g + 2], 0x6210);
+                            p2[g] = __byte_perm(__byte_perm(q[3 * g], q[3 * g + 1], 0x0052), q[3 * g + 2], 0x7410);
+                        }
+                        h[0] = tb_dot<G>(p0, kbx);
+                        h[1 % C] = tb_dot<G>(p1, kbx);
+                        h[2 % C] = tb_dot<G>(p2, kbx);
+                    } else {
+                        h[0] = tb_dot<G>(q, kbx);
                     }
-                    h[0] = tb_dot<G>(p0, kbx);
-                    h[1 % C] = tb_dot<G>(p1, kbx);
-                    h[2 % C] = tb_dot<G>(p2, kbx);
-                } else {
-                    h[0] = tb_dot<G>(q, kbx);
-                }
-                // push: the window keeps rows r - NT + 1 .. r, oldest in byte 0
+                    // push: the window keeps rows r - NT + 1 .. r, oldest in byte 0
 #pragma unroll
-                for (int c = 0; c < C; ++c) {
+                    for (int c = 0; c < C; ++c) {
 #pragma unroll
-                    for (int g = 0; g + 1 < G; ++g) win[c][g] = __funnelshift_r(win[c][g], win[c][g + 1], 8);
-                    win[c][G - 1] = (win[c][G - 1] >> 8) | (h[c] << 24);
-                }
-                while (next_top == r) {
-                    emit(true);
-                    next_top = yy < nv ? s_ytop[yy] : 0x7fffffff;
+                        for (int g = 0; g + 1 < G; ++g) win[c][g] = __funnelshift_r(win[c][g], win[c][g + 1], 8);
+                        win[c][G - 1] = (win[c][G - 1] >> 8) | (h[c] << 24);
+                    }
+                    while (next_top == r) {
+                        emit(true);
+                        next_top = yy < nv ? s_ytop[yy] : 0x7fffffff;
+                    }
                 }
             }
+        };
+        load(wa, first);
+        for (int r0 = first; r0 <= last; r0 += 2 * UR) {
+            load(wb, r0 + UR);
+            consume(wa, r0);
+            load(wa, r0 + 2 * UR);
+            consume(wb, r0 + UR);
         }
         while (yy < nr) emit(false);
     }
@@ -697,16 +709,24 @@ int launch_slide(const RsParams& p, int64_t blocks, int threads, int nt, cudaStr
     return TB_OK;
 }
 
-// Strip geometry of the sliding-window kernel: CTA = min(out_w, 256) columns x TR output rows.
+// Strip geometry of the sliding-window kernel: CTA = TC output columns (one thread each) x TR output rows.
+// Taller strips recompute fewer halo rows (2 * TR + 2 input rows per TR outputs at scale 2), so TR is
+// the tallest that still puts a full GPU's worth of threads in the grid; small grids are then cut
+// into narrower column tiles until every SM has a few CTAs (measured on C4: batch 256 -> 32 x 256,
+// batch 32 -> 16 x 128).
 inline void slide_geometry(RsParams& p, int B, int sm_count, int flags, int64_t* blocks, int* threads) {
-    const int TC = p.out_w < 256 ? p.out_w : 256;
-    const int tiles_x = (p.out_w + TC - 1) / TC;
-    int TR = kSlideMaxTR;         // taller strips recompute fewer halo rows; keep >= 8 CTAs per SM in the grid
-    while (TR > 8 && (int64_t)B * tiles_x * ((p.out_h + TR - 1) / TR) < 8 * (int64_t)sm_count) TR >>= 1;
-    if ((flags >> 24) & 0xff) TR = (flags >> 24) & 0xff;      // development knob
+    const int64_t want_threads = (int64_t)sm_count * 1024 * 3 / 4;
+    int TR = kSlideMaxTR;
+    while (TR > 8 && (int64_t)B * ((p.out_h + TR - 1) / TR) * p.out_w < want_threads) TR >>= 1;
+    int TC = p.out_w < 256 ? p.out_w : 256;
+    while (TC > 64 && (int64_t)B * ((p.out_h + TR - 1) / TR) * ((p.out_w + TC - 1) / TC) < 4 * (int64_t)sm_count) TC = ((TC / 2 + 31) / 32) * 32;
+    if ((flags >> 24) & 0xff) TR = (flags >> 24) & 0xff;             // development knobs
+    if ((flags >> 16) & 0xff) TC = 32 * ((flags >> 16) & 0xff);
     if (TR > kSlideMaxTR) TR = kSlideMaxTR;
     if (TR > p.out_h) TR = p.out_h;
-    p.TR = TR; p.TC = TC; p.tiles_x = tiles_x; p.tiles_y = (p.out_h + TR - 1) / TR;
+    if (TC > 256) TC = 256;
+    if (TC > p.out_w) TC = p.out_w;
+    p.TR = TR; p.TC = TC; p.tiles_x = (p.out_w + TC - 1) / TC; p.tiles_y = (p.out_h + TR - 1) / TR;
     *blocks = (int64_t)B * p.tiles_x * p.tiles_y;
     *threads = ((TC + 31) / 32) * 32;
 }
