@@ -149,10 +149,11 @@ def test_images_owned_by_a_cluster(H, W, C, crop, dtype):
     assert same(got, want)
 
 
-@pytest.mark.parametrize("cluster", [2, 4, 8])
+@pytest.mark.parametrize("cluster", [0, 2, 4, 8])
 def test_forced_cluster_sizes_on_small_images(cluster):
-    """The development knob (flags bits 8-11) runs small images through the cluster path: odd chunk
-    boundaries, every operation, scalar and vector store paths."""
+    """The development knobs (flags bits 8-11: cluster size, bits 12-15: threads per CTA) run small
+    images through the cluster path and every block size: odd chunk boundaries, every operation,
+    scalar and vector store paths."""
     rng = np.random.default_rng(cluster)
     for (H, W, C) in ((32, 32, 3), (19, 23, 3), (28, 28, 1), (5, 7, 3)):
         B = 9
@@ -160,11 +161,12 @@ def test_forced_cluster_sizes_on_small_images(cluster):
         flip = rng.integers(0, 2, B).astype(np.uint8)
         ops = [[ALL_OPS[(5 * b + j) % len(ALL_OPS)] for j in range(5)] for b in range(B)]
         spec = TransformSpec(flip_p=0.5, rand_augment=True, mean=CIFAR[0][:C], std=CIFAR[1][:C])
-        bt = BatchTransform(spec, device="cuda")
-        bt.flags = cluster << 8
-        got = bt(torch.from_numpy(batch).cuda(), params=(None, None, flip, ops))
         want = TO.transform_batch(batch, flip=flip, ops=ops, mean=CIFAR[0][:C], std=CIFAR[1][:C])
-        assert same(got, want), (H, W, C)
+        for threads in (0, 2, 3, 4):                    # default, 256, 512, 1024
+            bt = BatchTransform(spec, device="cuda")
+            bt.flags = (cluster << 8) | (threads << 12)
+            got = bt(torch.from_numpy(batch).cuda(), params=(None, None, flip, ops))
+            assert same(got, want), (H, W, C, threads)
 
 
 def test_mnist_rand_augment_replayed():

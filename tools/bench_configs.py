@@ -165,7 +165,7 @@ def augment_imagenet_case(name, B, iters, flags=0):
                       "frac_measured": gbs / PEAK}), flush=True)
 
 
-def augment_case(name, B, iters, host_params=False):
+def augment_case(name, B, iters, host_params=False, flags=0):
     """The reference's CIFAR training transform (resnet.py:96-103): RandomCrop(32, 4, reflect), flip,
     RandomRotation(15), RandAugment(), normalise -> fp32; records pre-encoded on the device
     (kernel time) or drawn + encoded + uploaded every step (host_params)."""
@@ -177,6 +177,7 @@ def augment_case(name, B, iters, host_params=False):
     spec = TransformSpec(crop=32, padding=4, padding_mode="reflect", flip_p=.5, rotation=15, rand_augment=True,
                          mean=CIFAR[0], std=CIFAR[1])
     bt = BatchTransform(spec, device=dev, seed=42)
+    bt.flags = flags
     nbuf = 24
     gen = torch.Generator(device=dev).manual_seed(1234)
     srcs = [torch.randint(0, 256, (B, 32, 32, 3), dtype=torch.uint8, device=dev, generator=gen) for _ in range(nbuf)]
@@ -347,6 +348,12 @@ def main():
     if want("aug"):
         for bsz in (256, 2048, 16384):
             augment_case(f"aug_cifar_b{bsz}", bsz, 200 if bsz < 10000 else 50)
+        if a.quick:
+            for bsz in (256, 512, 2048):
+                for th in (2, 3, 4):
+                    augment_case(f"aug_cifar_b{bsz}_threads{64 << th}", bsz, 200, flags=th << 12)
+        augment_case("aug_cifar_b256_again", 256, 400)      # the first case of a process runs before the clocks have ramped
+        augment_case("aug_cifar_b512", 512, 400)
         augment_imagenet_case("aug_imagenet224_b512", 512, 30)
         for cl in (2, 4, 8):
             augment_imagenet_case(f"aug_imagenet224_b512_cluster{cl}", 512, 30, flags=cl << 8)
