@@ -53,6 +53,7 @@ struct AugParams {
     int plane;          // out_h * out_w
     int buf_bytes;      // bytes of one image buffer held by one CTA (multiple of 16): the whole image, or its chunk
     uint64_t magic;     // ceil(2^40 / buf_bytes) (cluster launches)
+    uint64_t wmagic;    // ceil(2^40 / out_w): pixel index -> row without a division
 };
 
 __device__ __forceinline__ int aug_fold(int i, int n, int mode, bool& inside) {
@@ -161,6 +162,7 @@ __global__ void __launch_bounds__(kAugMaxThreads) tb_augment_kernel(AugParams p)
     const int gt = rank * nt + tid, gn = S * nt;      // this thread among the image's threads
     const int C = p.C, plane = p.plane, W = p.out_w, H = p.out_h;
     const int total = C * plane;
+    const uint64_t wmagic = p.wmagic;
 
     {
         const T* __restrict__ glut = (const T*)p.lut;
@@ -174,14 +176,27 @@ __global__ void __launch_bounds__(kAugMaxThreads) tb_augment_kernel(AugParams p)
         const int left = (p.left ? p.left[b] : 0) - p.pad_x;
         const bool flip = p.flip ? (p.flip[b] != 0) : false;
         const uint8_t* __restrict__ img = p.src + (int64_t)b * p.bs;
-        for (int q = gt; q < plane; q += gn) {
-            const int y = q / W, x = q - y * W;
-            const int xs = flip ? W - 1 - x : x;
-            bool inside = true;
-            const int u = aug_fold(top + y, p.H, p.pad_mode, inside);
-            const int v = aug_fold(left + xs, p.W, p.pad_mode, inside);
-            const uint8_t* __restrict__ s = img + (int64_t)u * p.pitch + (int64_t)v * p.px_stride;
-            for (int c = 0; c < C; ++c) cur.st(c * plane + q, inside ? s[c * p.ch_stride] : (uint8_t)0);
+        constexpr int GU = 4;            // pixels whose loads are in flight together
+        for (int q0 = gt; q0 < plane; q0 += GU * gn) {
+            uint8_t px[GU][3];
+#pragma unroll
+            for (int k = 0; k < GU; ++k) {
+                const int q = min(q0 + k * gn, plane - 1);
+                const int y = (int)(((uint64_t)(uint32_t)q * wmagic) >> 40), x = q - y * W;      // q / W, exact for q < 2^20
+                const int xs = flip ? W - 1 - x : x;
+                bool inside = true;
+                const int u = aug_fold(top + y, p.H, p.pad_mode, inside);
+                const int v = aug_fold(left + xs, p.W, p.pad_mode, inside);
+                const uint8_t* __restrict__ s = img + (int64_t)u * p.pitch + (int64_t)v * p.px_stride;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) px[k][c] = (c < C && inside) ? s[c * p.ch_stride] : (uint8_t)0;
+            }
+#pragma unroll
+            for (int k = 0; k < GU; ++k) {
+                const int q = q0 + k * gn;
+                if (q < plane)
+                    for (int c = 0; c < C; ++c) cur.st(c * plane + q, px[k][c]);
+            }
         }
     }
     aug_sync<CL>();
@@ -196,7 +211,7 @@ __global__ void __launch_bounds__(kAugMaxThreads) tb_augment_kernel(AugParams p)
         case TB_AUG_AFFINE: {
             const uint32_t a0 = rec[1], a1 = rec[2], a2 = rec[3], a3 = rec[4], a4 = rec[5], a5 = rec[6];
             for (int q = gt; q < plane; q += gn) {
-                const int y = q / W, x = q - y * W;
+                const int y = (int)(((uint64_t)(uint32_t)q * wmagic) >> 40), x = q - y * W;      // q / W, exact for q < 2^20
                 const int xin = (int)(a2 + (uint32_t)x * a0 + (uint32_t)y * a1) >> 16;
                 const int yin = (int)(a5 + (uint32_t)x * a3 + (uint32_t)y * a4) >> 16;
                 const bool ok = (unsigned)xin < (unsigned)W && (unsigned)yin < (unsigned)H;
@@ -238,7 +253,7 @@ __global__ void __launch_bounds__(kAugMaxThreads) tb_augment_kernel(AugParams p)
         case TB_AUG_SHARPNESS: {
             const float k1 = __fdiv_rn(1.0f, 13.0f), k5 = __fdiv_rn(5.0f, 13.0f);
             for (int q = gt; q < plane; q += gn) {
-                const int y = q / W, x = q - y * W;
+                const int y = (int)(((uint64_t)(uint32_t)q * wmagic) >> 40), x = q - y * W;      // q / W, exact for q < 2^20
                 const bool interior = x >= 1 && x < W - 1 && y >= 1 && y < H - 1;
                 for (int c = 0; c < C; ++c) {
                     const int at = c * plane + q;
@@ -486,6 +501,7 @@ extern "C" int tb_augment_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int 
     p.plane = (int)plane;
     p.buf_bytes = (int)buf;
     p.magic = ((((uint64_t)1) << 40) + (uint64_t)buf - 1) / (uint64_t)buf;
+    p.wmagic = ((((uint64_t)1) << 40) + (uint64_t)out_w - 1) / (uint64_t)out_w;
     cudaStream_t s = (cudaStream_t)stream;
     // few images: more threads per image shorten every pass (a CTA walks its image pass by pass)
     int threads = kAugThreads;
