@@ -107,6 +107,7 @@ int lookup(const tb_lmdb* db, const void* key, size_t klen, const uint8_t** data
                 const uint8_t* nd = node(mid);
                 if (!nd) return -1;
                 const uint16_t ks = rd<uint16_t>(nd + 6);
+                if ((size_t)(nd - pg) + 8 + ks > db->psize) return -1;      // key runs off the page: corrupt
                 if (cmp_key(nd + 8, ks, key, klen) <= 0) { pick = mid; lo = mid + 1; }
                 else hi = mid - 1;
             }
@@ -122,6 +123,7 @@ int lookup(const tb_lmdb* db, const void* key, size_t klen, const uint8_t** data
             const uint8_t* nd = node(mid);
             if (!nd) return -1;
             const uint16_t ks = rd<uint16_t>(nd + 6);
+            if ((size_t)(nd - pg) + 8 + ks > db->psize) return -1;
             const int c = cmp_key(nd + 8, ks, key, klen);
             if (c == 0) {
                 const uint16_t nf = rd<uint16_t>(nd + 4);
