@@ -264,7 +264,7 @@ struct RowAcc {
 // ALIGNED: every row starts on a 16-byte boundary (base and row stride are multiples of 16
 // bytes), so the head / body / tail split is the same for all rows.
 template <int DT, bool ALIGNED>
-__global__ void __launch_bounds__(kMxThreads) tb_metrics_kernel(const void* __restrict__ logits, int64_t N, int C,
+__global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_kernel(const void* __restrict__ logits, int64_t N, int C,
                                                                 int64_t row_stride, const int64_t* __restrict__ labels,
                                                                 int k, unsigned long long* __restrict__ counters,
                                                                 unsigned long long* __restrict__ confusion) {
