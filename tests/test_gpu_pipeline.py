@@ -148,3 +148,17 @@ def test_in_place_records_equal_gathered(tmp_path):
     assert torch.cat([y for _, y in outs]).cpu().tolist() == [int(i) % 5 for i in order]
     with pytest.raises(KeyError):
         reader.record_offsets([0, n + 3], 64 * 80 * 3)
+
+
+def test_example_cifar_pipeline_runs():
+    """examples/cifar_pipeline.py: LMDB -> BatchLoader -> fused training transform -> stand-in model ->
+    MetricState / DeviceRunningAverage -> all_reduce, as a user would wire it."""
+    import importlib.util
+    from pathlib import Path
+    path = Path(__file__).resolve().parent.parent / "examples" / "cifar_pipeline.py"
+    spec = importlib.util.spec_from_file_location("cifar_pipeline_example", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    rep = mod.main(["--images", "1024", "--batch", "128", "--epochs", "2"])
+    assert rep["epoch"] == 1 and rep["images"] == 1024 and 0.0 <= rep["top1"] <= rep["top5"] <= 1.0
+    assert np.isfinite(rep["loss"]) and rep["images_per_s"] > 0
