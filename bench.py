@@ -485,7 +485,7 @@ def run_ours(args, wl):
     if world == 1 and not args.no_cpu:
         workers = min(host_threads(), 64)
         torch.set_num_threads(max(1, host_threads()))
-        ips, done, dt = cpu_path(wl, steps=max(40, 6 * workers), warmup=workers + 2, workers=workers,
+        ips, done, dt = cpu_path(wl, steps=max(80, 12 * workers), warmup=workers + 2, workers=workers,
                                  max_seconds=20.0)
         import torchvision
         cpu = {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
