@@ -274,6 +274,23 @@ TB_API int tb_to_image_stretch_u8_static(const float* src, int64_t images, int C
                                          const float* std, uint8_t* dst, tb_stream_t stream);
 
 /*
+ * The resize / resized-crop path over a RAGGED batch: images of different sizes (what the reference's
+ * datasets hand to T.Resize(size) + T.CenterCrop(size) -- examples/img_stt/adain/adain.py:170 on
+ * paintings and COCO photographs -- or to T.RandomResizedCrop, examples/img_stt/online/online.py:173),
+ * one launch, fixed output size.  Image b starts at src + offsets[b] with row pitch pitches[b]
+ * (all multiples of 4 bytes).  geometry[b] = {top, left, height, width of the source region;
+ * resized height, width of that region; y, x of the output window inside the resized region (may
+ * be negative or overhang: zero fill, T.CenterCrop's padding); image height, width}.  Taps are
+ * computed in the kernel exactly as Pillow does for (region size -> resized size).  max_taps: 4
+ * when every region is at most twice its resized size per axis, 8 when at most four times
+ * (a sample beyond that yields zeros; the host wrapper refuses such batches).
+ *   offsets : DEVICE int64[B]   pitches : DEVICE int32[B]   geometry : DEVICE int32[B][10]
+ */
+TB_API int tb_resize_crop_ragged_u8_to_nchw(
+    const uint8_t* src, const int64_t* offsets, const int32_t* pitches, int B, int C, const int32_t* geometry, int max_taps,
+    void* dst, int dst_dtype, int out_h, int out_w, const uint8_t* flip, const void* lut, int flags, tb_stream_t stream);
+
+/*
  * One pass over a logits matrix: top-1 and top-k correct counts and confusion-matrix bins.
  * Replaces torchbooster.metrics.accuracy (torchbooster/metrics.py:11-27: argmax == labels, sum)
  * -- the count, before the division -- and adds the top-k / confusion accumulators the north
@@ -344,6 +361,12 @@ TB_API int tb_lmdb_record_offsets(const tb_lmdb* db, const int64_t* indices, int
 TB_API int64_t tb_rrc_params_walk(const uint64_t* words, const double* area_cand, const double* aspect_cand,
                                   int64_t n_words, int64_t batch, int height, int width, double ratio_min,
                                   double ratio_max, double flip_p, int32_t* box, uint8_t* flip);
+/* The same walk over images of different sizes: scale_cand[w] is the uniform draw itself, multiplied
+ * here by sample b's own area heights[b] * widths[b] (host int32 arrays). */
+TB_API int64_t tb_rrc_params_walk_ragged(
+    const uint64_t* words, const double* scale_cand, const double* aspect_cand, int64_t n_words, int64_t batch,
+    const int32_t* heights, const int32_t* widths, double ratio_min, double ratio_max, double flip_p,
+    int32_t* box, uint8_t* flip);
 
 #ifdef __cplusplus
 }

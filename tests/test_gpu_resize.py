@@ -189,3 +189,54 @@ def test_resized_crop_edge_boxes_and_limits():
     big = torch.zeros((1, 200, 200, 3), dtype=torch.uint8, device="cuda")
     with pytest.raises(NotImplementedError, match="four times"):
         bt(big, params=(np.array([[0, 0, 200, 200]], np.int32), None))
+
+
+def _ragged_images(rng, sizes, C=3):
+    return [rng.integers(0, 256, (h, w, C), dtype=np.uint8) for h, w in sizes]
+
+
+@pytest.mark.parametrize("resize,cc,dtype", [(64, 64, torch.float32),          # adain.py:170 at a small size
+                                             (48, 40, torch.bfloat16), (40, 56, torch.float32)])   # crop smaller / larger than the resized image
+def test_ragged_resize_center_crop_vs_torchvision(resize, cc, dtype):
+    """T.Resize(int) + T.CenterCrop over images of DIFFERENT sizes in one launch: portrait, landscape,
+    square, up- and down-scaling (1x .. 3.9x), identity-sized ones, odd widths (padded pitches)."""
+    rng = np.random.default_rng(resize)
+    big = int(3.9 * resize)
+    sizes = [(97, 131), (131, 97), (64, 64), (50, 3 * resize), (big, 77), (resize, resize + 9), (40, 41), (big - 1, big), (33, 129)]
+    imgs = _ragged_images(rng, sizes)
+    spec = TransformSpec(resize=resize, center_crop=cc, mean=IMAGENET[0], std=IMAGENET[1], dtype=dtype)
+    got = BatchTransform(spec, device="cuda").ragged(imgs)
+    want = torch.stack([TO.transform_sample(im, resize=resize, center_crop=cc, mean=IMAGENET[0], std=IMAGENET[1], dtype=dtype)
+                        for im in imgs])
+    assert same(got, want)
+
+
+def test_ragged_random_resized_crop_vs_torchvision():
+    """T.RandomResizedCrop(96) + flip over differently sized images: the literal transform under
+    torch.manual_seed against one launch with replayed draws; grey images too."""
+    import torchvision.transforms as T
+    from PIL import Image
+    rng = np.random.default_rng(3)
+    for C in (3, 1):
+        sizes = [(int(h), int(w)) for h, w in zip(rng.integers(60, 300, 12), rng.integers(60, 300, 12))]
+        imgs = _ragged_images(rng, sizes, C)
+        mean, std = (IMAGENET if C == 3 else ((.5,), (.5,)))
+        compose = T.Compose([T.RandomResizedCrop(96), T.RandomHorizontalFlip(), T.ToTensor(), T.Normalize(mean, std)])
+        torch.manual_seed(1234)
+        want = torch.stack([compose(Image.fromarray(im if C == 3 else im[:, :, 0])) for im in imgs])
+        spec = TransformSpec(random_resized_crop=96, flip_p=.5, mean=mean, std=std)
+        got = BatchTransform(spec, device="cuda", seed=1234).ragged(imgs)
+        assert same(got, want), C
+
+
+def test_ragged_limits():
+    rng = np.random.default_rng(0)
+    bt = BatchTransform(TransformSpec(resize=32, center_crop=32), device="cuda")
+    with pytest.raises(NotImplementedError, match="four times"):
+        bt.ragged(_ragged_images(rng, [(64, 64), (200, 300)]))
+    with pytest.raises(ValueError, match="different output sizes"):
+        BatchTransform(TransformSpec(resize=32), device="cuda").ragged(_ragged_images(rng, [(64, 64), (64, 100)]))
+    with pytest.raises(NotImplementedError):
+        BatchTransform(TransformSpec(crop=16), device="cuda").ragged(_ragged_images(rng, [(64, 64)]))
+    one = BatchTransform(TransformSpec(resize=(20, 30)), device="cuda").ragged(_ragged_images(rng, [(64, 64), (40, 100)]))
+    assert tuple(one.shape) == (2, 3, 20, 30)

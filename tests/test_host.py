@@ -223,3 +223,27 @@ def test_resized_crop_replay_equals_torchvision_golden(golden):
         assert np.array_equal(np.concatenate([f1, f2]), want[:, 4]), name
     with pytest.raises(ValueError, match="excludes"):
         TransformSpec(random_resized_crop=24, crop=8)
+
+
+def test_resized_crop_replay_over_images_of_different_sizes():
+    """draw_ragged: every sample draws from its own size, in sequence, like T.RandomResizedCrop over a
+    dataset of differently sized images; two calls continue one word stream."""
+    import torchvision.transforms as T
+    from PIL import Image
+    from torchbooster_b200.transforms import ResizedCropParams
+    rng = np.random.default_rng(8)
+    hs, ws = rng.integers(8, 400, 300), rng.integers(8, 400, 300)
+    state = torch.get_rng_state()
+    try:
+        torch.manual_seed(99)
+        want, flips = [], []
+        for h, w in zip(hs, ws):
+            want.append(T.RandomResizedCrop.get_params(Image.new("L", (int(w), int(h))), [0.08, 1.0], [3 / 4, 4 / 3]))
+            flips.append(int(torch.rand(1) < 0.5))
+    finally:
+        torch.set_rng_state(state)
+    rp = ResizedCropParams(99)
+    b1, f1 = rp.draw_ragged(hs[:120], ws[:120], 0.5)
+    b2, f2 = rp.draw_ragged(hs[120:], ws[120:], 0.5)
+    assert np.array_equal(np.concatenate([b1, b2]), np.array(want, np.int32))
+    assert np.concatenate([f1, f2]).tolist() == flips

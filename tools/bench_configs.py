@@ -145,6 +145,43 @@ def rrc_case(name, B, iters, flags=0):
                       "frac_measured": gbs / PEAK, "alg_bytes_per_image": alg / B}), flush=True)
 
 
+def ragged_case(name, B, iters):
+    """T.Resize(256) + T.CenterCrop(256) + normalise over COCO-like images of different sizes (short side
+    360-640, aspect 0.6-1.7), packed back to back on the device: kernel time of the ragged launch."""
+    if CASE and CASE not in name:
+        return
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(0)
+    short = rng.integers(360, 641, B)
+    aspect = rng.uniform(1.0, 1.7, B)
+    land = rng.integers(0, 2, B).astype(bool)
+    hs = np.where(land, short, (short * aspect).astype(np.int64)).astype(np.int64)
+    ws = np.where(land, (short * aspect).astype(np.int64), short).astype(np.int64)
+    bt = BatchTransform(TransformSpec(resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1]), device=dev)
+    geom = np.zeros((B, 10), np.int32)
+    for b in range(B):
+        g = bt.geometry(int(hs[b]), int(ws[b]))
+        geom[b] = (0, 0, hs[b], ws[b], g["rs"][0], g["rs"][1], g["off"][0], g["off"][1], hs[b], ws[b])
+    pitches = ((ws * 3 + 3) // 4 * 4).astype(np.int32)
+    nbytes = (hs * pitches + 15) // 16 * 16
+    offsets = np.concatenate([[0], np.cumsum(nbytes)[:-1]]).astype(np.int64)
+    src = torch.randint(0, 256, (int(nbytes.sum()),), dtype=torch.uint8, device=dev)
+    d_off, d_pitch, d_geom = (torch.from_numpy(a).to(dev) for a in (offsets, pitches, geom))
+    out = torch.empty((B, 3, 256, 256), dtype=torch.float32, device=dev)
+    lut = bt.lut(3)
+    L = N.lib()
+    stream = N.current_stream_ptr(dev)
+
+    def run(i):
+        N.check(L.tb_resize_crop_ragged_u8_to_nchw(src.data_ptr(), d_off.data_ptr(), d_pitch.data_ptr(), B, 3, d_geom.data_ptr(), 8,
+                                                   out.data_ptr(), N.dtype_code(torch.float32), 256, 256, None, lut.data_ptr(), 0, stream))
+    ms = time_loop(run, iters)
+    alg = float((hs * ws * 3).sum()) + B * 256 * 256 * 12
+    gbs = alg / (ms * 1e-3) / 1e9
+    print(json.dumps({"case": name, "B": B, "ms": ms, "images_per_s": B / (ms * 1e-3), "alg_GBps": gbs, "frac_measured": gbs / PEAK,
+                      "source_MB": float(nbytes.sum()) / 1e6, "note": "whole source images counted as algorithmic bytes"}), flush=True)
+
+
 def augment_imagenet_case(name, B, iters, flags=0):
     """RandomCrop(224) of 256x256 + flip + RandAugment() + normalise -> bf16: each image is owned by a
     cluster of 2 CTAs (distributed shared memory)."""
@@ -337,6 +374,9 @@ def main():
         loader_case("loader_c2_in_place", 4096, 512, 8, in_place=True)
         loader_case("loader_cifar_aug_b256", 50000, 256, 8, cifar_aug=True)
         loader_case("loader_cifar_aug_b2048", 50000, 2048, 8, cifar_aug=True)
+    if want("ragged"):
+        ragged_case("ragged_coco_like_b32", 32, 100)
+        ragged_case("ragged_coco_like_b256", 256, 30)
     if want("rrc"):
         rrc_case("rrc_c2_b512", 512, 100)
         rrc_case("rrc_c2_b2048", 2048, 30)

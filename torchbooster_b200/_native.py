@@ -47,6 +47,7 @@ SIGNATURES = {
     "tb_channel_minmax": (_i32, [_vp, _i64, _i32, _i64, _vp, _vp]),
     "tb_to_image_u8": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp]),
     "tb_to_image_stretch_u8_static": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "tb_resize_crop_ragged_u8_to_nchw": (_i32, [_vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _i32, _vp]),
     "tb_metrics_update": (_i32, [_vp, _i32, _i64, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
     "tb_running_sum_update": (_i32, [_vp, _i32, _i64, _vp, _vp]),
     "tb_lmdb_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),
@@ -58,6 +59,7 @@ SIGNATURES = {
     "tb_lmdb_cuda_unregister": (_i32, [_vp]),
     "tb_lmdb_record_offsets": (_i32, [_vp, _vp, _i64, _i64, _vp]),
     "tb_rrc_params_walk": (_i64, [_vp, _vp, _vp, _i64, _i64, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
+    "tb_rrc_params_walk_ragged": (_i64, [_vp, _vp, _vp, _i64, _i64, _vp, _vp, C.c_double, C.c_double, C.c_double, _vp, _vp]),
 }
 
 

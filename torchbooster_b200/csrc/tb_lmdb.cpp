@@ -283,24 +283,27 @@ extern "C" int tb_lmdb_gather(const tb_lmdb* db, const int64_t* indices, int64_t
 // ----------------------------------------------------------------------------------------------
 #include <math.h>
 
-extern "C" int64_t tb_rrc_params_walk(const uint64_t* words, const double* area_cand, const double* aspect_cand,
-                                      int64_t n_words, int64_t batch, int height, int width, double ratio_min,
-                                      double ratio_max, double flip_p, int32_t* box, uint8_t* flip) {
-    if (!words || !area_cand || !aspect_cand || !box || !flip || batch < 0 || height < 1 || width < 1)
-        return tb_fail(TB_EINVAL, "tb_rrc_params_walk: bad argument");
+// One walk for both layouts: a uniform batch (area_cand[w] = area * u_w, computed by the caller) or a
+// ragged one (scale_cand[w] = u_w, multiplied here by every sample's own area).
+static int64_t rrc_walk(const uint64_t* words, const double* cand, bool cand_is_area, const double* aspect_cand,
+                        int64_t n_words, int64_t batch, const int32_t* heights, const int32_t* widths, int height,
+                        int width, double ratio_min, double ratio_max, double flip_p, int32_t* box, uint8_t* flip) {
     int64_t pos = 0;
     for (int64_t b = 0; b < batch; ++b) {
         if (pos + 23 > n_words) return tb_fail(TB_EINVAL, "tb_rrc_params_walk: not enough words");
+        const int H = heights ? heights[b] : height, W = widths ? widths[b] : width;
+        if (H < 1 || W < 1) return tb_fail(TB_EINVAL, "tb_rrc_params_walk: bad image size");
+        const double area = (double)H * (double)W;
         bool found = false;
         for (int attempt = 0; attempt < 10 && !found; ++attempt) {
-            const double ta = area_cand[pos], ar = aspect_cand[pos + 1];
+            const double ta = cand_is_area ? cand[pos] : area * cand[pos], ar = aspect_cand[pos + 1];
             pos += 2;
             // Python's int(round(x)): round half to even
             const long w = lrint(nearbyint(sqrt(ta * ar)));
             const long h = lrint(nearbyint(sqrt(ta / ar)));
-            if (w > 0 && w <= width && h > 0 && h <= height) {
-                box[4 * b + 0] = (int32_t)(words[pos] % (uint64_t)(height - h + 1));
-                box[4 * b + 1] = (int32_t)(words[pos + 1] % (uint64_t)(width - w + 1));
+            if (w > 0 && w <= W && h > 0 && h <= H) {
+                box[4 * b + 0] = (int32_t)(words[pos] % (uint64_t)(H - h + 1));
+                box[4 * b + 1] = (int32_t)(words[pos + 1] % (uint64_t)(W - w + 1));
                 box[4 * b + 2] = (int32_t)h;
                 box[4 * b + 3] = (int32_t)w;
                 pos += 2;
@@ -308,13 +311,13 @@ extern "C" int64_t tb_rrc_params_walk(const uint64_t* words, const double* area_
             }
         }
         if (!found) {   // central crop fallback
-            const double in_ratio = (double)width / (double)height;
+            const double in_ratio = (double)W / (double)H;
             long w, h;
-            if (in_ratio < ratio_min) { w = width; h = lrint(nearbyint((double)w / ratio_min)); }
-            else if (in_ratio > ratio_max) { h = height; w = lrint(nearbyint((double)h * ratio_max)); }
-            else { w = width; h = height; }
-            box[4 * b + 0] = (int32_t)((height - h) / 2);
-            box[4 * b + 1] = (int32_t)((width - w) / 2);
+            if (in_ratio < ratio_min) { w = W; h = lrint(nearbyint((double)w / ratio_min)); }
+            else if (in_ratio > ratio_max) { h = H; w = lrint(nearbyint((double)h * ratio_max)); }
+            else { w = W; h = H; }
+            box[4 * b + 0] = (int32_t)((H - h) / 2);
+            box[4 * b + 1] = (int32_t)((W - w) / 2);
             box[4 * b + 2] = (int32_t)h;
             box[4 * b + 3] = (int32_t)w;
         }
@@ -326,6 +329,25 @@ extern "C" int64_t tb_rrc_params_walk(const uint64_t* words, const double* area_
         }
     }
     return pos;
+}
+
+extern "C" int64_t tb_rrc_params_walk(const uint64_t* words, const double* area_cand, const double* aspect_cand,
+                                      int64_t n_words, int64_t batch, int height, int width, double ratio_min,
+                                      double ratio_max, double flip_p, int32_t* box, uint8_t* flip) {
+    if (!words || !area_cand || !aspect_cand || !box || !flip || batch < 0 || height < 1 || width < 1)
+        return tb_fail(TB_EINVAL, "tb_rrc_params_walk: bad argument");
+    return rrc_walk(words, area_cand, true, aspect_cand, n_words, batch, nullptr, nullptr, height, width, ratio_min,
+                    ratio_max, flip_p, box, flip);
+}
+
+extern "C" int64_t tb_rrc_params_walk_ragged(const uint64_t* words, const double* scale_cand, const double* aspect_cand,
+                                             int64_t n_words, int64_t batch, const int32_t* heights,
+                                             const int32_t* widths, double ratio_min, double ratio_max, double flip_p,
+                                             int32_t* box, uint8_t* flip) {
+    if (!words || !scale_cand || !aspect_cand || !box || !flip || batch < 0 || !heights || !widths)
+        return tb_fail(TB_EINVAL, "tb_rrc_params_walk_ragged: bad argument");
+    return rrc_walk(words, scale_cand, false, aspect_cand, n_words, batch, heights, widths, 0, 0, ratio_min, ratio_max,
+                    flip_p, box, flip);
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -87,6 +87,9 @@ struct RsParams {
     int row_bytes;     // bytes per intermediate row in shared memory (multiple of 4)
     int words_ok;      // source rows may be read as aligned 32-bit words
     const int32_t* box;  // resized-crop mode: per-sample source box [B][4] = top, left, height, width
+    int box_words;       // 4, or 10 for a ragged batch: + resized h, w, crop offset y, x, image h, w
+    const int64_t* offsets;   // ragged batch: byte offset of every image from src (else b * bs)
+    const int32_t* pitches;   // ragged batch: row pitch of every image in bytes (else pitch)
 };
 
 __device__ __forceinline__ uint8_t tb_clip8(int acc) {
@@ -527,26 +530,33 @@ __global__ void __launch_bounds__(256) tb_resize_slide_kernel(RsParams p) {
     const int b = t / p.tiles_y;
     const int x0 = tx * p.TC, y0 = ty * p.TR;
     const int nc = min(p.TC, p.out_w - x0), nr = min(p.TR, p.out_h - y0);
-    int box_top = 0, box_left = 0, in_h = p.H, in_w = p.W;
+    int box_top = 0, box_left = 0, in_h = p.H, in_w = p.W, rs_h = p.rs_h, rs_w = p.rs_w;
+    int oy = BOX ? 0 : (p.top ? p.top[b] : 0) + p.off_y;
+    int ox = BOX ? 0 : (p.left ? p.left[b] : 0) + p.off_x;
+    int frame_h = p.H, frame_w = p.W;
     if constexpr (BOX) {
-        box_top = p.box[4 * b]; box_left = p.box[4 * b + 1]; in_h = p.box[4 * b + 2]; in_w = p.box[4 * b + 3];
+        const int32_t* g = p.box + (int64_t)p.box_words * b;
+        box_top = g[0]; box_left = g[1]; in_h = g[2]; in_w = g[3];
+        if (p.box_words == 10) {         // ragged batch: this sample's own resized size, crop offset and image size
+            rs_h = g[4]; rs_w = g[5]; oy = g[6]; ox = g[7]; frame_h = g[8]; frame_w = g[9];
+        }
         // a box the host did not vouch for (outside the image, or too large for NT taps) yields zeros
-        if (box_top < 0 || box_left < 0 || in_h < 1 || in_w < 1 || box_top + in_h > p.H || box_left + in_w > p.W ||
-            in_h > (NT / 2) * p.rs_h || in_w > (NT / 2) * p.rs_w)
+        if (box_top < 0 || box_left < 0 || in_h < 1 || in_w < 1 || box_top + in_h > frame_h || box_left + in_w > frame_w ||
+            rs_h < 1 || rs_w < 1 || in_h > (NT / 2) * rs_h || in_w > (NT / 2) * rs_w)
             in_h = in_w = 0;
     }
-    const int oy = BOX ? 0 : (p.top ? p.top[b] : 0) + p.off_y;
-    const int ox = BOX ? 0 : (p.left ? p.left[b] : 0) + p.off_x;
     const bool flip = p.flip ? (p.flip[b] != 0) : false;
+    const uint8_t* simg = p.src + (p.offsets ? p.offsets[b] : (int64_t)b * p.bs);
+    const int64_t pitch = p.pitches ? (int64_t)p.pitches[b] : p.pitch;
 
     // ---- vertical taps of this strip's output rows
     if ((int)threadIdx.x < nr) {
         const int ry = oy + y0 + (int)threadIdx.x;
         int top = -1;
-        if (ry >= 0 && ry < p.rs_h && in_h > 0) {
+        if (ry >= 0 && ry < rs_h && in_h > 0) {
             TapN<NT> tp;
             if constexpr (BOX) {
-                tp = tb_bilinear_tap<NT>(in_h, p.rs_h, ry);
+                tp = tb_bilinear_tap<NT>(in_h, rs_h, ry);
             } else {
                 tp.xmin = p.by[2 * ry]; tp.n = p.by[2 * ry + 1];
 #pragma unroll
@@ -561,19 +571,19 @@ __global__ void __launch_bounds__(256) tb_resize_slide_kernel(RsParams p) {
     const bool active = (int)threadIdx.x < nc;
     const int x = x0 + (int)threadIdx.x;
     const int rx = ox + (flip ? p.out_w - 1 - x : x);
-    const bool colin = active && in_w > 0 && rx >= 0 && rx < p.rs_w;
+    const bool colin = active && in_w > 0 && rx >= 0 && rx < rs_w;
     // A column outside the resized image keeps all-zero taps: its horizontal results, its window
     // and its outputs are then 0 without any special casing below.
     uint32_t kbx[G][3];
 #pragma unroll
     for (int g = 0; g < G; ++g) kbx[g][0] = kbx[g][1] = kbx[g][2] = 0;
     int a1 = 0, nw1 = 1;
-    const int64_t pitch_w = p.pitch >> 2;
-    const uint32_t* wbase = reinterpret_cast<const uint32_t*>(p.src + (int64_t)b * p.bs);      // always a readable word
+    const int64_t pitch_w = pitch >> 2;
+    const uint32_t* wbase = reinterpret_cast<const uint32_t*>(simg);      // always a readable word
     if (colin) {
         TapN<NT> tp;
         if constexpr (BOX) {
-            tp = tb_bilinear_tap<NT>(in_w, p.rs_w, rx);
+            tp = tb_bilinear_tap<NT>(in_w, rs_w, rx);
         } else {
             tp.xmin = p.bx[2 * rx]; tp.n = p.bx[2 * rx + 1];
 #pragma unroll
@@ -583,10 +593,10 @@ __global__ void __launch_bounds__(256) tb_resize_slide_kernel(RsParams p) {
         const int boff = (box_left + tp.xmin) * C;
         a1 = boff & 3;
         nw1 = (a1 + tp.n * C + 3) >> 2;                  // words that hold this window (1 .. NQ + 1)
-        wbase = reinterpret_cast<const uint32_t*>(p.src + (int64_t)b * p.bs + (boff - a1)) + (int64_t)box_top * pitch_w;
+        wbase = reinterpret_cast<const uint32_t*>(simg + (boff - a1)) + (int64_t)box_top * pitch_w;
     }
     const int sh1 = a1 * 8;
-    const uint32_t pitch_b = (uint32_t)p.pitch;
+    const uint32_t pitch_b = (uint32_t)pitch;
     const int64_t plane = (int64_t)p.out_h * p.out_w;
     T* d[C];
 #pragma unroll
@@ -787,7 +797,7 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     int rc = tb_device(&dev);
     if (rc) return rc;
 
-    RsParams p;
+    RsParams p = {};
     p.src = src; p.B = B; p.H = H; p.W = W; p.bs = src_batch_stride; p.pitch = src_row_pitch;
     p.rs_h = rs_h; p.rs_w = rs_w;
     p.bx = bounds_x; p.kx = taps_x; p.ksx = ks_x; p.by = bounds_y; p.ky = taps_y; p.ksy = ks_y;
@@ -894,7 +904,7 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
     p.src = src; p.B = B; p.H = H; p.W = W; p.bs = src_batch_stride; p.pitch = src_row_pitch;
     p.rs_h = out_h; p.rs_w = out_w;
     p.dst = dst; p.out_h = out_h; p.out_w = out_w;
-    p.flip = flip; p.lut = lut; p.box = box; p.words_ok = 1;
+    p.flip = flip; p.lut = lut; p.box = box; p.box_words = 4; p.words_ok = 1;
     if (!(flags & TB_FLAG_TWO_PHASE) && src_row_pitch < ((int64_t)1 << 32)) {
         int64_t blocks = 0;
         int threads = 0;
@@ -941,4 +951,39 @@ extern "C" int tb_resized_crop_bilinear_u8_nhwc_to_nchw(const uint8_t* src, int 
                            : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, true, nt, s);
     return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, true, nt, s)
                : launch_resize<uint16_t, 1>(p, smem, blocks, dev.max_smem_optin, true, nt, s);
+}
+
+// Ragged batch: every sample has its own image size, source region, resized size and crop offset
+// (T.Resize(int) + T.CenterCrop, or T.RandomResizedCrop, over images of different sizes).
+extern "C" int tb_resize_crop_ragged_u8_to_nchw(const uint8_t* src, const int64_t* offsets, const int32_t* pitches, int B,
+                                                int C, const int32_t* geometry, int max_taps, void* dst, int dst_dtype,
+                                                int out_h, int out_w, const uint8_t* flip, const void* lut, int flags,
+                                                tb_stream_t stream) {
+    TB_REQUIRE(B >= 0, "tb_resize_crop_ragged: negative B");
+    TB_REQUIRE(C == 1 || C == 3, "tb_resize_crop_ragged: C=%d not supported (Pillow premultiplies alpha for RGBA); use C in {1,3}", C);
+    TB_REQUIRE(out_h >= 1 && out_w >= 1, "tb_resize_crop_ragged: bad output size");
+    TB_REQUIRE(max_taps == 4 || max_taps == 8, "tb_resize_crop_ragged: max_taps is 4 (every scale <= 2) or 8 (<= 4)");
+    TB_REQUIRE(dst_dtype == TB_U8 || tb_dtype_size(dst_dtype) != 0, "tb_resize_crop_ragged: unknown dst_dtype %d", dst_dtype);
+    if (B == 0) return TB_OK;
+    TB_REQUIRE(src && offsets && pitches && geometry && dst && lut, "tb_resize_crop_ragged: NULL argument");
+    TB_REQUIRE(((uintptr_t)src & 3) == 0, "tb_resize_crop_ragged: src must be 4-byte aligned (and every offset / pitch a multiple of 4)");
+    TB_REQUIRE(dst_dtype == TB_U8 || ((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_resize_crop_ragged: dst misaligned for its dtype");
+    TbDevice dev;
+    int rc = tb_device(&dev);
+    if (rc) return rc;
+    RsParams p = {};
+    p.src = src; p.B = B; p.offsets = offsets; p.pitches = pitches;
+    p.rs_h = out_h; p.rs_w = out_w;
+    p.dst = dst; p.out_h = out_h; p.out_w = out_w;
+    p.flip = flip; p.lut = lut; p.box = geometry; p.box_words = 10; p.words_ok = 1;
+    int64_t blocks = 0;
+    int threads = 0;
+    slide_geometry(p, B, dev.sm_count, flags, &blocks, &threads);
+    TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize_crop_ragged: grid too large");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dst_dtype == TB_U8)
+        return C == 3 ? launch_slide<uint8_t, 3>(p, blocks, threads, max_taps, s) : launch_slide<uint8_t, 1>(p, blocks, threads, max_taps, s);
+    if (dst_dtype == TB_F32)
+        return C == 3 ? launch_slide<float, 3>(p, blocks, threads, max_taps, s) : launch_slide<float, 1>(p, blocks, threads, max_taps, s);
+    return C == 3 ? launch_slide<uint16_t, 3>(p, blocks, threads, max_taps, s) : launch_slide<uint16_t, 1>(p, blocks, threads, max_taps, s);
 }

@@ -221,6 +221,34 @@ class ResizedCropParams:
         self._words = words[used:]
         return box, flip
 
+    def draw_ragged(self, heights, widths, flip_p: Optional[float] = None):
+        """``ResizedCropParams.draw`` for images of different sizes: sample ``b`` draws from its own
+        ``heights[b] x widths[b]``.  Returns numpy ``(box int32[B,4], flip uint8[B])``."""
+        heights = np.ascontiguousarray(np.asarray(heights, np.int32))
+        widths = np.ascontiguousarray(np.asarray(widths, np.int32))
+        batch = int(heights.shape[0])
+        s0, s1 = np.float32(self.scale[0]), np.float32(self.scale[1])
+        box = np.zeros((batch, 4), np.int32)
+        flip = np.zeros(batch, np.uint8)
+        if batch == 0:
+            return box, flip
+        need = batch * 6 + 64
+        walk = N.lib().tb_rrc_params_walk_ragged
+        while True:
+            words = np.ascontiguousarray(self._take(need))
+            u_all = self._uniform(words, s0, s1).astype(np.float64)
+            ar_all = torch.exp(torch.from_numpy(self._uniform(words, self._lr[0], self._lr[1]))).numpy().astype(np.float64)
+            used = walk(words.ctypes.data, u_all.ctypes.data, ar_all.ctypes.data, words.shape[0], batch, heights.ctypes.data,
+                        widths.ctypes.data, min(self.ratio), max(self.ratio), -1.0 if flip_p is None else float(flip_p),
+                        box.ctypes.data, flip.ctypes.data)
+            if used >= 0:
+                break
+            need = words.shape[0] * 2 + 23 * batch
+            if need > 64 * (23 * batch + 64):
+                N.check(int(used))
+        self._words = words[used:]
+        return box, flip
+
 
 class BatchTransform:
     """``uint8 [B,H,W,C]`` -> ``[B,C,h,w]`` on the GPU, bit-identical to the reference pipeline.
@@ -469,6 +497,93 @@ class BatchTransform:
                 crop.data_ptr(), B, out_h, out_w, Cn, Cn * out_h * out_w, out_w, out.data_ptr(), N.dtype_code(sp.dtype),
                 out_h, out_w, None, None, None, 0, 0, N.PAD_MODES["none"], rec.data_ptr(), int(rec.shape[1]),
                 lut.data_ptr(), N.FLAG_SRC_PLANAR, stream))
+        return out
+
+    # -- ragged batches --------------------------------------------------------------------
+    def ragged(self, images, params=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """A batch of images of DIFFERENT sizes (what the reference's datasets really hold: paintings and
+        COCO photographs under ``T.Resize(size) + T.CenterCrop(size)``, ``adain.py:170``; ImageNet-style
+        ``T.RandomResizedCrop``) -> one ``[B,C,h,w]`` tensor, one launch.
+
+        ``images``: sequence of ``uint8 [H_b, W_b, C]`` host arrays / tensors.  Supported pipelines:
+        ``resize`` (+ ``center_crop``) with a common output size, and ``random_resized_crop`` (+ flip);
+        ``params=(boxes[B,4], flip)`` or a seed for the latter.  Every sample's taps are computed in the
+        kernel for its own (size -> resized size); reductions beyond 4x are refused.
+        """
+        sp = self.spec
+        rrc = sp.random_resized_crop is not None
+        if sp.augments or sp.pre_rotation is not None or sp.crop is not None or _pair(sp.padding) != (0, 0) or \
+                (not rrc and sp.resize is None):
+            raise NotImplementedError("ragged batches: resize (+ center_crop) or random_resized_crop (+ flip) pipelines")
+        arrs = [np.ascontiguousarray(im.numpy() if isinstance(im, torch.Tensor) else np.asarray(im)) for im in images]
+        B = len(arrs)
+        if B == 0:
+            raise ValueError("ragged() needs at least one image")
+        Cn = arrs[0].shape[2] if arrs[0].ndim == 3 else 0
+        for a in arrs:
+            if a.dtype != np.uint8 or a.ndim != 3 or a.shape[2] != Cn:
+                raise TypeError("images must be uint8 [H,W,C] arrays with the same channel count")
+        sizes = np.array([a.shape[:2] for a in arrs], np.int64)
+        # ---- per-sample geometry ---------------------------------------------------------
+        geom = np.zeros((B, 10), np.int32)
+        geom[:, 8:10] = sizes
+        flip = None
+        if rrc:
+            out_h, out_w = _pair(sp.random_resized_crop)
+            if params is None:
+                if self._rng is None:
+                    raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
+                params = self._rng.draw_ragged(sizes[:, 0], sizes[:, 1], sp.flip_p)
+            box, flip = params
+            geom[:, 0:4] = np.asarray(box, np.int32).reshape(B, 4)
+            geom[:, 4], geom[:, 5] = out_h, out_w
+        else:
+            fixed = None
+            for b, (h, w) in enumerate(sizes):
+                g = self.geometry(int(h), int(w))
+                geom[b, 0:4] = (0, 0, h, w)
+                geom[b, 4:6] = g["rs"]
+                geom[b, 6:8] = g["off"]
+                if fixed is None:
+                    fixed = g["out"]
+                elif fixed != g["out"]:
+                    raise ValueError(f"images resize to different output sizes ({fixed} and {g['out']}); add center_crop")
+            out_h, out_w = fixed
+        too_big = (geom[:, 2] > 4 * geom[:, 4]) | (geom[:, 3] > 4 * geom[:, 5])
+        if too_big.any():
+            b = int(np.argmax(too_big))
+            raise NotImplementedError(f"image {b}: a {geom[b, 2]}x{geom[b, 3]} region to {geom[b, 4]}x{geom[b, 5]} is more than "
+                                      "four times the output; reductions beyond 4x are not built for ragged batches")
+        taps = 4 if ((geom[:, 2] <= 2 * geom[:, 4]) & (geom[:, 3] <= 2 * geom[:, 5])).all() else 8
+        # ---- pack: rows padded to 4 bytes, images to 16 -----------------------------------
+        pitches = ((sizes[:, 1] * Cn + 3) // 4 * 4).astype(np.int32)
+        nbytes = (sizes[:, 0] * pitches + 15) // 16 * 16
+        offsets = np.concatenate([[0], np.cumsum(nbytes)[:-1]]).astype(np.int64)
+        host = torch.empty(int(nbytes.sum()), dtype=torch.uint8, pin_memory=True)
+        hv = host.numpy()
+        for a, off, pitch in zip(arrs, offsets, pitches):
+            h, w = a.shape[:2]
+            hv[off:off + h * pitch].reshape(h, pitch)[:, :w * Cn] = a.reshape(h, w * Cn)
+        meta = torch.empty(B * (8 + 4 + 40 + 1), dtype=torch.uint8, pin_memory=True)       # offsets | pitches | geometry | flip
+        mv = meta.numpy()
+        mv[:8 * B].view(np.int64)[:] = offsets
+        mv[8 * B:12 * B].view(np.int32)[:] = pitches
+        mv[12 * B:52 * B].view(np.int32)[:] = geom.reshape(-1)
+        mv[52 * B:] = 0 if flip is None else np.asarray(flip, np.uint8)
+        self._ragged_hosts = (host, meta)                   # pinned sources stay alive until the copies have run
+        dsrc = host.to(self.device, non_blocking=True)
+        dmeta = meta.to(self.device, non_blocking=True)
+        if out is None:
+            out = torch.empty((B, Cn, out_h, out_w), dtype=sp.dtype, device=self.device)
+        elif tuple(out.shape) != (B, Cn, out_h, out_w) or out.dtype != sp.dtype or not out.is_contiguous() or out.device != self.device:
+            raise ValueError(f"out must be a contiguous tensor of shape {(B, Cn, out_h, out_w)}, dtype {sp.dtype} on {self.device}")
+        lut = self.lut(Cn)
+        base = dmeta.data_ptr()
+        with torch.cuda.device(self.device):
+            N.check(N.lib().tb_resize_crop_ragged_u8_to_nchw(
+                dsrc.data_ptr(), base, base + 8 * B, B, Cn, base + 12 * B, taps, out.data_ptr(), N.dtype_code(sp.dtype),
+                out_h, out_w, None if flip is None else base + 52 * B, lut.data_ptr(), self.flags,
+                N.current_stream_ptr(self.device)))
         return out
 
     # -- the call --------------------------------------------------------------------------
