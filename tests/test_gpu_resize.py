@@ -231,9 +231,17 @@ def test_ragged_random_resized_crop_vs_torchvision():
 
 def test_ragged_limits():
     rng = np.random.default_rng(0)
-    bt = BatchTransform(TransformSpec(resize=32, center_crop=32), device="cuda")
-    with pytest.raises(NotImplementedError, match="four times"):
-        bt.ragged(_ragged_images(rng, [(64, 64), (200, 300)]))
+    # regions beyond 4x take the any-scale kernel, one launch each, inside the same call
+    big = _ragged_images(rng, [(64, 64), (200, 300), (90, 77), (500, 131), (33, 400)])
+    spec = TransformSpec(resize=32, center_crop=32, mean=IMAGENET[0], std=IMAGENET[1])
+    want = torch.stack([TO.transform_sample(im, resize=32, center_crop=32, mean=IMAGENET[0], std=IMAGENET[1]) for im in big])
+    assert same(BatchTransform(spec, device="cuda").ragged(big), want)
+    boxes = np.array([[0, 0, 64, 64], [10, 20, 180, 260], [5, 5, 80, 70], [100, 3, 390, 120], [1, 100, 30, 250]], np.int32)
+    flip = np.array([0, 1, 1, 0, 1], np.uint8)
+    spec = TransformSpec(random_resized_crop=24, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1])
+    want = torch.stack([TO.transform_sample(im, resized_crop=tuple(int(v) for v in bx) + (24, 24), flip=bool(f), mean=IMAGENET[0],
+                                            std=IMAGENET[1]) for im, bx, f in zip(big, boxes, flip)])
+    assert same(BatchTransform(spec, device="cuda").ragged(big, params=(boxes, flip)), want)
     with pytest.raises(ValueError, match="different output sizes"):
         BatchTransform(TransformSpec(resize=32), device="cuda").ragged(_ragged_images(rng, [(64, 64), (64, 100)]))
     with pytest.raises(NotImplementedError):

@@ -508,7 +508,8 @@ class BatchTransform:
         ``images``: sequence of ``uint8 [H_b, W_b, C]`` host arrays / tensors.  Supported pipelines:
         ``resize`` (+ ``center_crop``) with a common output size, and ``random_resized_crop`` (+ flip);
         ``params=(boxes[B,4], flip)`` or a seed for the latter.  Every sample's taps are computed in the
-        kernel for its own (size -> resized size); reductions beyond 4x are refused.
+        kernel for its own (size -> resized size); a region more than four times its resized size gets its
+        own launch of the any-scale kernel inside the same call.
         """
         sp = self.spec
         rrc = sp.random_resized_crop is not None
@@ -549,12 +550,13 @@ class BatchTransform:
                 elif fixed != g["out"]:
                     raise ValueError(f"images resize to different output sizes ({fixed} and {g['out']}); add center_crop")
             out_h, out_w = fixed
+        # regions more than four times their resized size do not fit the eight-tap kernel: the common launch
+        # skips them (an empty region writes zeros) and each gets a launch of the any-scale kernel below
         too_big = (geom[:, 2] > 4 * geom[:, 4]) | (geom[:, 3] > 4 * geom[:, 5])
-        if too_big.any():
-            b = int(np.argmax(too_big))
-            raise NotImplementedError(f"image {b}: a {geom[b, 2]}x{geom[b, 3]} region to {geom[b, 4]}x{geom[b, 5]} is more than "
-                                      "four times the output; reductions beyond 4x are not built for ragged batches")
-        taps = 4 if ((geom[:, 2] <= 2 * geom[:, 4]) & (geom[:, 3] <= 2 * geom[:, 5])).all() else 8
+        slow = [(int(b), geom[b].copy()) for b in np.nonzero(too_big)[0]]
+        geom[too_big, 2:4] = 0
+        ok = ~too_big
+        taps = 4 if ((geom[ok, 2] <= 2 * geom[ok, 4]) & (geom[ok, 3] <= 2 * geom[ok, 5])).all() else 8
         # ---- pack: rows padded to 4 bytes, images to 16 -----------------------------------
         pitches = ((sizes[:, 1] * Cn + 3) // 4 * 4).astype(np.int32)
         nbytes = (sizes[:, 0] * pitches + 15) // 16 * 16
@@ -584,6 +586,16 @@ class BatchTransform:
                 dsrc.data_ptr(), base, base + 8 * B, B, Cn, base + 12 * B, taps, out.data_ptr(), N.dtype_code(sp.dtype),
                 out_h, out_w, None if flip is None else base + 52 * B, lut.data_ptr(), self.flags,
                 N.current_stream_ptr(self.device)))
+            for b, g in slow:           # any-scale kernel, host-built taps (cached per size pair), one sample per launch
+                top, left, in_h, in_w, rs_h, rs_w, oy, ox = (int(v) for v in g[:8])
+                ksx, bx, kx = self._resize_taps(in_w, rs_w) if rs_w != in_w else (0, None, None)
+                ksy, by, ky = self._resize_taps(in_h, rs_h) if rs_h != in_h else (0, None, None)
+                ptr = lambda t: None if t is None else t.data_ptr()
+                N.check(N.lib().tb_resize_bilinear_u8_nhwc_to_nchw(
+                    dsrc.data_ptr() + int(offsets[b]) + top * int(pitches[b]) + left * Cn, 1, in_h, in_w, Cn, 0, int(pitches[b]),
+                    rs_h, rs_w, ptr(bx), ptr(kx), ksx, ptr(by), ptr(ky), ksy, out[b].data_ptr(), N.dtype_code(sp.dtype),
+                    out_h, out_w, None, None, None if flip is None else int(base + 52 * B + b), oy, ox, lut.data_ptr(), self.flags,
+                    N.current_stream_ptr(self.device)))
         return out
 
     # -- the call --------------------------------------------------------------------------
