@@ -185,10 +185,26 @@ def test_resized_crop_edge_boxes_and_limits():
         bad = boxes.copy(); bad[0] = [60, 60, 10, 10]
         out = bt(torch.from_numpy(batch).cuda(), params=(bad, flip))
         assert same(out[1:], want[1:]) and bool((out[0] == bt.lut(3)[:, 0].view(3, 1, 1)).all())
-    # reductions beyond 4x are not built for per-sample boxes
-    big = torch.zeros((1, 200, 200, 3), dtype=torch.uint8, device="cuda")
-    with pytest.raises(NotImplementedError, match="four times"):
-        bt(big, params=(np.array([[0, 0, 200, 200]], np.int32), None))
+    # frames more than 4x the output (the uniform entry point refuses them) go through per-sample records;
+    # boxes beyond 4x take the any-scale kernel; rows that are not 4-byte aligned are re-pitched
+    for (Hb, Wb) in ((200, 200), (150, 201)):
+        big = rng.integers(0, 256, (3, Hb, Wb, 3), dtype=np.uint8)
+        bx = np.array([[0, 0, Hb, Wb], [20, 30, 100, 90], [7, 11, Hb - 10, 150]], np.int32)
+        fl = np.array([1, 0, 1], np.uint8)
+        want = TO.transform_batch(big, boxes=bx, out_size=(S, S), flip=fl, mean=IMAGENET[0], std=IMAGENET[1])
+        got = bt(torch.from_numpy(big).cuda(), params=(bx, fl))
+        assert same(got, want), (Hb, Wb, [int((got[b].cpu() != want[b]).sum()) for b in range(3)])
+        outside = bx.copy(); outside[2] = [7, 11, Hb, 150]              # leaves the image: zeros, nothing read out of bounds
+        got = bt(torch.from_numpy(big).cuda(), params=(outside, fl))
+        assert same(got[:2], want[:2]) and bool((got[2] == bt.lut(3)[:, 0].view(3, 1, 1)).all())
+    with pytest.raises(NotImplementedError, match="four times"):     # the C entry point itself still says so
+        from torchbooster_b200 import _native as N
+        z = torch.zeros((1, 200, 200, 3), dtype=torch.uint8, device="cuda")
+        o = torch.empty((1, 3, S, S), device="cuda")
+        bxd = torch.tensor([[0, 0, 200, 200]], dtype=torch.int32, device="cuda")
+        N.check(N.lib().tb_resized_crop_bilinear_u8_nhwc_to_nchw(z.data_ptr(), 1, 200, 200, 3, z.stride(0), z.stride(1), bxd.data_ptr(),
+                                                                o.data_ptr(), 0, S, S, None, bt.lut(3).data_ptr(), 0,
+                                                                N.current_stream_ptr(z.device)))
 
 
 def _ragged_images(rng, sizes, C=3):

@@ -550,13 +550,6 @@ class BatchTransform:
                 elif fixed != g["out"]:
                     raise ValueError(f"images resize to different output sizes ({fixed} and {g['out']}); add center_crop")
             out_h, out_w = fixed
-        # regions more than four times their resized size do not fit the eight-tap kernel: the common launch
-        # skips them (an empty region writes zeros) and each gets a launch of the any-scale kernel below
-        too_big = (geom[:, 2] > 4 * geom[:, 4]) | (geom[:, 3] > 4 * geom[:, 5])
-        slow = [(int(b), geom[b].copy()) for b in np.nonzero(too_big)[0]]
-        geom[too_big, 2:4] = 0
-        ok = ~too_big
-        taps = 4 if ((geom[ok, 2] <= 2 * geom[ok, 4]) & (geom[ok, 3] <= 2 * geom[ok, 5])).all() else 8
         # ---- pack: rows padded to 4 bytes, images to 16 -----------------------------------
         pitches = ((sizes[:, 1] * Cn + 3) // 4 * 4).astype(np.int32)
         nbytes = (sizes[:, 0] * pitches + 15) // 16 * 16
@@ -566,14 +559,35 @@ class BatchTransform:
         for a, off, pitch in zip(arrs, offsets, pitches):
             h, w = a.shape[:2]
             hv[off:off + h * pitch].reshape(h, pitch)[:, :w * Cn] = a.reshape(h, w * Cn)
+        self._ragged_host = host                            # the pinned source stays alive until the copy has run
+        dsrc = host.to(self.device, non_blocking=True)
+        return self._launch_ragged(dsrc, offsets, pitches, geom, flip, Cn, out_h, out_w, out)
+
+    def _launch_ragged(self, dsrc: torch.Tensor, offsets: np.ndarray, pitches: np.ndarray, geom: np.ndarray, flip, Cn: int,
+                       out_h: int, out_w: int, out: Optional[torch.Tensor]) -> torch.Tensor:
+        """Per-sample geometry records over device memory ``dsrc``: one launch of the eight-tap kernel for
+        every region within 4x of its resized size, one launch of the any-scale kernel for each of the rest."""
+        sp = self.spec
+        B = int(geom.shape[0])
+        geom = geom.copy()
+        # regions more than four times their resized size do not fit the eight-tap kernel: the common launch
+        # skips them (an empty region writes zeros) and each gets a launch of the any-scale kernel below
+        too_big = (geom[:, 2] > 4 * geom[:, 4]) | (geom[:, 3] > 4 * geom[:, 5])
+        # a region that leaves its image stays with the common launch, which writes zeros for it
+        inside = (geom[:, 0] >= 0) & (geom[:, 1] >= 0) & (geom[:, 2] >= 1) & (geom[:, 3] >= 1) & \
+                 (geom[:, 0] + geom[:, 2] <= geom[:, 8]) & (geom[:, 1] + geom[:, 3] <= geom[:, 9])
+        too_big &= inside
+        slow = [(int(b), geom[b].copy()) for b in np.nonzero(too_big)[0]]
+        geom[too_big, 2:4] = 0
+        ok = ~too_big
+        taps = 4 if ((geom[ok, 2] <= 2 * geom[ok, 4]) & (geom[ok, 3] <= 2 * geom[ok, 5])).all() else 8
         meta = torch.empty(B * (8 + 4 + 40 + 1), dtype=torch.uint8, pin_memory=True)       # offsets | pitches | geometry | flip
         mv = meta.numpy()
         mv[:8 * B].view(np.int64)[:] = offsets
         mv[8 * B:12 * B].view(np.int32)[:] = pitches
         mv[12 * B:52 * B].view(np.int32)[:] = geom.reshape(-1)
         mv[52 * B:] = 0 if flip is None else np.asarray(flip, np.uint8)
-        self._ragged_hosts = (host, meta)                   # pinned sources stay alive until the copies have run
-        dsrc = host.to(self.device, non_blocking=True)
+        self._ragged_meta = meta                            # pinned source stays alive until the copy has run
         dmeta = meta.to(self.device, non_blocking=True)
         if out is None:
             out = torch.empty((B, Cn, out_h, out_w), dtype=sp.dtype, device=self.device)
@@ -581,21 +595,21 @@ class BatchTransform:
             raise ValueError(f"out must be a contiguous tensor of shape {(B, Cn, out_h, out_w)}, dtype {sp.dtype} on {self.device}")
         lut = self.lut(Cn)
         base = dmeta.data_ptr()
+        ptr = lambda t: None if t is None else t.data_ptr()
         with torch.cuda.device(self.device):
+            stream = N.current_stream_ptr(self.device)
             N.check(N.lib().tb_resize_crop_ragged_u8_to_nchw(
                 dsrc.data_ptr(), base, base + 8 * B, B, Cn, base + 12 * B, taps, out.data_ptr(), N.dtype_code(sp.dtype),
-                out_h, out_w, None if flip is None else base + 52 * B, lut.data_ptr(), self.flags,
-                N.current_stream_ptr(self.device)))
+                out_h, out_w, None if flip is None else base + 52 * B, lut.data_ptr(), self.flags, stream))
             for b, g in slow:           # any-scale kernel, host-built taps (cached per size pair), one sample per launch
                 top, left, in_h, in_w, rs_h, rs_w, oy, ox = (int(v) for v in g[:8])
                 ksx, bx, kx = self._resize_taps(in_w, rs_w) if rs_w != in_w else (0, None, None)
                 ksy, by, ky = self._resize_taps(in_h, rs_h) if rs_h != in_h else (0, None, None)
-                ptr = lambda t: None if t is None else t.data_ptr()
                 N.check(N.lib().tb_resize_bilinear_u8_nhwc_to_nchw(
                     dsrc.data_ptr() + int(offsets[b]) + top * int(pitches[b]) + left * Cn, 1, in_h, in_w, Cn, 0, int(pitches[b]),
                     rs_h, rs_w, ptr(bx), ptr(kx), ksx, ptr(by), ptr(ky), ksy, out[b].data_ptr(), N.dtype_code(sp.dtype),
                     out_h, out_w, None, None, None if flip is None else int(base + 52 * B + b), oy, ox, lut.data_ptr(), self.flags,
-                    N.current_stream_ptr(self.device)))
+                    stream))
         return out
 
     # -- the call --------------------------------------------------------------------------
@@ -623,6 +637,26 @@ class BatchTransform:
             if params is None or len(params) != 4:
                 raise ValueError("this pipeline needs params=(box[B,4], flip, ops, pre) or a seed")
             return self._resized_crop_chain(batch, params, out)
+        if rrc and (H > 4 * out_h or W > 4 * out_w or batch.stride(1) % 4 or batch.stride(0) % 4 or batch.data_ptr() % 4):
+            # frames the uniform entry point refuses (more than 4x the output, or rows not 4-byte aligned): the same
+            # kernel through per-sample records, boxes read on the host
+            if params is None:
+                raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
+            hbox, hflip = params
+            hbox = (hbox.cpu().numpy() if isinstance(hbox, torch.Tensor) else np.asarray(hbox)).astype(np.int32).reshape(B, 4)
+            if hflip is not None:
+                hflip = (hflip.cpu().numpy() if isinstance(hflip, torch.Tensor) else np.asarray(hflip)).astype(np.uint8)
+            if batch.stride(1) % 4 or batch.stride(0) % 4 or batch.data_ptr() % 4:
+                padded = torch.zeros((B, H, (W * Cn + 3) // 4 * 4), dtype=torch.uint8, device=self.device)
+                padded[:, :, :W * Cn] = batch.reshape(B, H, W * Cn)
+                batch_mem, bs, pitch = padded, padded.stride(0), padded.stride(1)
+            else:
+                batch_mem, bs, pitch = batch, batch.stride(0), batch.stride(1)
+            geom = np.zeros((B, 10), np.int32)
+            geom[:, 0:4] = hbox
+            geom[:, 4], geom[:, 5], geom[:, 8], geom[:, 9] = out_h, out_w, H, W
+            return self._launch_ragged(batch_mem, np.arange(B, dtype=np.int64) * bs, np.full(B, pitch, np.int32), geom, hflip, Cn,
+                                       out_h, out_w, out)
         if rrc:
             if params is None:
                 raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
