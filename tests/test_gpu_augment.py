@@ -169,6 +169,18 @@ def test_forced_cluster_sizes_on_small_images(cluster):
             assert same(got, want), (H, W, C, threads)
 
 
+def test_image_sizes_around_the_shared_memory_opt_in():
+    """Found by tools/soak.py: 2 x 20.5 KB of image + the kernel's 7 KB of static shared memory crosses the
+    48 KB default although the dynamic part alone does not."""
+    rng = np.random.default_rng(6)
+    for (H, W) in ((58, 118), (92, 76), (64, 106), (63, 108), (80, 100)):
+        batch = rng.integers(0, 256, (2, H, W, 3), dtype=np.uint8)
+        ops = [[("Rotate", 12.0), ("Equalize", 0.0)], [("Sharpness", 0.5), ("AutoContrast", 0.0)]]
+        spec = TransformSpec(rand_augment=True, mean=CIFAR[0], std=CIFAR[1])
+        got = BatchTransform(spec, device="cuda")(torch.from_numpy(batch).cuda(), params=(None, None, None, ops))
+        assert same(got, TO.transform_batch(batch, ops=ops, mean=CIFAR[0], std=CIFAR[1])), (H, W)
+
+
 def test_mnist_rand_augment_replayed():
     """lenet.py:95: T.Compose([T.RandAugment(), T.ToTensor()]) on 28x28 grey images -- no crop, flip or
     rotation in the pipeline, so only RandAugment draws; two batches from one seed."""

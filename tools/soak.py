@@ -1,0 +1,247 @@
+#!/usr/bin/env python
+"""Randomised soak of every CUDA path against the oracle (torchvision / numpy restatements): far more
+seeds and shapes than the test-suite holds.  `python tools/soak.py --seconds 120 [--seed 0]`.
+Prints one line per failure with everything needed to replay it, and a summary."""
+import argparse
+import sys
+import time
+import traceback
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+from oracle import augment_oracle as AO          # noqa: E402
+from oracle import metrics_oracle as MO          # noqa: E402
+from oracle import transform_oracle as TO        # noqa: E402
+from torchbooster_b200 import augment as A       # noqa: E402
+from torchbooster_b200.metrics import MetricState  # noqa: E402
+from torchbooster_b200.transforms import BatchTransform, ToImage, TransformSpec  # noqa: E402
+
+DTYPES = [torch.float32, torch.bfloat16, torch.float16]
+MODES = ["constant", "reflect", "edge", "symmetric"]
+NAMES = list(AO.RAND_AUGMENT_OPS) + ["RandomRotation", "Invert"]
+
+
+def same(a, b):
+    a, b = a.cpu().contiguous(), b.cpu().contiguous()
+    view = {torch.float32: torch.int32, torch.bfloat16: torch.int16, torch.float16: torch.int16, torch.uint8: torch.uint8}[a.dtype]
+    return a.dtype == b.dtype and a.shape == b.shape and torch.equal(a.view(view), b.view(view))
+
+
+def images(rng, B, H, W, C):
+    kind = rng.integers(0, 4)
+    if kind == 0:
+        return rng.integers(0, 256, (B, H, W, C), dtype=np.uint8)
+    if kind == 1:
+        return (rng.integers(0, 256, (B, 1, 1, C)) + rng.integers(-6, 7, (B, H, W, C))).clip(0, 255).astype(np.uint8)
+    if kind == 2:
+        return np.broadcast_to(rng.integers(0, 256, (B, 1, 1, C), dtype=np.uint8), (B, H, W, C)).copy()
+    return (rng.integers(0, 2, (B, H, W, C)) * 255).astype(np.uint8)
+
+
+def mean_std(C):
+    return ((0.485, 0.456, 0.406)[:C], (0.229, 0.224, 0.225)[:C])
+
+
+def case_transform(rng):
+    C = int(rng.choice([1, 3, 3, 3, 4, 2]))
+    H, W, B = int(rng.integers(1, 90)), int(rng.integers(1, 90)), int(rng.integers(1, 9))
+    pad = int(rng.integers(0, min(H, W, 6)))
+    mode = MODES[int(rng.integers(0, 4))]
+    if mode == "reflect":
+        pad = min(pad, H - 1, W - 1)
+    th, tw = int(rng.integers(1, H + 2 * pad + 1)), int(rng.integers(1, W + 2 * pad + 1))
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    batch = images(rng, B, H, W, C)
+    top = rng.integers(0, H + 2 * pad - th + 1, B).astype(np.int32)
+    left = rng.integers(0, W + 2 * pad - tw + 1, B).astype(np.int32)
+    flip = rng.integers(0, 2, B).astype(np.uint8)
+    if C == 2:
+        return None         # PIL has no two-channel mode: covered by the index-map tests
+    m, s = ((0.5,) * C, (0.25,) * C) if C == 4 else mean_std(C)
+    spec = TransformSpec(crop=(th, tw), padding=pad, padding_mode=mode, flip_p=.5, mean=m, std=s, dtype=dtype)
+    bt = BatchTransform(spec, device="cuda")
+    bt.flags = int(rng.choice([0, 1, 2]))
+    got = bt(torch.from_numpy(batch).cuda(), params=(top, left, flip))
+    want = TO.transform_batch(batch, crop_top=top, crop_left=left, out_size=(th, tw), flip=flip, padding=pad, padding_mode=mode,
+                              mean=m, std=s, dtype=dtype)
+    return same(got, want), dict(kind="transform", C=C, H=H, W=W, B=B, pad=pad, mode=mode, th=th, tw=tw, dtype=str(dtype), flags=bt.flags)
+
+
+def case_resize(rng):
+    C = int(rng.choice([1, 3, 3]))
+    H, W, B = int(rng.integers(2, 200)), int(rng.integers(2, 200)), int(rng.integers(1, 5))
+    rs = (int(rng.integers(1, 150)), int(rng.integers(1, 150))) if rng.integers(0, 2) else int(rng.integers(2, 150))
+    cc = None if rng.integers(0, 3) == 0 else (int(rng.integers(1, 120)), int(rng.integers(1, 120)))
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    batch = images(rng, B, H, W, C)
+    m, s = mean_std(C)
+    spec = TransformSpec(resize=rs, center_crop=cc, mean=m, std=s, dtype=dtype)
+    bt = BatchTransform(spec, device="cuda")
+    bt.flags = int(rng.choice([0, 1, 16]))
+    got = bt(torch.from_numpy(batch).cuda())
+    want = TO.transform_batch(batch, resize=rs, center_crop=cc, mean=m, std=s, dtype=dtype)
+    return same(got, want), dict(kind="resize", C=C, H=H, W=W, B=B, rs=rs, cc=cc, dtype=str(dtype), flags=bt.flags)
+
+
+def case_rrc(rng):
+    C = int(rng.choice([1, 3, 3]))
+    H, W, B = int(rng.integers(4, 260)), int(rng.integers(4, 260)), int(rng.integers(1, 7))
+    size = (int(rng.integers(1, 120)), int(rng.integers(1, 120)))
+    seed = int(rng.integers(0, 2 ** 31))
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    batch = images(rng, B, H, W, C)
+    m, s = mean_std(C)
+    from oracle import params_oracle as PO
+    boxes, flip = PO.draw_resized_crop_flip(seed, B, H, W)
+    spec = TransformSpec(random_resized_crop=size, flip_p=.5, mean=m, std=s, dtype=dtype)
+    bt = BatchTransform(spec, device="cuda", seed=seed)
+    bt.flags = int(rng.choice([0, 16]))
+    got = bt(torch.from_numpy(batch).cuda())
+    want = TO.transform_batch(batch, boxes=boxes, out_size=size, flip=flip, mean=m, std=s, dtype=dtype)
+    return same(got, want), dict(kind="rrc", C=C, H=H, W=W, B=B, size=size, seed=seed, dtype=str(dtype), flags=bt.flags)
+
+
+def case_ragged(rng):
+    C = int(rng.choice([1, 3, 3]))
+    B = int(rng.integers(1, 7))
+    sizes = [(int(rng.integers(3, 220)), int(rng.integers(3, 220))) for _ in range(B)]
+    imgs = [images(rng, 1, h, w, C)[0] for h, w in sizes]
+    m, s = mean_std(C)
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    if rng.integers(0, 2):
+        rs, cc = int(rng.integers(2, 100)), int(rng.integers(1, 100))
+        spec = TransformSpec(resize=rs, center_crop=cc, mean=m, std=s, dtype=dtype)
+        got = BatchTransform(spec, device="cuda").ragged(imgs)
+        want = torch.stack([TO.transform_sample(im, resize=rs, center_crop=cc, mean=m, std=s, dtype=dtype) for im in imgs])
+        info = dict(kind="ragged_resize", C=C, sizes=sizes, rs=rs, cc=cc, dtype=str(dtype))
+    else:
+        import torchvision.transforms as T
+        from PIL import Image
+        size, seed = int(rng.integers(1, 100)), int(rng.integers(0, 2 ** 31))
+        compose = T.Compose([T.RandomResizedCrop(size), T.RandomHorizontalFlip(), T.ToTensor(), T.Normalize(m, s)])
+        state = torch.get_rng_state()
+        torch.manual_seed(seed)
+        want = torch.stack([compose(Image.fromarray(im if C == 3 else im[:, :, 0])) for im in imgs]).to(dtype)
+        torch.set_rng_state(state)
+        got = BatchTransform(TransformSpec(random_resized_crop=size, flip_p=.5, mean=m, std=s, dtype=dtype), device="cuda",
+                             seed=seed).ragged(imgs)
+        info = dict(kind="ragged_rrc", C=C, sizes=sizes, size=size, seed=seed, dtype=str(dtype))
+    return same(got, want), info
+
+
+def case_augment(rng):
+    C = int(rng.choice([1, 3, 3]))
+    H, W, B = int(rng.integers(2, 120)), int(rng.integers(2, 120)), int(rng.integers(1, 10))
+    pad = int(rng.integers(0, min(H, W, 5)))
+    mode = MODES[int(rng.integers(0, 4))]
+    if mode == "reflect":
+        pad = min(pad, H - 1, W - 1)
+    th, tw = int(rng.integers(1, H + 2 * pad + 1)), int(rng.integers(1, W + 2 * pad + 1))
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    batch = images(rng, B, H, W, C)
+    top = rng.integers(0, H + 2 * pad - th + 1, B).astype(np.int32)
+    left = rng.integers(0, W + 2 * pad - tw + 1, B).astype(np.int32)
+    flip = rng.integers(0, 2, B).astype(np.uint8)
+    ops = []
+    for b in range(B):
+        mags = A.rand_augment_magnitudes(th, tw, int(rng.integers(0, 31)))
+        mine = []
+        for _ in range(int(rng.integers(0, 7))):
+            name = NAMES[int(rng.integers(0, len(NAMES)))]
+            mag = float(np.float32(rng.uniform(-360, 360))) if name == "RandomRotation" else mags.get(name, 0.0)
+            if name not in ("Posterize", "Solarize", "RandomRotation") and rng.integers(0, 2):
+                mag = -mag
+            mine.append((name, mag))
+        ops.append(mine)
+    m, s = mean_std(C)
+    spec = TransformSpec(crop=(th, tw), padding=pad, padding_mode=mode, flip_p=.5, rotation=10, rand_augment=True, mean=m, std=s, dtype=dtype)
+    bt = BatchTransform(spec, device="cuda")
+    bt.flags = (int(rng.choice([0, 0, 2, 4, 8])) << 8) | (int(rng.choice([0, 2, 3, 4])) << 12)
+    info = dict(kind="augment", C=C, H=H, W=W, B=B, pad=pad, mode=mode, th=th, tw=tw, dtype=str(dtype), flags=bt.flags, ops=ops)
+    try:
+        got = bt(torch.from_numpy(batch).cuda(), params=(top, left, flip, ops))
+    except Exception as e:
+        return False, dict(info, ops=None, error=repr(e))
+    want = TO.transform_batch(batch, crop_top=top, crop_left=left, out_size=(th, tw), flip=flip, ops=ops, padding=pad,
+                              padding_mode=mode, mean=m, std=s, dtype=dtype)
+    return same(got, want), info
+
+
+def case_metrics(rng):
+    N, C, k = int(rng.integers(1, 600)), int(rng.integers(1, 1300)), int(rng.integers(1, 8))
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    g = torch.Generator().manual_seed(int(rng.integers(0, 2 ** 31)))
+    logits = torch.randn(N, C, generator=g)
+    kind = int(rng.integers(0, 4))
+    if kind == 1:
+        logits = (logits * 2).round() / 2                      # many exact ties
+    elif kind == 2:
+        logits[torch.rand(N, C, generator=g) < 0.01] = float("nan")
+        logits[torch.rand(N, C, generator=g) < 0.01] = float("inf")
+        logits[torch.rand(N, C, generator=g) < 0.01] = -float("inf")
+    elif kind == 3:
+        logits = torch.zeros(N, C) * torch.where(torch.rand(N, C, generator=g) < 0.5, -1.0, 1.0)     # +0 / -0
+    logits = logits.to(dtype)
+    labels = torch.randint(0, C, (N,), generator=g)
+    st = MetricState(C, k=k, device="cuda")
+    st.update(logits.cuda(), labels.cuda())
+    res = st.compute()
+    ok = (res["correct_1"] == MO.topk_correct(logits.float(), labels, 1) and res[f"correct_{k}"] == MO.topk_correct(logits.float(), labels, k)
+          and np.array_equal(res["confusion"].cpu().numpy(), MO.confusion(logits.float(), labels, C)))
+    return ok, dict(kind="metrics", N=N, C=C, k=k, dtype=str(dtype), variant=kind)
+
+
+def case_image(rng):
+    C = int(rng.choice([1, 3, 3]))
+    H, W = int(rng.integers(1, 150)), int(rng.integers(1, 150))
+    mode = [None, "clamp", "stretch"][int(rng.integers(0, 3))]
+    g = torch.Generator().manual_seed(int(rng.integers(0, 2 ** 31)))
+    m, s = (np.array(v) for v in mean_std(C))
+    x = torch.randn((C, H, W), generator=g) * float(rng.uniform(0.1, 3))
+    if mode is None:
+        x = ((torch.rand((C, H, W), generator=g) * 0.99 + 0.005) - torch.tensor(m, dtype=torch.float32)[:, None, None]) / \
+            torch.tensor(s, dtype=torch.float32)[:, None, None]
+        x = x.clamp(min=float(((0.002 - m) / s).max()), max=float(((0.997 - m) / s).min()))
+    got = ToImage.inverse_of(m, s, mode)(x.cuda())
+    want = TO.to_image(x, mean=-m / s, std=1.0 / s, mode=mode)
+    return np.array_equal(got.cpu().numpy(), want), dict(kind="to_image", C=C, H=H, W=W, mode=mode)
+
+
+CASES = [case_transform, case_resize, case_rrc, case_ragged, case_augment, case_metrics, case_image]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--seconds", type=float, default=60)
+    ap.add_argument("--seed", type=int, default=0)
+    a = ap.parse_args()
+    rng = np.random.default_rng(a.seed)
+    t0 = time.time()
+    done, fails = {}, 0
+    i = 0
+    while time.time() - t0 < a.seconds:
+        fn = CASES[i % len(CASES)]
+        sub = int(rng.integers(0, 2 ** 31))
+        i += 1
+        try:
+            r = fn(np.random.default_rng(sub))
+            if r is None:
+                continue
+            ok, info = r
+        except Exception as e:      # an exception is a finding too
+            ok, info = False, dict(kind=fn.__name__, error=repr(e), trace=traceback.format_exc()[-600:])
+        done[fn.__name__] = done.get(fn.__name__, 0) + 1
+        if not ok:
+            fails += 1
+            print("FAIL", dict(sub_seed=sub, **info), flush=True)
+    torch.cuda.synchronize()
+    print("soak:", done, "failures:", fails, flush=True)
+    return 1 if fails else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -379,7 +379,8 @@ __global__ void __launch_bounds__(kAugMaxThreads) tb_augment_kernel(AugParams p)
 template <typename T>
 int launch_augment(const AugParams& p, int cluster, int threads, size_t smem, cudaStream_t s) {
     if (cluster == 1) {
-        if (smem > 48 * 1024)
+        // static + dynamic shared memory beyond 48 KiB needs the opt-in (the kernel holds ~7 KiB statically)
+        if (smem > 40 * 1024)
             TB_CUDA(cudaFuncSetAttribute(tb_augment_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         tb_augment_kernel<T, false><<<p.B, threads, smem, s>>>(p);
     } else {
