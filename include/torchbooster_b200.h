@@ -34,7 +34,7 @@ extern "C" {
 #define TB_F32  0
 #define TB_BF16 1
 #define TB_F16  2
-#define TB_U8   3   /* tb_resized_crop_bilinear_u8_nhwc_to_nchw only: bytes out (lut = uint8 [C][256]), the hand-off to tb_augment */
+#define TB_U8   3   /* the resize entry points only: bytes out (lut = uint8 [C][256]), the hand-off to tb_augment */
 
 /* padding modes of torchvision F.pad (torchvision/transforms/_functional_pil.py:147-223) */
 #define TB_PAD_NONE      0  /* no padding declared; reads outside the image still give 0 */

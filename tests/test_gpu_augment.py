@@ -247,3 +247,21 @@ def test_resized_crop_chains_vs_the_compose(pre, flip_p, rot, ra, dtype):
                          mean=IMAGENET[0], std=IMAGENET[1], dtype=dtype)
     got = BatchTransform(spec, device="cuda", seed=2718)(torch.from_numpy(batch).cuda())
     assert same(got, want)
+
+
+def test_resized_crop_chain_on_frames_beyond_4x():
+    """Found by tools/soak.py: the chained pipelines also take the per-sample-records route when the frame is
+    more than four times the output (236x188 -> 46) or its rows are not 4-byte aligned (W * 3 = 375)."""
+    import torchvision.transforms as T
+    from PIL import Image
+    rng = np.random.default_rng(12)
+    for (H, W, size, pre, ra) in ((236, 188, 46, 180, False), (216, 144, 13, 15, True), (90, 125, 40, None, True)):
+        batch = rng.integers(0, 256, (3, H, W, 3), dtype=np.uint8)
+        stages = ([T.RandomRotation(pre)] if pre is not None else []) + [T.RandomResizedCrop(size), T.RandomHorizontalFlip()] + \
+            ([T.RandAugment()] if ra else []) + [T.ToTensor(), T.Normalize(IMAGENET[0], IMAGENET[1])]
+        compose = T.Compose(stages)
+        torch.manual_seed(77)
+        want = torch.stack([compose(Image.fromarray(batch[b])) for b in range(3)])
+        spec = TransformSpec(random_resized_crop=size, pre_rotation=pre, flip_p=0.5, rand_augment=ra, mean=IMAGENET[0], std=IMAGENET[1])
+        got = BatchTransform(spec, device="cuda", seed=77)(torch.from_numpy(batch).cuda())
+        assert same(got, want), (H, W, size, pre, ra)

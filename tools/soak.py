@@ -211,7 +211,103 @@ def case_image(rng):
     return np.array_equal(got.cpu().numpy(), want), dict(kind="to_image", C=C, H=H, W=W, mode=mode)
 
 
-CASES = [case_transform, case_resize, case_rrc, case_ragged, case_augment, case_metrics, case_image]
+def case_stream(rng):
+    """C == 3 with 16-byte aligned rows: the streaming (bulk-copy) kernel, device and pinned-host sources,
+    strided batches, caller-provided outputs."""
+    B = int(rng.integers(1, 40))
+    H, W = int(rng.integers(8, 150)), 16 * int(rng.integers(1, 12))
+    pad = int(rng.choice([0, 0, 0, 2, 4]))
+    mode = MODES[int(rng.integers(0, 4))]
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    px = 4 if dtype == torch.float32 else 8
+    tw = px * int(rng.integers(1, (W + 2 * pad) // px + 1))
+    th = int(rng.integers(1, H + 2 * pad + 1))
+    batch = images(rng, B, H, W, 3)
+    top = rng.integers(0, H + 2 * pad - th + 1, B).astype(np.int32)
+    left = rng.integers(0, W + 2 * pad - tw + 1, B).astype(np.int32)
+    flip = rng.integers(0, 2, B).astype(np.uint8)
+    m, s = mean_std(3)
+    one_minus = bool(rng.integers(0, 4) == 0)
+    spec = TransformSpec(crop=(th, tw), padding=pad, padding_mode=mode, flip_p=.5, mean=m, std=s, one_minus=one_minus, dtype=dtype)
+    bt = BatchTransform(spec, device="cuda")
+    bt.flags = int(rng.choice([0, 2, 2, 6]))
+    src_kind = int(rng.integers(0, 3))
+    if src_kind == 0:
+        src = torch.from_numpy(batch).cuda()
+    elif src_kind == 1:
+        src = torch.from_numpy(batch).pin_memory()                  # read in place over PCIe
+    else:
+        wide = torch.zeros((B, H + 3, W + 16, 3), dtype=torch.uint8, device="cuda")
+        wide[:, :H, :W] = torch.from_numpy(batch).cuda()
+        src = wide[:, :H, :W]                                       # batch stride and row pitch larger than dense
+    out = torch.empty((B, 3, th, tw), dtype=dtype, device="cuda") if rng.integers(0, 2) else None
+    info = dict(kind="stream", B=B, H=H, W=W, pad=pad, mode=mode, th=th, tw=tw, dtype=str(dtype), flags=bt.flags, src=src_kind,
+                one_minus=one_minus)
+    try:
+        got = bt(src, params=(top, left, flip), out=out)
+    except Exception as e:
+        return False, dict(info, error=repr(e))
+    want = TO.transform_batch(batch, crop_top=top, crop_left=left, out_size=(th, tw), flip=flip, padding=pad, padding_mode=mode,
+                              mean=m, std=s, one_minus=one_minus, dtype=dtype)
+    return same(got, want), info
+
+
+def case_chain(rng):
+    """pre_rotation -> RandomResizedCrop -> flip -> rotation -> RandAugment (online.py:173 and variants), seeded,
+    against the literal Compose; and large images through the cluster path of the augment kernel."""
+    import torchvision.transforms as T
+    from PIL import Image
+    C = 3
+    if rng.integers(0, 2):
+        B, H, W, size = int(rng.integers(1, 5)), 4 * int(rng.integers(10, 60)), 4 * int(rng.integers(10, 60)), int(rng.integers(8, 120))
+        pre = None if rng.integers(0, 2) else float(rng.choice([15, 90, 180]))
+        flip_p = None if rng.integers(0, 2) else 0.5
+        rot = None if rng.integers(0, 2) else 20.0
+        ra = bool(rng.integers(0, 2))
+        if pre is None and rot is None and not ra:
+            ra = True
+        seed = int(rng.integers(0, 2 ** 31))
+        batch = images(rng, B, H, W, C)
+        m, s = mean_std(C)
+        stages = ([T.RandomRotation(pre)] if pre is not None else []) + [T.RandomResizedCrop(size)] + \
+            ([T.RandomHorizontalFlip(flip_p)] if flip_p is not None else []) + ([T.RandomRotation(rot)] if rot is not None else []) + \
+            ([T.RandAugment()] if ra else []) + [T.ToTensor(), T.Normalize(m, s)]
+        compose = T.Compose(stages)
+        state = torch.get_rng_state()
+        torch.manual_seed(seed)
+        want = torch.stack([compose(Image.fromarray(batch[b])) for b in range(B)])
+        torch.set_rng_state(state)
+        spec = TransformSpec(random_resized_crop=size, pre_rotation=pre, flip_p=flip_p, rotation=rot, rand_augment=ra, mean=m, std=s)
+        info = dict(kind="chain", B=B, H=H, W=W, size=size, pre=pre, flip_p=flip_p, rot=rot, ra=ra, seed=seed)
+        try:
+            got = BatchTransform(spec, device="cuda", seed=seed)(torch.from_numpy(batch).cuda())
+        except Exception as e:
+            return False, dict(info, error=repr(e))
+        return same(got, want), info
+    B, H, W = int(rng.integers(1, 4)), int(rng.integers(100, 420)), int(rng.integers(100, 420))
+    batch = images(rng, B, H, W, C)
+    m, s = mean_std(C)
+    ops = []
+    for b in range(B):
+        mags = A.rand_augment_magnitudes(H, W, int(rng.integers(0, 31)))
+        mine = []
+        for _ in range(int(rng.integers(1, 5))):
+            name = NAMES[int(rng.integers(0, len(NAMES)))]
+            mag = float(np.float32(rng.uniform(-360, 360))) if name == "RandomRotation" else mags.get(name, 0.0)
+            if name not in ("Posterize", "Solarize", "RandomRotation") and rng.integers(0, 2):
+                mag = -mag
+            mine.append((name, mag))
+        ops.append(mine)
+    spec = TransformSpec(rand_augment=True, mean=m, std=s)
+    info = dict(kind="augment_large", B=B, H=H, W=W, ops=ops)
+    try:
+        got = BatchTransform(spec, device="cuda")(torch.from_numpy(batch).cuda(), params=(None, None, None, ops))
+    except Exception as e:
+        return False, dict(info, ops=None, error=repr(e))
+    return same(got, TO.transform_batch(batch, ops=ops, mean=m, std=s)), info
+
+
+CASES = [case_transform, case_resize, case_rrc, case_ragged, case_augment, case_metrics, case_image, case_stream, case_chain]
 
 
 def main():
@@ -221,7 +317,7 @@ def main():
     a = ap.parse_args()
     rng = np.random.default_rng(a.seed)
     t0 = time.time()
-    done, fails = {}, 0
+    done, fails, classes = {}, 0, {}
     i = 0
     while time.time() - t0 < a.seconds:
         fn = CASES[i % len(CASES)]
@@ -237,8 +333,13 @@ def main():
         done[fn.__name__] = done.get(fn.__name__, 0) + 1
         if not ok:
             fails += 1
-            print("FAIL", dict(sub_seed=sub, **info), flush=True)
+            key = (info.get("kind"), str(info.get("error", "mismatch"))[:60])
+            classes[key] = classes.get(key, 0) + 1
+            if classes[key] <= 3:
+                print("FAIL", dict(sub_seed=sub, **info), flush=True)
     torch.cuda.synchronize()
+    for key, n in sorted(classes.items(), key=lambda kv: -kv[1]):
+        print("CLASS", n, key, flush=True)
     print("soak:", done, "failures:", fails, flush=True)
     return 1 if fails else 0
 

@@ -779,7 +779,7 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     TB_REQUIRE(B >= 0 && H >= 1 && W >= 1, "tb_resize: bad source shape B=%d H=%d W=%d", B, H, W);
     TB_REQUIRE(C == 1 || C == 3, "tb_resize: C=%d not supported (Pillow premultiplies alpha for RGBA); use C in {1,3}", C);
     TB_REQUIRE(rs_h >= 1 && rs_w >= 1 && out_h >= 1 && out_w >= 1, "tb_resize: bad output sizes");
-    TB_REQUIRE(tb_dtype_size(dst_dtype) != 0, "tb_resize: unknown dst_dtype %d", dst_dtype);
+    TB_REQUIRE(dst_dtype == TB_U8 || tb_dtype_size(dst_dtype) != 0, "tb_resize: unknown dst_dtype %d", dst_dtype);
     TB_REQUIRE(src_row_pitch >= (int64_t)W * C && src_batch_stride >= 0, "tb_resize: bad source strides");
     if (rs_w != W) {
         TB_REQUIRE(bounds_x && taps_x, "tb_resize: horizontal taps missing");
@@ -791,7 +791,7 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     }
     if (B == 0) return TB_OK;
     TB_REQUIRE(src && dst && lut, "tb_resize: NULL src/dst/lut");
-    TB_REQUIRE(((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_resize: dst misaligned for its dtype");
+    TB_REQUIRE(dst_dtype == TB_U8 || ((uintptr_t)dst % tb_dtype_size(dst_dtype)) == 0, "tb_resize: dst misaligned for its dtype");
 
     TbDevice dev;
     int rc = tb_device(&dev);
@@ -820,6 +820,8 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
         slide_geometry(p, B, dev.sm_count, flags, &blocks, &threads);
         TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize: grid too large");
         cudaStream_t s = (cudaStream_t)stream;
+        if (dst_dtype == TB_U8)
+            return C == 3 ? launch_slide<uint8_t, 3>(p, blocks, threads, nt, s) : launch_slide<uint8_t, 1>(p, blocks, threads, nt, s);
         if (dst_dtype == TB_F32)
             return C == 3 ? launch_slide<float, 3>(p, blocks, threads, nt, s) : launch_slide<float, 1>(p, blocks, threads, nt, s);
         return C == 3 ? launch_slide<uint16_t, 3>(p, blocks, threads, nt, s) : launch_slide<uint16_t, 1>(p, blocks, threads, nt, s);
@@ -869,6 +871,9 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_resize: grid too large");
     cudaStream_t s = (cudaStream_t)stream;
     const bool f32 = dst_dtype == TB_F32;
+    if (dst_dtype == TB_U8)
+        return C == 3 ? launch_resize<uint8_t, 3>(p, smem, blocks, dev.max_smem_optin, fast, nt, s)
+                      : launch_resize<uint8_t, 1>(p, smem, blocks, dev.max_smem_optin, fast, nt, s);
     if (C == 3) return f32 ? launch_resize<float, 3>(p, smem, blocks, dev.max_smem_optin, fast, nt, s)
                            : launch_resize<uint16_t, 3>(p, smem, blocks, dev.max_smem_optin, fast, nt, s);
     return f32 ? launch_resize<float, 1>(p, smem, blocks, dev.max_smem_optin, fast, nt, s)

@@ -452,6 +452,36 @@ class BatchTransform:
         N.check(rc)
         return out
 
+    def _identity_bytes(self, channels: int) -> torch.Tensor:
+        if getattr(self, "_bytes_lut", None) is None or self._bytes_lut.shape[0] != channels:
+            self._bytes_lut = torch.arange(256, dtype=torch.uint8, device=self.device).repeat(channels, 1).contiguous()
+        return self._bytes_lut
+
+    @staticmethod
+    def _needs_records(batch: torch.Tensor, out_h: int, out_w: int) -> bool:
+        """Frames the uniform resized-crop entry point refuses: more than 4x the output, or rows / images not 4-byte aligned."""
+        _, H, W, _ = batch.shape
+        return bool(H > 4 * out_h or W > 4 * out_w or batch.stride(1) % 4 or batch.stride(0) % 4 or batch.data_ptr() % 4)
+
+    def _resized_crop_records(self, batch: torch.Tensor, box, flip, out_h: int, out_w: int, out: Optional[torch.Tensor],
+                              as_bytes: bool = False) -> torch.Tensor:
+        """The resized crop of a uniform batch through per-sample records (boxes read on the host)."""
+        B, H, W, Cn = batch.shape
+        hbox = (box.cpu().numpy() if isinstance(box, torch.Tensor) else np.asarray(box)).astype(np.int32).reshape(B, 4)
+        hflip = None
+        if flip is not None:
+            hflip = (flip.cpu().numpy() if isinstance(flip, torch.Tensor) else np.asarray(flip)).astype(np.uint8)
+        if batch.stride(1) % 4 or batch.stride(0) % 4 or batch.data_ptr() % 4:
+            mem = torch.zeros((B, H, (W * Cn + 3) // 4 * 4), dtype=torch.uint8, device=self.device)
+            mem[:, :, :W * Cn] = batch.reshape(B, H, W * Cn)
+        else:
+            mem = batch
+        geom = np.zeros((B, 10), np.int32)
+        geom[:, 0:4] = hbox
+        geom[:, 4], geom[:, 5], geom[:, 8], geom[:, 9] = out_h, out_w, H, W
+        return self._launch_ragged(mem, np.arange(B, dtype=np.int64) * mem.stride(0), np.full(B, mem.stride(1), np.int32), geom,
+                                   hflip, Cn, out_h, out_w, out, as_bytes=as_bytes)
+
     def _resized_crop_chain(self, batch: torch.Tensor, params, out: Optional[torch.Tensor]) -> torch.Tensor:
         """[RandomRotation on the source ->] RandomResizedCrop [-> flip] [-> rotation / RandAugment on the crop] ->
         table: up to three launches that hand uint8 images on (``online.py:173``)."""
@@ -480,18 +510,23 @@ class BatchTransform:
                 src = torch.empty((B, H, W, Cn), dtype=torch.uint8, device=self.device)
                 N.check(L.tb_affine_nearest_u8_nhwc(batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1),
                                                     rec.data_ptr(), src.data_ptr(), stream))
-            box, flip = self._boxes_to_device(box_flip, B)
+            records = self._needs_records(src, out_h, out_w)
             if ops is None:                                                 # stage B straight to the output
+                if records:
+                    return self._resized_crop_records(src, box_flip[0], box_flip[1], out_h, out_w, out)
+                box, flip = self._boxes_to_device(box_flip, B)
                 N.check(L.tb_resized_crop_bilinear_u8_nhwc_to_nchw(
                     src.data_ptr(), B, H, W, Cn, src.stride(0), src.stride(1), box.data_ptr(), out.data_ptr(),
                     N.dtype_code(sp.dtype), out_h, out_w, ptr(flip), lut.data_ptr(), self.flags, stream))
                 return out
-            if getattr(self, "_bytes_lut", None) is None or self._bytes_lut.shape[0] != Cn:
-                self._bytes_lut = torch.arange(256, dtype=torch.uint8, device=self.device).repeat(Cn, 1).contiguous()
-            crop = torch.empty((B, Cn, out_h, out_w), dtype=torch.uint8, device=self.device)      # stage B: bytes, planar
-            N.check(L.tb_resized_crop_bilinear_u8_nhwc_to_nchw(
-                src.data_ptr(), B, H, W, Cn, src.stride(0), src.stride(1), box.data_ptr(), crop.data_ptr(),
-                N.TB_U8, out_h, out_w, ptr(flip), self._bytes_lut.data_ptr(), self.flags, stream))
+            if records:                                                     # stage B: bytes, planar
+                crop = self._resized_crop_records(src, box_flip[0], box_flip[1], out_h, out_w, None, as_bytes=True)
+            else:
+                box, flip = self._boxes_to_device(box_flip, B)
+                crop = torch.empty((B, Cn, out_h, out_w), dtype=torch.uint8, device=self.device)
+                N.check(L.tb_resized_crop_bilinear_u8_nhwc_to_nchw(
+                    src.data_ptr(), B, H, W, Cn, src.stride(0), src.stride(1), box.data_ptr(), crop.data_ptr(),
+                    N.TB_U8, out_h, out_w, ptr(flip), self._identity_bytes(Cn).data_ptr(), self.flags, stream))
             rec = self._ops_to_device(ops, B, out_h, out_w, Cn)             # stage C: operations on the crop, then the table
             N.check(L.tb_augment_u8_nhwc_to_nchw(
                 crop.data_ptr(), B, out_h, out_w, Cn, Cn * out_h * out_w, out_w, out.data_ptr(), N.dtype_code(sp.dtype),
@@ -564,7 +599,7 @@ class BatchTransform:
         return self._launch_ragged(dsrc, offsets, pitches, geom, flip, Cn, out_h, out_w, out)
 
     def _launch_ragged(self, dsrc: torch.Tensor, offsets: np.ndarray, pitches: np.ndarray, geom: np.ndarray, flip, Cn: int,
-                       out_h: int, out_w: int, out: Optional[torch.Tensor]) -> torch.Tensor:
+                       out_h: int, out_w: int, out: Optional[torch.Tensor], as_bytes: bool = False) -> torch.Tensor:
         """Per-sample geometry records over device memory ``dsrc``: one launch of the eight-tap kernel for
         every region within 4x of its resized size, one launch of the any-scale kernel for each of the rest."""
         sp = self.spec
@@ -589,17 +624,19 @@ class BatchTransform:
         mv[52 * B:] = 0 if flip is None else np.asarray(flip, np.uint8)
         self._ragged_meta = meta                            # pinned source stays alive until the copy has run
         dmeta = meta.to(self.device, non_blocking=True)
+        odt = torch.uint8 if as_bytes else sp.dtype         # as_bytes: planar uint8 out, the hand-off to the augment kernel
         if out is None:
-            out = torch.empty((B, Cn, out_h, out_w), dtype=sp.dtype, device=self.device)
-        elif tuple(out.shape) != (B, Cn, out_h, out_w) or out.dtype != sp.dtype or not out.is_contiguous() or out.device != self.device:
-            raise ValueError(f"out must be a contiguous tensor of shape {(B, Cn, out_h, out_w)}, dtype {sp.dtype} on {self.device}")
-        lut = self.lut(Cn)
+            out = torch.empty((B, Cn, out_h, out_w), dtype=odt, device=self.device)
+        elif tuple(out.shape) != (B, Cn, out_h, out_w) or out.dtype != odt or not out.is_contiguous() or out.device != self.device:
+            raise ValueError(f"out must be a contiguous tensor of shape {(B, Cn, out_h, out_w)}, dtype {odt} on {self.device}")
+        lut = self._identity_bytes(Cn) if as_bytes else self.lut(Cn)
+        code = N.TB_U8 if as_bytes else N.dtype_code(sp.dtype)
         base = dmeta.data_ptr()
         ptr = lambda t: None if t is None else t.data_ptr()
         with torch.cuda.device(self.device):
             stream = N.current_stream_ptr(self.device)
             N.check(N.lib().tb_resize_crop_ragged_u8_to_nchw(
-                dsrc.data_ptr(), base, base + 8 * B, B, Cn, base + 12 * B, taps, out.data_ptr(), N.dtype_code(sp.dtype),
+                dsrc.data_ptr(), base, base + 8 * B, B, Cn, base + 12 * B, taps, out.data_ptr(), code,
                 out_h, out_w, None if flip is None else base + 52 * B, lut.data_ptr(), self.flags, stream))
             for b, g in slow:           # any-scale kernel, host-built taps (cached per size pair), one sample per launch
                 top, left, in_h, in_w, rs_h, rs_w, oy, ox = (int(v) for v in g[:8])
@@ -607,7 +644,7 @@ class BatchTransform:
                 ksy, by, ky = self._resize_taps(in_h, rs_h) if rs_h != in_h else (0, None, None)
                 N.check(N.lib().tb_resize_bilinear_u8_nhwc_to_nchw(
                     dsrc.data_ptr() + int(offsets[b]) + top * int(pitches[b]) + left * Cn, 1, in_h, in_w, Cn, 0, int(pitches[b]),
-                    rs_h, rs_w, ptr(bx), ptr(kx), ksx, ptr(by), ptr(ky), ksy, out[b].data_ptr(), N.dtype_code(sp.dtype),
+                    rs_h, rs_w, ptr(bx), ptr(kx), ksx, ptr(by), ptr(ky), ksy, out[b].data_ptr(), code,
                     out_h, out_w, None, None, None if flip is None else int(base + 52 * B + b), oy, ox, lut.data_ptr(), self.flags,
                     stream))
         return out
@@ -637,26 +674,10 @@ class BatchTransform:
             if params is None or len(params) != 4:
                 raise ValueError("this pipeline needs params=(box[B,4], flip, ops, pre) or a seed")
             return self._resized_crop_chain(batch, params, out)
-        if rrc and (H > 4 * out_h or W > 4 * out_w or batch.stride(1) % 4 or batch.stride(0) % 4 or batch.data_ptr() % 4):
-            # frames the uniform entry point refuses (more than 4x the output, or rows not 4-byte aligned): the same
-            # kernel through per-sample records, boxes read on the host
+        if rrc and self._needs_records(batch, out_h, out_w):
             if params is None:
                 raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
-            hbox, hflip = params
-            hbox = (hbox.cpu().numpy() if isinstance(hbox, torch.Tensor) else np.asarray(hbox)).astype(np.int32).reshape(B, 4)
-            if hflip is not None:
-                hflip = (hflip.cpu().numpy() if isinstance(hflip, torch.Tensor) else np.asarray(hflip)).astype(np.uint8)
-            if batch.stride(1) % 4 or batch.stride(0) % 4 or batch.data_ptr() % 4:
-                padded = torch.zeros((B, H, (W * Cn + 3) // 4 * 4), dtype=torch.uint8, device=self.device)
-                padded[:, :, :W * Cn] = batch.reshape(B, H, W * Cn)
-                batch_mem, bs, pitch = padded, padded.stride(0), padded.stride(1)
-            else:
-                batch_mem, bs, pitch = batch, batch.stride(0), batch.stride(1)
-            geom = np.zeros((B, 10), np.int32)
-            geom[:, 0:4] = hbox
-            geom[:, 4], geom[:, 5], geom[:, 8], geom[:, 9] = out_h, out_w, H, W
-            return self._launch_ragged(batch_mem, np.arange(B, dtype=np.int64) * bs, np.full(B, pitch, np.int32), geom, hflip, Cn,
-                                       out_h, out_w, out)
+            return self._resized_crop_records(batch, params[0], params[1], out_h, out_w, out)
         if rrc:
             if params is None:
                 raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
