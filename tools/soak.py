@@ -307,7 +307,47 @@ def case_chain(rng):
     return same(got, TO.transform_batch(batch, ops=ops, mean=m, std=s)), info
 
 
-CASES = [case_transform, case_resize, case_rrc, case_ragged, case_augment, case_metrics, case_image, case_stream, case_chain]
+def case_loader(rng):
+    """LMDB file -> BatchLoader (gathered into pinned slots, or the registered map read in place) -> transform,
+    ragged last batch, labels; against the oracle on the same sampler order."""
+    import tempfile
+    from oracle import params_oracle as PO
+    from torchbooster_b200.lmdb import LMDBReader, write_image_lmdb
+    from torchbooster_b200.loader import BatchLoader
+    n, bs = int(rng.integers(1, 120)), int(rng.integers(1, 40))
+    H, W = int(rng.integers(4, 70)), 16 * int(rng.integers(1, 6)) if rng.integers(0, 2) else int(rng.integers(4, 70))
+    th, tw = int(rng.integers(1, H + 1)), int(rng.integers(1, W + 1))
+    in_place = bool(rng.integers(0, 2))
+    seed = int(rng.integers(0, 2 ** 31))
+    imgs = images(rng, n, H, W, 3)
+    order = rng.permutation(n)
+    m, s = mean_std(3)
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    info = dict(kind="loader", n=n, bs=bs, H=H, W=W, th=th, tw=tw, in_place=in_place, seed=seed, dtype=str(dtype))
+    with tempfile.TemporaryDirectory() as tmp:
+        write_image_lmdb(tmp + "/db", imgs, labels=np.arange(n) % 7)
+        reader = LMDBReader(tmp + "/db")
+        spec = TransformSpec(crop=(th, tw), flip_p=.5, mean=m, std=s, dtype=dtype)
+        try:
+            loader = BatchLoader(reader, (H, W, 3), bs, sampler=order.tolist(), labels=reader.read_labels(),
+                                 transform=BatchTransform(spec, device="cuda", seed=seed), in_place=in_place, threads=3)
+            outs = [(x.clone(), y.clone()) for x, y in loader]
+            torch.cuda.synchronize()
+        except NotImplementedError as e:
+            if in_place and "registration" in str(e):
+                return None
+            return False, dict(info, error=repr(e))
+        except Exception as e:
+            return False, dict(info, error=repr(e))
+        finally:
+            reader.close()
+    top, left, flip = PO.draw_crop_flip(seed, n, H, W, th, tw, 0)
+    want = TO.transform_batch(imgs[order], crop_top=top, crop_left=left, out_size=(th, tw), flip=flip, mean=m, std=s, dtype=dtype)
+    ok = same(torch.cat([x for x, _ in outs]), want) and torch.cat([y for _, y in outs]).cpu().tolist() == [int(i) % 7 for i in order]
+    return ok, info
+
+
+CASES = [case_transform, case_resize, case_rrc, case_ragged, case_augment, case_metrics, case_image, case_stream, case_chain, case_loader]
 
 
 def main():

@@ -24,6 +24,7 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -360,9 +361,11 @@ struct TbLmdbCuda {
     void* device_base;
 };
 static TbLmdbCuda g_registered[16];
+static std::mutex g_registered_mu;       // register / unregister may come from different threads
 
 extern "C" int tb_lmdb_cuda_register(tb_lmdb* db, void** device_base) {
     TB_REQUIRE(db && device_base, "tb_lmdb_cuda_register: NULL argument");
+    std::lock_guard<std::mutex> lock(g_registered_mu);
     for (auto& r : g_registered)
         if (r.db == db) { *device_base = r.device_base; return TB_OK; }
     int ro_supported = 0, dev = 0;
@@ -390,6 +393,7 @@ extern "C" int tb_lmdb_cuda_register(tb_lmdb* db, void** device_base) {
 }
 
 extern "C" int tb_lmdb_cuda_unregister(tb_lmdb* db) {
+    std::lock_guard<std::mutex> lock(g_registered_mu);
     for (auto& r : g_registered)
         if (r.db == db) {
             cudaHostUnregister((void*)db->map);
