@@ -162,3 +162,53 @@ def test_example_cifar_pipeline_runs():
     rep = mod.main(["--images", "1024", "--batch", "128", "--epochs", "2"])
     assert rep["epoch"] == 1 and rep["images"] == 1024 and 0.0 <= rep["top1"] <= rep["top5"] <= 1.0
     assert np.isfinite(rep["loss"]) and rep["images_per_s"] > 0
+
+
+def test_kernels_replay_from_a_cuda_graph():
+    """Every hot kernel enqueued through the C ABI can be captured once and replayed (bench.py's timed loop is
+    such a graph): crop / flip, resize, augmentation chain and scoring with device-resident parameters."""
+    from torchbooster_b200 import augment as A
+    rng = np.random.default_rng(3)
+    dev = torch.device("cuda")
+    IM = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+    raw = torch.from_numpy(rng.integers(0, 256, (8, 64, 96, 3), dtype=np.uint8)).to(dev)
+    top = torch.from_numpy(rng.integers(0, 17, 8).astype(np.int32)).to(dev)
+    left = torch.from_numpy(rng.integers(0, 33, 8).astype(np.int32)).to(dev)
+    flip = torch.from_numpy(rng.integers(0, 2, 8).astype(np.uint8)).to(dev)
+    ops = [[("Rotate", 9.0), ("Equalize", 0.0)]] * 8
+    rec = torch.from_numpy(A.encode_ops(ops, 48, 64, 3)).to(dev)
+    t_crop = BatchTransform(TransformSpec(crop=(48, 64), flip_p=.5, mean=IM[0], std=IM[1], dtype=torch.bfloat16), device=dev)
+    t_rs = BatchTransform(TransformSpec(resize=(32, 48), mean=IM[0], std=IM[1]), device=dev)
+    t_aug = BatchTransform(TransformSpec(crop=(48, 64), flip_p=.5, rand_augment=True, mean=IM[0], std=IM[1]), device=dev)
+    o_crop = torch.empty((8, 3, 48, 64), dtype=torch.bfloat16, device=dev)
+    o_rs = torch.empty((8, 3, 32, 48), device=dev)
+    o_aug = torch.empty((8, 3, 48, 64), device=dev)
+    logits = torch.randn(8, 10, device=dev)
+    labels = torch.randint(0, 10, (8,), device=dev)
+    state = MetricState(10, k=3, device=dev)
+
+    def step():
+        t_crop(raw, params=(top, left, flip), out=o_crop)
+        t_rs(raw, out=o_rs)
+        t_aug(raw, params=(top, left, flip, rec), out=o_aug)
+        state.update(logits, labels)
+
+    step()                                          # warm-up outside capture: tables, tap tables, function attributes
+    torch.cuda.synchronize()
+    want = (o_crop.clone(), o_rs.clone(), o_aug.clone())
+    state.reset()
+    for o in (o_crop, o_rs, o_aug):
+        o.zero_()
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            step()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    for got, w in zip((o_crop, o_rs, o_aug), want):
+        assert torch.equal(got.view(torch.uint8), w.view(torch.uint8))
+    res = state.compute()
+    assert res["n"] == 24 and res["correct_1"] == 3 * int((logits.argmax(-1) == labels).sum())
