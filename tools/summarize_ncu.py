@@ -90,6 +90,11 @@ def main():
         t = summarize_report(src / "prof_rs.ncu-rep", OUT / f"{tag}_ncu_resize.txt", "resize kernel, C4 workload (batch 256)")
         for name, v in t.items():
             traffic["c4_b256"] = sum(v) / len(v)
+    if (src / "prof_rrc.ncu-rep").exists():
+        t = summarize_report(src / "prof_rrc.ncu-rep", OUT / f"{tag}_ncu_resized_crop.txt",
+                             "resized-crop kernel, 512 x (256x256 box -> 224x224, bf16), per-sample boxes, taps computed in-kernel")
+        for name, v in t.items():
+            traffic["rrc_c2_b512"] = sum(v) / len(v)
     if (src / "prof_aug.ncu-rep").exists():
         t = summarize_report(src / "prof_aug.ncu-rep", OUT / f"{tag}_ncu_augment.txt",
                              "augment kernel, CIFAR training transform (resnet.py:96-103), batch 2048")
