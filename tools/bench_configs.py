@@ -382,9 +382,9 @@ def main():
         rrc_case("rrc_c2_b2048", 2048, 30)
         rrc_case("rrc_c2_b512_two_phase", 512, 100, flags=16)
         if a.quick:
-            for per in (1, 2, 4, 7, 14):
-                rrc_case(f"rrc_c2_b512_per{per}", 512, 100, flags=per << 16)
-                rrc_case(f"rrc_c2_b2048_per{per}", 2048, 30, flags=per << 16)
+            for tr in (16, 32, 64):
+                rrc_case(f"rrc_c2_b512_tr{tr}", 512, 100, flags=tr << 24)
+                rrc_case(f"rrc_c2_b2048_tr{tr}", 2048, 30, flags=tr << 24)
     if want("aug"):
         for bsz in (256, 2048, 16384):
             augment_case(f"aug_cifar_b{bsz}", bsz, 200 if bsz < 10000 else 50)

@@ -506,7 +506,7 @@ __global__ void __launch_bounds__(256) tb_resize_fast_kernel(RsParams p) {
 // Works for every scale the NT taps cover, up- and down-scaling (an output row is emitted after
 // 0, 1 or several pushes).
 // ----------------------------------------------------------------------------------------------
-constexpr int kSlideMaxTR = 32;
+constexpr int kSlideMaxTR = 64;
 
 // v = *p when take, else v keeps its bits (no zeroing, no branch)
 __device__ __forceinline__ void tb_ldg_if(uint32_t& v, const uint32_t* p, bool take) {
@@ -723,11 +723,13 @@ int launch_slide(const RsParams& p, int64_t blocks, int threads, int nt, cudaStr
 // Taller strips recompute fewer halo rows (2 * TR + 2 input rows per TR outputs at scale 2), so TR is
 // the tallest that still puts a full GPU's worth of threads in the grid; small grids are then cut
 // into narrower column tiles until every SM has a few CTAs (measured on C4: batch 256 -> 32 x 256,
-// batch 32 -> 16 x 128).
+// batch 32 -> 16 x 128; 512 resized crops of 224 x 224 -> 64 x 224).
 inline void slide_geometry(RsParams& p, int B, int sm_count, int flags, int64_t* blocks, int* threads) {
     const int64_t want_threads = (int64_t)sm_count * 1024 * 3 / 4;
-    int TR = kSlideMaxTR;
+    int TR = 32;
     while (TR > 8 && (int64_t)B * ((p.out_h + TR - 1) / TR) * p.out_w < want_threads) TR >>= 1;
+    // very large grids afford 64-row strips (halo and per-strip set-up halve again) while >= 12 CTAs per SM remain
+    if (TR == 32 && (int64_t)B * ((p.out_h + 63) / 64) * ((p.out_w + 255) / 256) >= 12 * (int64_t)sm_count) TR = 64;
     int TC = p.out_w < 256 ? p.out_w : 256;
     while (TC > 64 && (int64_t)B * ((p.out_h + TR - 1) / TR) * ((p.out_w + TC - 1) / TC) < 4 * (int64_t)sm_count) TC = ((TC / 2 + 31) / 32) * 32;
     if ((flags >> 24) & 0xff) TR = (flags >> 24) & 0xff;             // development knobs
