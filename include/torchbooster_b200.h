@@ -335,6 +335,11 @@ TB_API int64_t tb_lmdb_entries(const tb_lmdb* db);
 TB_API int     tb_lmdb_get(const tb_lmdb* db, const void* key, int64_t klen, const void** data, int64_t* len);
 TB_API int     tb_lmdb_gather(const tb_lmdb* db, const int64_t* indices, int64_t n, int64_t record_bytes,
                               void* dst, int threads);
+/* Records of different sizes.  dst == NULL: sizes[i] <- length of record str(indices[i]).  Otherwise record i
+ * is also copied to dst + offsets[i] (offsets laid out by the caller from a first call's sizes; capacity =
+ * bytes available at dst).  TB_ENOENT for a missing key. */
+TB_API int     tb_lmdb_gather_ragged(const tb_lmdb* db, const int64_t* indices, int64_t n, int64_t* sizes,
+                                     const int64_t* offsets, void* dst, int64_t capacity, int threads);
 
 /*
  * In-place GPU access to an LMDB database: tb_lmdb_cuda_register page-locks the read-only map and

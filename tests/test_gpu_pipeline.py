@@ -212,3 +212,34 @@ def test_kernels_replay_from_a_cuda_graph():
         assert torch.equal(got.view(torch.uint8), w.view(torch.uint8))
     res = state.compute()
     assert res["n"] == 24 and res["correct_1"] == 3 * int((logits.argmax(-1) == labels).sum())
+
+
+def test_batch_loader_over_images_of_different_sizes(tmp_path):
+    """LMDB of differently sized images (TBI1 records) -> BatchLoader(ragged=True) -> Resize + CenterCrop, and
+    seeded RandomResizedCrop + flip, one launch per batch, against torchvision per sample."""
+    import torchvision.transforms as T
+    from PIL import Image
+    from torchbooster_b200.lmdb import write_ragged_image_lmdb
+    from torchbooster_b200.loader import BatchLoader
+    rng = np.random.default_rng(14)
+    n = 70
+    imgs = [rng.integers(0, 256, (int(h), int(w), 3), dtype=np.uint8) for h, w in zip(rng.integers(40, 160, n), rng.integers(40, 160, n))]
+    write_ragged_image_lmdb(str(tmp_path / "db"), imgs, labels=np.arange(n) % 4)
+    reader = LMDBReader(str(tmp_path / "db"))
+    order = rng.permutation(n).tolist()
+    IM = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+    spec = TransformSpec(resize=48, center_crop=40, mean=IM[0], std=IM[1])
+    loader = BatchLoader(reader, (0, 0, 3), 16, sampler=order, labels=reader.read_labels(), ragged=True,
+                         transform=BatchTransform(spec, device="cuda"), threads=3)
+    outs = [(x.clone(), y.clone()) for x, y in loader]
+    torch.cuda.synchronize()
+    want = torch.stack([TO.transform_sample(imgs[i], resize=48, center_crop=40, mean=IM[0], std=IM[1]) for i in order])
+    assert torch.equal(torch.cat([x for x, _ in outs]).cpu(), want)
+    assert torch.cat([y for _, y in outs]).cpu().tolist() == [i % 4 for i in order]
+    compose = T.Compose([T.RandomResizedCrop(32), T.RandomHorizontalFlip(), T.ToTensor(), T.Normalize(IM[0], IM[1])])
+    torch.manual_seed(5)
+    want = torch.stack([compose(Image.fromarray(imgs[i])) for i in order])
+    spec = TransformSpec(random_resized_crop=32, flip_p=.5, mean=IM[0], std=IM[1])
+    loader = BatchLoader(reader, (0, 0, 3), 32, sampler=order, ragged=True, transform=BatchTransform(spec, device="cuda", seed=5))
+    got = torch.cat([x.clone() for x, _ in loader])
+    assert torch.equal(got.cpu(), want)

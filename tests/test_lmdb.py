@@ -148,3 +148,31 @@ def test_batch_loader_host_side(image_db):
 def torch_equal_list(tensors, want):
     import torch
     return np.array_equal(torch.cat(tensors).numpy(), np.asarray(want))
+
+
+def test_ragged_image_records_round_trip(tmp_path):
+    """Images of different sizes: 16-byte TBI1 header + rows padded to 4 bytes; gathered back to back with
+    16-byte aligned offsets; missing keys and a reused (too small, then large enough) buffer."""
+    import torch
+    from torchbooster_b200.lmdb import RAGGED_MAGIC, write_ragged_image_lmdb
+    rng = np.random.default_rng(2)
+    sizes = [(10, 7), (33, 21), (5, 40), (1, 1), (64, 50), (300, 200)]          # the last ones live on overflow pages
+    imgs = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in sizes]
+    write_ragged_image_lmdb(str(tmp_path / "db"), imgs, labels=range(len(imgs)))
+    reader = LMDBReader(str(tmp_path / "db"))
+    assert len(reader) == len(imgs) and reader.read_labels().tolist() == list(range(len(imgs)))
+    order = [5, 0, 3, 1, 4, 2]
+    small = torch.empty(64, dtype=torch.uint8)
+    buf, off, sz = reader.get_ragged_batch(order, out=small, threads=3)
+    assert buf.numel() >= int(off[-1] + sz[-1]) and (off % 16 == 0).all()
+    again, off2, _ = reader.get_ragged_batch(order, out=buf, threads=1)
+    assert again.data_ptr() == buf.data_ptr() and np.array_equal(off, off2)
+    hv = buf.numpy()
+    for o, i in zip(off, order):
+        magic, h, w, c = (int(v) for v in hv[o:o + 16].view("<u4"))
+        assert magic == RAGGED_MAGIC and (h, w, c) == imgs[i].shape
+        pitch = (w * c + 3) // 4 * 4
+        assert np.array_equal(hv[o + 16:o + 16 + h * pitch].reshape(h, pitch)[:, :w * c].reshape(h, w, c), imgs[i])
+    with pytest.raises(KeyError):
+        reader.get_ragged_batch([0, 99])
+    assert reader.get_ragged_batch([])[1].shape == (0,)

@@ -55,6 +55,7 @@ SIGNATURES = {
     "tb_lmdb_entries": (_i64, [_vp]),
     "tb_lmdb_get": (_i32, [_vp, C.c_char_p, _i64, C.POINTER(_vp), C.POINTER(_i64)]),
     "tb_lmdb_gather": (_i32, [_vp, _vp, _i64, _i64, _vp, _i32]),
+    "tb_lmdb_gather_ragged": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i64, _i32]),
     "tb_lmdb_cuda_register": (_i32, [_vp, C.POINTER(_vp)]),
     "tb_lmdb_cuda_unregister": (_i32, [_vp]),
     "tb_lmdb_record_offsets": (_i32, [_vp, _vp, _i64, _i64, _vp]),

@@ -270,6 +270,49 @@ extern "C" int tb_lmdb_gather(const tb_lmdb* db, const int64_t* indices, int64_t
     return TB_OK;
 }
 
+// Records of different sizes (images stored with a small header, torchbooster_b200/lmdb.py
+// write_ragged_image_lmdb).  Two uses of one call: with dst == NULL it reports sizes[i] = length of
+// record str(indices[i]); with dst it also copies record i to dst + offsets[i] (the caller laid the
+// offsets out from the sizes of a first call) and checks every record still has that size.
+extern "C" int tb_lmdb_gather_ragged(const tb_lmdb* db, const int64_t* indices, int64_t n, int64_t* sizes,
+                                            const int64_t* offsets, void* dst, int64_t capacity, int threads) {
+    TB_REQUIRE(db && n >= 0 && (n == 0 || (indices && sizes)), "tb_lmdb_gather_ragged: bad argument");
+    TB_REQUIRE(dst == nullptr || offsets != nullptr, "tb_lmdb_gather_ragged: a destination needs offsets");
+    if (threads < 1) threads = 1;
+    if (threads > n) threads = (int)(n ? n : 1);
+    std::vector<int> status(threads, 0);
+    std::vector<int64_t> bad(threads, -1);
+    auto work = [&](int t) {
+        char key[24];
+        for (int64_t i = t; i < n; i += threads) {
+            const int kl = snprintf(key, sizeof(key), "%lld", (long long)indices[i]);
+            const uint8_t* d = nullptr;
+            size_t len = 0;
+            const int rc = lookup(db, key, (size_t)kl, &d, &len);
+            if (rc != 0) { status[t] = rc == 1 ? 1 : 2; bad[t] = indices[i]; return; }
+            if (dst) {
+                if ((int64_t)len != sizes[i] || offsets[i] < 0 || offsets[i] + (int64_t)len > capacity) { status[t] = 3; bad[t] = indices[i]; return; }
+                memcpy((uint8_t*)dst + offsets[i], d, len);
+            } else {
+                sizes[i] = (int64_t)len;
+            }
+        }
+    };
+    if (threads == 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < threads; ++t) pool.emplace_back(work, t);
+        for (auto& th : pool) th.join();
+    }
+    for (int t = 0; t < threads; ++t) {
+        if (status[t] == 1) return tb_fail(TB_ENOENT, "tb_lmdb_gather_ragged: key %lld not found", (long long)bad[t]);
+        if (status[t] == 2) return tb_fail(TB_EINVAL, "tb_lmdb_gather_ragged: corrupt page structure at key %lld", (long long)bad[t]);
+        if (status[t] == 3) return tb_fail(TB_EINVAL, "tb_lmdb_gather_ragged: record %lld changed size or does not fit the destination", (long long)bad[t]);
+    }
+    return TB_OK;
+}
+
 // ----------------------------------------------------------------------------------------------
 // Host helper of T.RandomResizedCrop's parameter replay: the sequential accept / reject walk of
 // RandomResizedCrop.get_params (torchvision/transforms/transforms.py) over pre-drawn generator

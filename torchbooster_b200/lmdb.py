@@ -102,6 +102,38 @@ class LMDBReader:
         N.check(rc)
         return out
 
+    def get_ragged_batch(self, indices, out=None, threads: int = 8):
+        """Records ``str(i)`` of DIFFERENT sizes -> ``(buffer, offsets, sizes)``: one pinned ``uint8`` host tensor
+        holding them back to back (every record starts on a 16-byte boundary), the byte offset and length of
+        each.  ``out``: a pinned tensor to reuse when it is large enough."""
+        import numpy as np
+        import torch
+        if self.env is None or getattr(self, "_pid", None) != os.getpid():
+            self.env = None
+            self.open()
+        idx = np.ascontiguousarray(np.asarray(indices, dtype=np.int64))
+        n = int(idx.shape[0])
+        sizes = np.zeros(n, np.int64)
+        L = N.lib()
+
+        def call(offsets, dst, capacity):
+            rc = L.tb_lmdb_gather_ragged(self.env, idx.ctypes.data, n, sizes.ctypes.data,
+                                         None if offsets is None else offsets.ctypes.data, dst, capacity, threads)
+            if rc == N.TB_ENOENT:
+                raise KeyError(N.last_error())
+            N.check(rc)
+
+        call(None, None, 0)
+        padded = (sizes + 15) // 16 * 16
+        offsets = np.concatenate([[0], np.cumsum(padded)[:-1]]).astype(np.int64) if n else np.zeros(0, np.int64)
+        total = int(padded.sum())
+        if out is None or out.numel() < total:
+            out = torch.empty(max(total, 16), dtype=torch.uint8, pin_memory=torch.cuda.is_available())
+        elif out.dtype != torch.uint8 or not out.is_contiguous() or out.is_cuda:
+            raise ValueError("out must be a contiguous host uint8 tensor")
+        call(offsets, out.data_ptr(), out.numel())
+        return out, offsets, sizes
+
     def cuda_register(self) -> int:
         """Page-lock the map and map it into the GPU's address space; returns the device address
         of its first byte.  Afterwards ``BatchTransform.from_records`` / ``BatchLoader(in_place=True)``
@@ -307,6 +339,35 @@ def write_image_lmdb(path: str, images, labels: Optional[Iterable[int]] = None) 
     items = [(str(i).encode(), images[i].tobytes()) for i in range(images.shape[0])]
     items.append((b"length", str(images.shape[0]).encode()))
     items.append((b"shape", ",".join(str(s) for s in images.shape[1:]).encode()))
+    if labels is not None:
+        labels = [int(l) for l in labels]
+        items += [(f"label/{i}".encode(), str(l).encode()) for i, l in enumerate(labels)]
+        items.append((b"labels", np.asarray(labels, dtype="<i8").tobytes()))
+    return write_lmdb(path, items)
+
+
+RAGGED_MAGIC = 0x31494254          # "TBI1": header of an image record that carries its own shape
+
+
+def write_ragged_image_lmdb(path: str, images, labels: Optional[Iterable[int]] = None) -> str:
+    """Images of DIFFERENT sizes: record ``str(i)`` = 16-byte header ``{magic "TBI1", H, W, C}`` (little-endian
+    uint32) + the rows of the uint8 HWC image, each padded to a multiple of 4 bytes -- the layout
+    ``BatchTransform.ragged_records`` hands to the kernel as it is.  ``labels`` / ``length`` as in
+    ``write_image_lmdb``."""
+    import numpy as np
+    items = []
+    for i, im in enumerate(images):
+        a = np.ascontiguousarray(np.asarray(im))
+        if a.dtype != np.uint8 or a.ndim != 3:
+            raise ValueError("images must be uint8 [H,W,C] arrays")
+        h, w, c = a.shape
+        pitch = (w * c + 3) // 4 * 4
+        rows = np.zeros((h, pitch), np.uint8)
+        rows[:, :w * c] = a.reshape(h, w * c)
+        items.append((str(i).encode(), np.array([RAGGED_MAGIC, h, w, c], "<u4").tobytes() + rows.tobytes()))
+    n = len(items)
+    items.append((b"length", str(n).encode()))
+    items.append((b"shape", b"ragged"))
     if labels is not None:
         labels = [int(l) for l in labels]
         items += [(f"label/{i}".encode(), str(l).encode()) for i, l in enumerate(labels)]

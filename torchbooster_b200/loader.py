@@ -36,7 +36,7 @@ class BatchLoader:
 
     def __init__(self, reader: LMDBReader, shape: Tuple[int, int, int], batch_size: int,
                  sampler: Optional[Iterable[int]] = None, transform=None, labels=None, drop_last: bool = False,
-                 prefetch: int = 2, threads: int = 8, in_place: bool = False) -> None:
+                 prefetch: int = 2, threads: int = 8, in_place: bool = False, ragged: bool = False) -> None:
         if batch_size < 1 or prefetch < 1:
             raise ValueError("batch_size and prefetch must be >= 1")
         self.reader, self.shape, self.batch_size = reader, tuple(int(s) for s in shape), int(batch_size)
@@ -45,6 +45,11 @@ class BatchLoader:
         self.record_bytes = int(np.prod(self.shape))
         self.labels = None if labels is None else torch.as_tensor(np.asarray(labels), dtype=torch.int64)
         self._pin = torch.cuda.is_available()
+        # ragged: records of different sizes (write_ragged_image_lmdb); `shape` is ignored, the transform
+        # must be a resize (+ center_crop) or random_resized_crop pipeline
+        self.ragged = bool(ragged)
+        if self.ragged and (transform is None or in_place):
+            raise ValueError("ragged needs a transform and excludes in_place")
         # in_place: the database map is registered with CUDA and the kernel reads the records where
         # they lie -- no gather at all; the background thread only looks the record offsets up.
         self._base = None
@@ -68,6 +73,9 @@ class BatchLoader:
         slots = [] if self._base is not None else [
             torch.empty((self.batch_size, self.record_bytes), dtype=torch.uint8, pin_memory=self._pin)
             for _ in range(nslots)]
+        if self.ragged:
+            slots = []
+        ragged_slots = [None] * nslots
         released = [None] * nslots          # CUDA event after the last kernel that read the slot
         q: "queue.Queue" = queue.Queue(maxsize=self.prefetch)
         stop = threading.Event()
@@ -85,6 +93,11 @@ class BatchLoader:
                     ev = released[s]
                     if ev is not None:
                         ev.synchronize()
+                    if self.ragged:
+                        buf, off, _ = self.reader.get_ragged_batch(idx, out=ragged_slots[s], threads=self.threads)
+                        ragged_slots[s] = buf            # grown when a batch did not fit
+                        q.put(((s, off), idx))
+                        continue
                     out = slots[s][:idx.shape[0]]
                     self.reader.get_batch(idx, self.record_bytes, out=out, threads=self.threads)
                     q.put((s, idx))
@@ -107,6 +120,17 @@ class BatchLoader:
                     y = None
                     if self.labels is not None:
                         y = self.labels[torch.from_numpy(idx)].pin_memory().to(self.transform.device, non_blocking=True)
+                    yield x, y
+                    continue
+                if self.ragged:
+                    slot, off = s
+                    x = self.transform.ragged_records(ragged_slots[slot], off)
+                    y = None
+                    if self.labels is not None:
+                        y = self.labels[torch.from_numpy(idx)].pin_memory().to(self.transform.device, non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(torch.cuda.current_stream(self.transform.device))
+                    released[slot] = ev
                     yield x, y
                     continue
                 raw = slots[s][:idx.shape[0]].view(idx.shape[0], *self.shape)

@@ -535,32 +535,12 @@ class BatchTransform:
         return out
 
     # -- ragged batches --------------------------------------------------------------------
-    def ragged(self, images, params=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """A batch of images of DIFFERENT sizes (what the reference's datasets really hold: paintings and
-        COCO photographs under ``T.Resize(size) + T.CenterCrop(size)``, ``adain.py:170``; ImageNet-style
-        ``T.RandomResizedCrop``) -> one ``[B,C,h,w]`` tensor, one launch.
-
-        ``images``: sequence of ``uint8 [H_b, W_b, C]`` host arrays / tensors.  Supported pipelines:
-        ``resize`` (+ ``center_crop``) with a common output size, and ``random_resized_crop`` (+ flip);
-        ``params=(boxes[B,4], flip)`` or a seed for the latter.  Every sample's taps are computed in the
-        kernel for its own (size -> resized size); a region more than four times its resized size gets its
-        own launch of the any-scale kernel inside the same call.
-        """
+    def _ragged_geometry(self, sizes: np.ndarray, params):
+        """Per-sample records ``[top, left, h, w, resized h, resized w, y, x, image h, image w]`` for images of the
+        given sizes under this spec (resize + center_crop, or random_resized_crop), the flips, and the output size."""
         sp = self.spec
         rrc = sp.random_resized_crop is not None
-        if sp.augments or sp.pre_rotation is not None or sp.crop is not None or _pair(sp.padding) != (0, 0) or \
-                (not rrc and sp.resize is None):
-            raise NotImplementedError("ragged batches: resize (+ center_crop) or random_resized_crop (+ flip) pipelines")
-        arrs = [np.ascontiguousarray(im.numpy() if isinstance(im, torch.Tensor) else np.asarray(im)) for im in images]
-        B = len(arrs)
-        if B == 0:
-            raise ValueError("ragged() needs at least one image")
-        Cn = arrs[0].shape[2] if arrs[0].ndim == 3 else 0
-        for a in arrs:
-            if a.dtype != np.uint8 or a.ndim != 3 or a.shape[2] != Cn:
-                raise TypeError("images must be uint8 [H,W,C] arrays with the same channel count")
-        sizes = np.array([a.shape[:2] for a in arrs], np.int64)
-        # ---- per-sample geometry ---------------------------------------------------------
+        B = int(sizes.shape[0])
         geom = np.zeros((B, 10), np.int32)
         geom[:, 8:10] = sizes
         flip = None
@@ -585,6 +565,64 @@ class BatchTransform:
                 elif fixed != g["out"]:
                     raise ValueError(f"images resize to different output sizes ({fixed} and {g['out']}); add center_crop")
             out_h, out_w = fixed
+        return geom, flip, out_h, out_w
+
+    def _check_ragged_spec(self) -> None:
+        sp = self.spec
+        if sp.augments or sp.pre_rotation is not None or sp.crop is not None or _pair(sp.padding) != (0, 0) or \
+                (sp.random_resized_crop is None and sp.resize is None):
+            raise NotImplementedError("ragged batches: resize (+ center_crop) or random_resized_crop (+ flip) pipelines")
+
+    def ragged_records(self, buffer: torch.Tensor, offsets, params=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """The same over image records as ``write_ragged_image_lmdb`` stores them (16-byte ``TBI1`` header + rows
+        padded to 4 bytes), lying in one host buffer at ``offsets`` -- what ``LMDBReader.get_ragged_batch``
+        returns: the buffer goes to the device as it is and the kernel reads every image where it lies."""
+        from .lmdb import RAGGED_MAGIC
+        self._check_ragged_spec()
+        off = np.ascontiguousarray(np.asarray(offsets, np.int64))
+        B = int(off.shape[0])
+        if B == 0:
+            raise ValueError("ragged_records() needs at least one record")
+        hv = buffer.numpy()
+        if int((off % 4).max()):
+            raise ValueError("record offsets must be multiples of 4 bytes")
+        head = np.stack([hv[o:o + 16].view("<u4") for o in off]).astype(np.int64)
+        if (head[:, 0] != RAGGED_MAGIC).any():
+            raise ValueError("a record does not start with the TBI1 image header (write_ragged_image_lmdb)")
+        sizes, chans = head[:, 1:3], head[:, 3]
+        Cn = int(chans[0])
+        if (chans != Cn).any():
+            raise ValueError("records hold different channel counts")
+        geom, flip, out_h, out_w = self._ragged_geometry(sizes, params)
+        pitches = ((sizes[:, 1] * Cn + 3) // 4 * 4).astype(np.int32)
+        if not buffer.is_pinned():
+            buffer = buffer.pin_memory()
+        self._ragged_host = buffer
+        dsrc = buffer.to(self.device, non_blocking=True)
+        return self._launch_ragged(dsrc, off + 16, pitches, geom, flip, Cn, out_h, out_w, out)
+
+    def ragged(self, images, params=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """A batch of images of DIFFERENT sizes (what the reference's datasets really hold: paintings and
+        COCO photographs under ``T.Resize(size) + T.CenterCrop(size)``, ``adain.py:170``; ImageNet-style
+        ``T.RandomResizedCrop``) -> one ``[B,C,h,w]`` tensor, one launch.
+
+        ``images``: sequence of ``uint8 [H_b, W_b, C]`` host arrays / tensors.  Supported pipelines:
+        ``resize`` (+ ``center_crop``) with a common output size, and ``random_resized_crop`` (+ flip);
+        ``params=(boxes[B,4], flip)`` or a seed for the latter.  Every sample's taps are computed in the
+        kernel for its own (size -> resized size); a region more than four times its resized size gets its
+        own launch of the any-scale kernel inside the same call.
+        """
+        self._check_ragged_spec()
+        arrs = [np.ascontiguousarray(im.numpy() if isinstance(im, torch.Tensor) else np.asarray(im)) for im in images]
+        B = len(arrs)
+        if B == 0:
+            raise ValueError("ragged() needs at least one image")
+        Cn = arrs[0].shape[2] if arrs[0].ndim == 3 else 0
+        for a in arrs:
+            if a.dtype != np.uint8 or a.ndim != 3 or a.shape[2] != Cn:
+                raise TypeError("images must be uint8 [H,W,C] arrays with the same channel count")
+        sizes = np.array([a.shape[:2] for a in arrs], np.int64)
+        geom, flip, out_h, out_w = self._ragged_geometry(sizes, params)
         # ---- pack: rows padded to 4 bytes, images to 16 -----------------------------------
         pitches = ((sizes[:, 1] * Cn + 3) // 4 * 4).astype(np.int32)
         nbytes = (sizes[:, 0] * pitches + 15) // 16 * 16
