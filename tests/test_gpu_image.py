@@ -47,6 +47,36 @@ def test_round_trip_and_batches():
     assert ToImage.to_pil(back[0]).size == (56, 40)
 
 
+def signed_zero_cases():
+    """Tensors whose extrema involve -0.0 (its bit pattern is INT_MIN: an atomic on the signed view of a float
+    must not treat it as 'non-negative')."""
+    g = torch.Generator().manual_seed(11)
+    # (a) the maximum is exactly -0.0, everything else negative: hi must be -0.0, not a value below it
+    a = -torch.rand((3, 64, 96), generator=g) - 0.25
+    a[:, 10, 32:64] = -0.0
+    # (b) one whole warp's share is -0.0 while other warps hold the (negative) minimum and a positive maximum
+    b = torch.randn((3, 128, 128), generator=g)
+    b[:, 40:44, :] = -0.0
+    # (c) only zeros of both signs and negatives; single channel
+    c = -torch.rand((1, 50, 70), generator=g)
+    c[0, ::3] = -0.0
+    c[0, 1, 1] = 0.0
+    return [a, b, c]
+
+
+@pytest.mark.parametrize("case", [0, 1, 2])
+def test_stretch_with_negative_zero_extrema(case):
+    x = signed_zero_cases()[case]
+    want = TO.to_image(x, mode="stretch")
+    ti = ToImage(mode="stretch")
+    for _ in range(8):                                       # the old fault depended on the order of the atomics
+        assert np.array_equal(ti(x.cuda()).cpu().numpy(), want)
+    n = x.shape[0]
+    m, s = MEAN[:n], STD[:n]
+    want = TO.to_image(x, mean=-m / s, std=1.0 / s, mode="stretch")
+    assert np.array_equal(ToImage.inverse_of(m, s, "stretch")(x.cuda()).cpu().numpy(), want)
+
+
 def test_constant_input_and_errors():
     x = torch.full((3, 8, 8), 0.25)
     got = ToImage(mode="stretch")(x.cuda())                  # 0 / 0 = NaN -> byte 0, as on the CPU

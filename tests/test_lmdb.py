@@ -176,3 +176,43 @@ def test_ragged_image_records_round_trip(tmp_path):
     with pytest.raises(KeyError):
         reader.get_ragged_batch([0, 99])
     assert reader.get_ragged_batch([])[1].shape == (0,)
+
+
+def test_reopen_and_len_do_not_leak_or_close_an_open_reader(tmp_path):
+    """open() twice releases the first handle; len() on an OPEN reader whose database has no length key (length
+    0) neither reopens nor closes it (only a closed reader does the reference's open-and-close, lmdb.py:85-90)."""
+    write_lmdb(str(tmp_path / "nolen"), [(b"0", b"abc")])
+    r = LMDBReader(str(tmp_path / "nolen"))
+    r.open()
+    first = r.env.value
+    r.open()
+    assert r.env is not None and r.get(b"0") == b"abc"
+    held = r.env.value
+    assert len(r) == 0 and r.env is not None and r.env.value == held
+    r.close()
+    assert len(r) == 0 and r.env is None
+    del first
+
+
+def test_unsupported_main_db_flags_are_refused(tmp_path):
+    """A main database with reverse / integer keys or duplicates is not misread as 'key not found': it does not open."""
+    write_lmdb(str(tmp_path / "db"), [(b"0", b"abc"), (b"length", b"1")])
+    f = tmp_path / "db" / "data.mdb"
+    raw = bytearray(f.read_bytes())
+    psize = int.from_bytes(raw[16 + 24:16 + 28], "little")
+    for page in (0, 1):
+        off = page * psize + 16 + 24 + 48 + 4           # meta: dbs[1].md_flags
+        raw[off:off + 2] = (0x08).to_bytes(2, "little")  # MDB_INTEGERKEY
+    f.write_bytes(bytes(raw))
+    with pytest.raises(IOError, match="not supported"):
+        LMDBReader(str(tmp_path / "db")).open()
+
+
+def test_map_is_read_only_and_unreserved(tmp_path):
+    """The reader's map is PROT_READ (what readonly=True gives the reference): it shows as 'r--p' in /proc/self/maps."""
+    write_lmdb(str(tmp_path / "db"), [(b"0", b"abc"), (b"length", b"1")])
+    r = LMDBReader(str(tmp_path / "db"))
+    r.open()
+    lines = [ln for ln in open("/proc/self/maps") if str(tmp_path / "db" / "data.mdb") in ln]
+    assert lines and all(ln.split()[1] == "r--p" for ln in lines)
+    r.close()

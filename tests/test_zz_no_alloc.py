@@ -51,3 +51,38 @@ def test_grey_and_limits():
     assert rc == N.TB_EINVAL and "beyond" in N.last_error()
     empty = torch.zeros((0, 3, 4, 4), device="cuda")
     assert _static(empty, ti.mean, ti.std, torch.empty((0, 4, 4, 3), dtype=torch.uint8, device="cuda")) == N.TB_OK
+
+
+def test_negative_zero_extrema_through_the_fixed_array():
+    """Same bytes as the two-call form when -0.0 is an extremum (the atomics branch on the sign bit)."""
+    from test_gpu_image import signed_zero_cases
+    for x in signed_zero_cases():
+        Cn, H, W = x.shape
+        ti = ToImage(mode="stretch")
+        xb = x.cuda()[None]
+        want = ti(xb[0])
+        out = torch.empty((1, H, W, Cn), dtype=torch.uint8, device="cuda")
+        mean32, std32 = np.zeros(Cn, np.float32), np.ones(Cn, np.float32)
+        for _ in range(4):
+            N.check(_static(xb, mean32, std32, out))
+            assert torch.equal(out[0], want)
+
+
+def test_a_refused_call_enqueues_nothing():
+    """Every argument rule is checked before the first launch: the launch counter of the library stays put."""
+    ok = torch.zeros((1, 3, 4, 4), device="cuda")
+    out = torch.empty((1, 4, 4, 3), dtype=torch.uint8, device="cuda")
+    one, zero = np.ones(3, np.float32), np.zeros(3, np.float32)
+    two = torch.zeros((1, 2, 4, 4), device="cuda")
+    lib = N.lib()
+    before = lib.tb_launch_count()
+    assert _static(two, zero[:2], one[:2], torch.empty((1, 4, 4, 2), dtype=torch.uint8, device="cuda")) == N.TB_EINVAL
+    assert "tb_to_image_stretch_u8_static" in N.last_error() and "PIL mode" in N.last_error()
+    assert _static(ok, zero, zero, out) == N.TB_EINVAL and "division by zero" in N.last_error()
+    assert _static(ok, zero, -one, out) == N.TB_EINVAL and "std > 0" in N.last_error()
+    B, Cn, H, W = ok.shape
+    assert lib.tb_to_image_stretch_u8_static(ok.data_ptr(), B, Cn, H, W, zero.ctypes.data, None, out.data_ptr(),
+                                             N.current_stream_ptr(ok.device)) == N.TB_EINVAL
+    assert lib.tb_to_image_stretch_u8_static(None, B, Cn, H, W, zero.ctypes.data, one.ctypes.data, out.data_ptr(),
+                                             N.current_stream_ptr(ok.device)) == N.TB_EINVAL
+    assert lib.tb_launch_count() == before

@@ -28,12 +28,19 @@ struct ImgParams {
     const float* minmax;    // device [C][2]: per-channel min, max of src (TB_IMAGE_STRETCH)
 };
 
+// Float extrema through integer atomics on the bit pattern.  The branch is on the SIGN BIT, not on
+// `v >= 0`: -0.0f compares equal to zero but its pattern is 0x80000000 (INT_MIN as a signed int), which
+// on the signed route would wipe out a negative minimum already stored and could never raise a maximum.
+// Sign clear: signed order == float order (and every sign-set pattern is a negative int, so it wins a min
+// and loses a max as it should).  Sign set: unsigned order is the reverse float order, and every sign-set
+// pattern is above every sign-clear one.  NaNs never get here (fminf / fmaxf drop them; torch.min / max
+// would propagate them and the stretched image would be all-NaN, i.e. undefined bytes, either way).
 __device__ __forceinline__ void atomic_min_float(float* addr, float v) {
-    if (v >= 0.0f) atomicMin((int*)addr, __float_as_int(v));
+    if (__float_as_int(v) >= 0) atomicMin((int*)addr, __float_as_int(v));
     else atomicMax((unsigned int*)addr, __float_as_uint(v));
 }
 __device__ __forceinline__ void atomic_max_float(float* addr, float v) {
-    if (v >= 0.0f) atomicMax((int*)addr, __float_as_int(v));
+    if (__float_as_int(v) >= 0) atomicMax((int*)addr, __float_as_int(v));
     else atomicMin((unsigned int*)addr, __float_as_uint(v));
 }
 
@@ -118,27 +125,39 @@ extern "C" int tb_channel_minmax(const float* src, int64_t images, int C, int64_
     return TB_OK;
 }
 
+// Every argument rule of the display transform in one place, so that an entry point that enqueues several
+// kernels (the static stretch below) can refuse a bad call BEFORE its first launch.
+static int check_to_image_args(const char* fn, const float* src, int64_t images, int C, int H, int W, const float* mean,
+                               const float* std, int mode, bool minmax_given, const uint8_t* dst) {
+    TB_REQUIRE(images >= 0 && H >= 1 && W >= 1, "%s: bad shape", fn);
+    TB_REQUIRE(C == 1 || C == 3 || C == 4, "%s: C=%d is not a PIL mode (1, 3 or 4 channels)", fn, C);
+    TB_REQUIRE(mode >= TB_IMAGE_PLAIN && mode <= TB_IMAGE_STRETCH, "%s: unknown mode %d", fn, mode);
+    TB_REQUIRE((mean == nullptr) == (std == nullptr), "%s: mean and std come together", fn);
+    for (int c = 0; c < C && mean; ++c) {
+        // torchvision raises for a zero std (_functional_tensor.py:923-924); the stretch relies on std > 0
+        TB_REQUIRE(std[c] != 0.0f, "%s: std evaluated to zero, leading to division by zero", fn);
+        TB_REQUIRE(mode != TB_IMAGE_STRETCH || std[c] > 0.0f, "%s: the stretch needs std > 0", fn);
+    }
+    if (images == 0) return TB_OK;
+    TB_REQUIRE(src && dst, "%s: NULL src/dst", fn);
+    TB_REQUIRE(mode != TB_IMAGE_STRETCH || minmax_given, "%s: the stretch needs the per-channel extrema (tb_channel_minmax)", fn);
+    return TB_OK;
+}
+
 extern "C" int tb_to_image_u8(const float* src, int64_t images, int C, int H, int W, const float* mean, const float* std,
                               int mode, const float* minmax, uint8_t* dst, tb_stream_t stream) {
-    TB_REQUIRE(images >= 0 && H >= 1 && W >= 1, "tb_to_image_u8: bad shape");
-    TB_REQUIRE(C == 1 || C == 3 || C == 4, "tb_to_image_u8: C=%d is not a PIL mode (1, 3 or 4 channels)", C);
-    TB_REQUIRE(mode >= TB_IMAGE_PLAIN && mode <= TB_IMAGE_STRETCH, "tb_to_image_u8: unknown mode %d", mode);
-    TB_REQUIRE((mean == nullptr) == (std == nullptr), "tb_to_image_u8: mean and std come together");
+    int rc = check_to_image_args("tb_to_image_u8", src, images, C, H, W, mean, std, mode, minmax != nullptr, dst);
+    if (rc) return rc;
     if (images == 0) return TB_OK;
-    TB_REQUIRE(src && dst, "tb_to_image_u8: NULL src/dst");
-    TB_REQUIRE(mode != TB_IMAGE_STRETCH || minmax, "tb_to_image_u8: the stretch needs the per-channel extrema (tb_channel_minmax)");
     ImgParams p;
     p.src = src; p.dst = dst; p.images = images; p.C = C; p.plane = (int64_t)H * W; p.mode = mode; p.minmax = minmax;
     for (int c = 0; c < 4; ++c) { p.mean[c] = 0.0f; p.std[c] = 1.0f; }
     for (int c = 0; c < C && mean; ++c) {
-        // torchvision raises for a zero std (_functional_tensor.py:923-924); the stretch relies on std > 0
-        TB_REQUIRE(std[c] != 0.0f, "tb_to_image_u8: std evaluated to zero, leading to division by zero");
-        TB_REQUIRE(mode != TB_IMAGE_STRETCH || std[c] > 0.0f, "tb_to_image_u8: the stretch needs std > 0");
         p.mean[c] = mean[c];
         p.std[c] = std[c];
     }
     TbDevice dev;
-    int rc = tb_device(&dev);
+    rc = tb_device(&dev);
     if (rc) return rc;
     const int64_t total = images * p.plane;
     const int64_t want = (total + 255) / 256, cap = (int64_t)dev.sm_count * 16;
@@ -191,9 +210,12 @@ extern "C" int tb_to_image_stretch_u8_static(const float* src, int64_t images, i
                                              const float* std, uint8_t* dst, tb_stream_t stream) {
     TB_REQUIRE(C >= 1 && C <= TB_IMAGE_STATIC_MAX_CHANNELS, "tb_to_image_stretch_u8_static: C=%d beyond the %d channels the fixed array holds",
                C, TB_IMAGE_STATIC_MAX_CHANNELS);
-    TB_REQUIRE(images >= 0 && H >= 1 && W >= 1, "tb_to_image_stretch_u8_static: bad shape");
+    // every argument rule of the two passes, checked before anything is enqueued: a refused call leaves
+    // neither kernels on the stream nor the shared array touched
+    int rc = check_to_image_args("tb_to_image_stretch_u8_static", src, images, C, H, W, mean, std, TB_IMAGE_STRETCH, true, dst);
+    if (rc) return rc;
     float* extrema = nullptr;
-    int rc = stretch_extrema(&extrema);
+    rc = stretch_extrema(&extrema);
     if (rc) return rc;
     if (images == 0) return TB_OK;
     tb_reset_extrema_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(extrema, C);

@@ -4,7 +4,8 @@
 // lmdb.open(readonly=True, lock=False, readahead=False) -> txn.get(key)), which is absent from
 // this image.  Only what that call path needs: newest valid meta page, main DB B-tree descent
 // with memcmp key order, leaf nodes and overflow ("big data") values.  No writes, no locks, no
-// sub-databases / dupsort.  Values are returned as pointers into the private read-only map.
+// sub-databases / dupsort / reverse or integer keys (refused at open).  Values are returned as pointers into
+// the private read-only map.
 //
 // On-disk layout restated from liblmdb's mdb.c (not vendored in the reference; no .mdb fixture
 // exists there either -- parity for this reader is UNPINNED):
@@ -172,11 +173,10 @@ extern "C" int tb_lmdb_open(const char* path, tb_lmdb** out) {
         close(fd);
         return tb_fail(TB_EINVAL, "tb_lmdb_open: %s is too small to be an LMDB data file", file.c_str());
     }
-    // Private copy-on-write mapping that is never written.  PROT_WRITE is only there because
-    // cudaHostRegister (tb_lmdb_cuda_register) refuses mappings without it (measured on this
-    // platform: every PROT_READ-only file mapping fails with cudaErrorInvalidValue, even with
-    // cudaHostRegisterReadOnly).
-    void* map = mmap(nullptr, size, PROT_READ | PROT_WRITE, MAP_PRIVATE, fd, 0);
+    // Read-only private mapping, no swap reservation: what lmdb.open(readonly=True, lock=False) gives the
+    // reference (torchbooster/lmdb.py:50-58) -- a database larger than RAM + swap opens, and nothing is charged
+    // against the commit limit.  Only tb_lmdb_cuda_register needs more (it flips the protection there).
+    void* map = mmap(nullptr, size, PROT_READ, MAP_PRIVATE | MAP_NORESERVE, fd, 0);
     close(fd);
     if (map == MAP_FAILED) return tb_fail(TB_EINVAL, "tb_lmdb_open: mmap(%s): %s", file.c_str(), strerror(errno));
     // readahead=False in the reference: records are read at random
@@ -198,6 +198,14 @@ extern "C" int tb_lmdb_open(const char* path, tb_lmdb** out) {
         return tb_fail(TB_EINVAL, "tb_lmdb_open: %s has no valid LMDB meta page (magic 0xBEEFC0DE, version 1)", file.c_str());
     }
     const Meta& m = (!m1.ok || (m0.ok && m0.txnid >= m1.txnid)) ? m0 : m1;
+    // Main-DB flags change the key order or the node format (MDB_REVERSEKEY 0x02, MDB_DUPSORT 0x04,
+    // MDB_INTEGERKEY 0x08, MDB_DUPFIXED 0x10, MDB_INTEGERDUP 0x20, MDB_REVERSEDUP 0x40): the descent below
+    // assumes plain memcmp order and single values, so such a database is refused instead of misread.
+    if (m.flags & 0x7e) {
+        munmap(map, size);
+        return tb_fail(TB_ENOTSUP, "tb_lmdb_open: %s: main database flags 0x%x (reverse / integer keys or duplicates) are not supported",
+                       file.c_str(), (unsigned)m.flags);
+    }
     tb_lmdb* db = new tb_lmdb;
     db->map = base; db->size = size; db->psize = m.psize; db->root = m.root; db->entries = m.entries;
     db->last_pg = m.last_pg; db->depth = m.depth; db->flags = m.flags;
@@ -416,9 +424,16 @@ extern "C" int tb_lmdb_cuda_register(tb_lmdb* db, void** device_base) {
     (void)cudaDeviceGetAttribute(&ro_supported, cudaDevAttrHostRegisterReadOnlySupported, dev);
     unsigned flags = cudaHostRegisterMapped | cudaHostRegisterPortable;
     if (ro_supported) flags |= cudaHostRegisterReadOnly;
+    // cudaHostRegister refuses file mappings without PROT_WRITE on this platform (cudaErrorInvalidValue even
+    // with cudaHostRegisterReadOnly), so the protection of the private mapping is widened here and only here.
+    // Nothing ever writes through it.  Cost to know about: registration page-locks the WHOLE file in host
+    // memory (and may copy pages into anonymous memory), so this is for databases that fit in RAM.
+    if (mprotect((void*)db->map, db->size, PROT_READ | PROT_WRITE) != 0)
+        return tb_fail(TB_ENOTSUP, "tb_lmdb_cuda_register: mprotect(%zu bytes, read+write): %s", db->size, strerror(errno));
     cudaError_t e = cudaHostRegister((void*)db->map, db->size, flags);
     if (e != cudaSuccess) {
         (void)cudaGetLastError();
+        mprotect((void*)db->map, db->size, PROT_READ);
         return tb_fail(TB_ENOTSUP, "tb_lmdb_cuda_register: cudaHostRegister(%zu bytes, flags 0x%x) failed: %s "
                        "(read-only registration supported: %d)", db->size, flags, cudaGetErrorString(e), ro_supported);
     }
@@ -427,11 +442,13 @@ extern "C" int tb_lmdb_cuda_register(tb_lmdb* db, void** device_base) {
     if (e != cudaSuccess) {
         (void)cudaGetLastError();
         cudaHostUnregister((void*)db->map);
+        mprotect((void*)db->map, db->size, PROT_READ);
         return tb_cuda_fail(e, "cudaHostGetDevicePointer");
     }
     for (auto& r : g_registered)
         if (!r.db) { r.db = db; r.device_base = dptr; *device_base = dptr; return TB_OK; }
     cudaHostUnregister((void*)db->map);
+    mprotect((void*)db->map, db->size, PROT_READ);
     return tb_fail(TB_ENOTSUP, "tb_lmdb_cuda_register: too many registered databases");
 }
 
@@ -440,6 +457,7 @@ extern "C" int tb_lmdb_cuda_unregister(tb_lmdb* db) {
     for (auto& r : g_registered)
         if (r.db == db) {
             cudaHostUnregister((void*)db->map);
+            mprotect((void*)db->map, db->size, PROT_READ);
             r.db = nullptr;
             r.device_base = nullptr;
         }

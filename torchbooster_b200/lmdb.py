@@ -51,7 +51,9 @@ class LMDBReader:
         self.length = None
 
     def open(self) -> None:
-        """Open the environment (per process; never carried across fork)."""
+        """Open the environment (per process; never carried across fork).  A handle this process already holds is
+        released first, so opening twice does not leak the previous map."""
+        self.close()
         handle = C.c_void_p()
         rc = N.lib().tb_lmdb_open(os.fsencode(str(self.path)), C.byref(handle))
         if rc != 0 or not handle:
@@ -171,9 +173,13 @@ class LMDBReader:
             return None
 
     def __len__(self) -> int:
+        # torchbooster/lmdb.py:85-90: a reader that is still closed opens and closes again so that no
+        # environment is carried across a later fork; a reader already open in this process stays open.
         if not self.length:
-            self.open()
-            self.close()
+            was_open = self.env is not None and getattr(self, "_pid", None) == os.getpid()
+            if not was_open:
+                self.open()
+                self.close()
         return self.length
 
     def __iter__(self) -> Iterator[bytes]:
