@@ -74,6 +74,7 @@ extern "C" {
 #define TB_FLAG_FORCE_STREAM  2  /* tests: take the streaming path even where the gather kernel is the better launch */
 #define TB_FLAG_NO_PDL        4  /* launch without programmatic stream serialization */
 #define TB_FLAG_TWO_PHASE    16  /* tests: the two-phase (shared-memory intermediate) resize kernel instead of the sliding-window one */
+#define TB_FLAG_SLIDE        32  /* tests: the sliding-window resize kernel where the ring (bulk-copy staged) kernel would run */
 #define TB_FLAG_SRC_PLANAR    8  /* tb_augment: the source is uint8 [B][C][H][W] (src_row_pitch = bytes per row of one plane) */
 
 typedef struct CUstream_st* tb_stream_t;   /* == cudaStream_t */

@@ -91,7 +91,7 @@ def test_c4_resize_512_to_256_normalise(B):
     batch = images((B, 512, 512, 3))
     want = TO.transform_batch(batch, resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1])
     dev = torch.from_numpy(batch).cuda()
-    for flags in (0, N.FLAG_TWO_PHASE, N.FLAG_FORCE_GENERIC):
+    for flags in (0, N.FLAG_SLIDE, N.FLAG_TWO_PHASE, N.FLAG_FORCE_GENERIC):
         bt = BatchTransform(TransformSpec(resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1]), device="cuda")
         bt.flags = flags
         got = bt(dev)

@@ -35,7 +35,7 @@ def test_golden_pillow_resize(golden):
         assert same(out, ref), f"case {i}"
 
 
-BOTH_KERNELS = (0, 16)      # sliding-window kernel (default), TB_FLAG_TWO_PHASE
+BOTH_KERNELS = (0, 16, 32)      # default (ring kernel where rows are 16-byte aligned, else sliding-window), TB_FLAG_TWO_PHASE, TB_FLAG_SLIDE
 
 CASES = [
     # B, H, W, C, resize, center_crop, dtype
@@ -132,7 +132,7 @@ def test_fuzz_resize_against_integer_oracle(seed):
             want.append(TO.index_map_sample(rs, lut.view(view).numpy(), top=int(top[b]), left=int(left[b]), out_h=th,
                                             out_w=tw, flip=bool(flip[b]), pad_y=pad, pad_x=pad, pad_mode="constant"))
         spec = TransformSpec(resize=(rs_h, rs_w), crop=(th, tw), padding=pad, flip_p=.5, mean=mean, std=std, dtype=dtype)
-        for flags in (0, 1, 16):
+        for flags in (0, 1, 16, 32):
             bt = BatchTransform(spec, device="cuda")
             bt.flags = flags
             got = bt(torch.from_numpy(batch).cuda(), params=(top, left, flip)).cpu().view(view).numpy()
@@ -264,3 +264,44 @@ def test_ragged_limits():
         BatchTransform(TransformSpec(crop=16), device="cuda").ragged(_ragged_images(rng, [(64, 64)]))
     one = BatchTransform(TransformSpec(resize=(20, 30)), device="cuda").ragged(_ragged_images(rng, [(64, 64), (40, 100)]))
     assert tuple(one.shape) == (2, 3, 20, 30)
+
+
+RING_CASES = [
+    # B, H, W (W * 3 a multiple of 16), resized (h, w), crop (h, w), padding, dtype   -- all reach the ring kernel
+    (3, 96, 128, (48, 64), (48, 64), 0, torch.float32),          # exact 2x: top byte plane only
+    (2, 100, 160, (77, 123), (60, 100), 3, torch.float32),       # odd sizes, crop with constant padding
+    (1, 64, 1024, (40, 600), (40, 600), 0, torch.bfloat16),      # three column tiles of 256, bf16
+    (5, 120, 96, (30, 24), (28, 24), 0, torch.float32),          # exactly 4x: eight taps
+    (2, 130, 112, (50, 40), (50, 33), 0, torch.float16),         # 2.6x / 2.8x: eight taps, narrow last tile
+    (4, 48, 64, (70, 100), (64, 96), 0, torch.float32),          # upscaling
+    (40, 32, 32, (24, 20), (24, 20), 0, torch.float32),          # many small images: chunks of a few rows
+    (1, 700, 48, (400, 30), (400, 30), 0, torch.float32),        # tall: several 64-row chunks per image
+]
+
+
+@pytest.mark.parametrize("B,H,W,rs,crop,pad,dtype", RING_CASES)
+def test_ring_kernel_vs_integer_oracle(B, H, W, rs, crop, pad, dtype):
+    """The bulk-copy staged (ring) resize kernel, every group count, against the integer restatement of Pillow."""
+    from oracle import resize_oracle as RO
+    from torchbooster_b200 import _native as N
+    rng = np.random.default_rng(B * 1000 + H + W)
+    batch = rng.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+    th, tw = crop
+    top = rng.integers(0, rs[0] + 2 * pad - th + 1, B).astype(np.int32)
+    left = rng.integers(0, rs[1] + 2 * pad - tw + 1, B).astype(np.int32)
+    flip = rng.integers(0, 2, B).astype(np.uint8)
+    mean, std = IMAGENET
+    x = torch.arange(256, dtype=torch.uint8).to(torch.float32).div(255)
+    lut = ((x[None, :] - torch.tensor(mean)[:, None]) / torch.tensor(std)[:, None]).to(dtype)
+    view = torch.int32 if dtype == torch.float32 else torch.int16
+    want = np.stack([TO.index_map_sample(RO.resize_u8(batch[b], rs[0], rs[1]), lut.view(view).numpy(), top=int(top[b]),
+                                         left=int(left[b]), out_h=th, out_w=tw, flip=bool(flip[b]), pad_y=pad, pad_x=pad,
+                                         pad_mode="constant") for b in range(B)])
+    spec = TransformSpec(resize=rs, crop=crop, padding=pad, flip_p=.5, mean=mean, std=std, dtype=dtype)
+    before = N.lib().tb_launch_count()
+    for flags in (0, 1 << 8, 2 << 8, 3 << 8, N.FLAG_NO_PDL, N.FLAG_SLIDE):
+        bt = BatchTransform(spec, device="cuda")
+        bt.flags = flags
+        got = bt(torch.from_numpy(batch).cuda(), params=(top, left, flip)).cpu().view(view).numpy()
+        assert np.array_equal(got, want), flags
+    assert N.lib().tb_launch_count() - before >= 6

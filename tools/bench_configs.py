@@ -360,6 +360,15 @@ def main():
         c4 = dict(resize=256, center_crop=256, mean=IMAGENET[0], std=IMAGENET[1])
         transform_case("c4_stt_b32", 32, 512, 512, c4, 1572864, 200, params=False)
         transform_case("c4_stt_b256", 256, 512, 512, c4, 1572864, 50, params=False)
+        for bsz in (1, 4, 8, 16, 64, 128, 512):
+            transform_case(f"c4_scan_b{bsz}", bsz, 512, 512, c4, 1572864, 200 if bsz < 100 else 50, params=False)
+            transform_case(f"c4_scan_b{bsz}_slide", bsz, 512, 512, c4, 1572864, 200 if bsz < 100 else 50, flags=32, params=False)
+        transform_case("c4_stt_b32_slide", 32, 512, 512, c4, 1572864, 200, flags=32, params=False)
+        transform_case("c4_stt_b256_slide", 256, 512, 512, c4, 1572864, 50, flags=32, params=False)
+        for ng in (1, 2, 3):
+            transform_case(f"c4_stt_b32_ng{ng}", 32, 512, 512, c4, 1572864, 200, flags=ng << 8, params=False)
+            transform_case(f"c4_stt_b256_ng{ng}", 256, 512, 512, c4, 1572864, 50, flags=ng << 8, params=False)
+        transform_case("c4_stt_b256_bf16", 256, 512, 512, dict(c4, dtype=torch.bfloat16), 786432 + 393216, 50, params=False)
         transform_case("c4_stt_b32_two_phase", 32, 512, 512, c4, 1572864, 200, flags=16, params=False)
         transform_case("c4_stt_b256_two_phase", 256, 512, 512, c4, 1572864, 50, flags=16, params=False)
         if a.quick:

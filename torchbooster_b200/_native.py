@@ -17,7 +17,7 @@ TB_OK, TB_EINVAL, TB_ENOTSUP, TB_ENOENT = 0, -22, -95, -2
 TB_F32, TB_BF16, TB_F16, TB_U8 = 0, 1, 2, 3
 PAD_MODES = {"none": 0, "constant": 1, "reflect": 2, "edge": 3, "symmetric": 4}
 LUT_TO_TENSOR, LUT_NORMALIZE, LUT_ONE_MINUS, LUT_NORMALIZE_ONE_MINUS = 0, 1, 2, 3
-FLAG_FORCE_GENERIC, FLAG_FORCE_STREAM, FLAG_NO_PDL, FLAG_SRC_PLANAR, FLAG_TWO_PHASE = 1, 2, 4, 8, 16
+FLAG_FORCE_GENERIC, FLAG_FORCE_STREAM, FLAG_NO_PDL, FLAG_SRC_PLANAR, FLAG_TWO_PHASE, FLAG_SLIDE = 1, 2, 4, 8, 16, 32
 
 _i32, _i64, _vp = C.c_int, C.c_int64, C.c_void_p
 

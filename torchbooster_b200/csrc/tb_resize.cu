@@ -10,6 +10,7 @@
 // horizontal pass for exactly the input rows / resized columns that tile needs into shared
 // memory, phase 2 runs the vertical pass out of shared memory, looks the byte up and stores.
 #include <math.h>
+#include <type_traits>
 #include <vector>
 
 #include "tb_common.cuh"
@@ -743,6 +744,508 @@ inline void slide_geometry(RsParams& p, int B, int sm_count, int flags, int64_t*
     *threads = ((TC + 31) / 32) * 32;
 }
 
+
+// ----------------------------------------------------------------------------------------------
+// ring variant of the sliding-window kernel (C == 3, float / 16-bit outputs, 16-byte aligned rows).
+//
+// Same arithmetic and the same per-thread register window as tb_resize_slide_kernel; what changes is
+// how the bytes arrive and how the work is cut:
+//   * the input rows of a strip are fetched ONCE per column tile by 1-D bulk async copies
+//     (cp.async.bulk, TMA engine, SASS UBLKCP) into a shared-memory ring of row slots, completion on
+//     mbarriers; the column threads read their 16-byte windows out of the ring (LDS) instead of every
+//     thread pulling its own overlapping window through L1.  A dedicated producer warp runs ahead of the
+//     consumers by the depth of the ring (full / empty mbarrier pairs per slot), so no thread ever sits
+//     out a DRAM round trip;
+//   * one persistent CTA per SM holds the lookup table LANE-REPLICATED (word = value, row of 32 lanes
+//     per byte value and channel, 96 KiB): lane l reads word l of its row, so the lookups never collide
+//     on a bank whatever the 32 byte values are (the plain [c][256] table cost 35 % extra wavefronts);
+//   * the flattened (column tile, image, output row) space is split EVENLY over the groups of the grid
+//     (a group = tc column threads), in chunks of at most kSlideMaxTR rows that never straddle an image:
+//     no wave quantisation (2048 strips over 592 resident CTAs ran 4 waves for 3.46 waves of work);
+//   * tap byte planes that are zero for a whole warp (horizontal) or output row (vertical) are skipped:
+//     an exact 2x / 4x reduction has taps k * 2^-3 / 2^-4, i.e. only the top byte plane, and its dot
+//     product is one DP4A instead of three.  Same integers either way.
+// ----------------------------------------------------------------------------------------------
+constexpr int kRingRG = 4;            // input rows per ring slot (one full / empty barrier pair per slot)
+constexpr int kRingMaxGroups = 3;
+constexpr uint32_t kRingTabBytes = 3u * 256u * 32u * 4u;
+
+struct RingGeom {
+    int ng;                 // groups per CTA
+    int tc;                 // column threads per group (multiple of 32)
+    int slots;              // ring slots per group
+    int seg_pitch;          // bytes per staged row (multiple of 16, >= longest segment + 16)
+    int tiles_x;
+    int max_rows;           // output rows per chunk
+    long long total_rows;   // tiles_x * B * out_h
+    uint32_t ring_off, bar_off, kyb_off, ytop_off, dyn_bytes;
+};
+
+__device__ __forceinline__ void tb_named_barrier(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+// Shared-memory loads by 32-bit window address (no generic-address arithmetic in the loop).  volatile keeps them
+// ordered against the mbarrier wait / arrive that guard the ring; ALU code moves freely around them.
+template <int OFF>
+__device__ __forceinline__ uint32_t tb_lds_at(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+    return v;
+}
+__device__ __forceinline__ uint4 tb_lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+template <typename T>
+__device__ __forceinline__ void tb_st_cs(T* p, uint32_t bits);
+template <>
+__device__ __forceinline__ void tb_st_cs<float>(float* p, uint32_t bits) {
+    asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(p), "r"(bits));       // no "memory": dst is never read back
+}
+template <>
+__device__ __forceinline__ void tb_st_cs<uint16_t>(uint16_t* p, uint32_t bits) {
+    asm volatile("st.global.cs.b16 [%0], %1;" ::"l"(p), "h"((uint16_t)bits));
+}
+
+// Dot product of G groups of four samples with their taps, in one of three tap encodings:
+//   MODE 0  taps scaled by 4 (24 bits, none equal to 2^22) and only their top byte plane non-zero (an exact 2x / 4x
+//           reduction): one DP4A per group; the rounded result is BYTE 1 of the accumulator;
+//   MODE 1  taps scaled by 4, three byte planes: the result is BYTE 3 of the accumulator (no final shift);
+//   MODE 2  plain 22-bit taps (a tap of exactly 1.0 = 2^22 does not fit 24 bits once scaled): the result is the value.
+// Scaled: sum(p * 4k) + 2^23 = 4 * (sum(p * k) + 2^21), so bits 24-31 are Pillow's (2^21 + sum) >> 22; the sum stays
+// below 2^32 because the taps sum to at most 2^22 + NT / 2.
+template <int G, int MODE>
+__device__ __forceinline__ uint32_t tb_dot_mode(const uint32_t* px, const uint32_t (*kb)[3]) {
+    if (MODE == 2) return tb_dot<G>(px, kb);
+    uint32_t a = 128u;
+#pragma unroll
+    for (int g = 0; g < G; ++g) a = __dp4a(px[g], kb[g][2], a);
+    if (MODE == 0) return a;
+    a <<= 8;
+#pragma unroll
+    for (int g = 0; g < G; ++g) a = __dp4a(px[g], kb[g][1], a);
+    a <<= 8;
+#pragma unroll
+    for (int g = 0; g < G; ++g) a = __dp4a(px[g], kb[g][0], a);
+    return a;
+}
+// newest sample into the top byte of a window word, the oldest drops out of byte 0
+template <int MODE>
+__device__ __forceinline__ uint32_t tb_push_mode(uint32_t win, uint32_t a) {
+    if (MODE == 0) return __byte_perm(win, a, 0x5321);
+    if (MODE == 1) return __byte_perm(win, a, 0x7321);
+    return (win >> 8) | (a << 24);
+}
+// 128 * result (the byte offset of a table row) from an accumulator
+template <int MODE>
+__device__ __forceinline__ uint32_t tb_row7_mode(uint32_t a) {
+    if (MODE == 0) return (a >> 1) & 0x7f80u;
+    if (MODE == 1) return (a >> 17) & 0x7f80u;
+    return a << 7;
+}
+// taps -> byte planes; scaled by 4 unless one of them is 2^22.  Returns 1 when the plain encoding was used.
+template <int G, int NT>
+__device__ __forceinline__ uint32_t tb_pack_taps_scaled(const int* k, uint32_t (*kb)[3]) {
+    bool unity = false;
+#pragma unroll
+    for (int j = 0; j < NT; ++j) unity = unity || k[j] >= (1 << kPrecisionBits);
+    int k4[NT];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) k4[j] = unity ? k[j] : k[j] << 2;
+    tb_pack_taps<G>(k4, kb);
+    return unity ? 1u : 0u;
+}
+
+// One chunk of a group's share of the flattened row space: output rows [y0, y0 + nr) of column tile tx of
+// image b, the input rows [first, last] they depend on and the byte segment [s0, s0 + seg_len) of every
+// such row that the tile's columns read.  Producer and consumers derive it independently from (F, F1).
+struct RingChunk {
+    int b, tx, y0, nr;
+    int oy, ox, flip;
+    int first, last;        // last < first: nothing to fetch (all rows / columns outside the resized image)
+    int s0, seg_len;
+};
+template <int NT>
+__device__ __forceinline__ bool tb_ring_next(const RsParams& p, const RingGeom& g, long long& F, long long F1, RingChunk& c) {
+    if (F >= F1) return false;
+    const long long unit = F / p.out_h;
+    c.y0 = (int)(F - unit * p.out_h);
+    c.b = (int)(unit / g.tiles_x);
+    c.tx = (int)(unit - (long long)c.b * g.tiles_x);
+    long long nr = p.out_h - c.y0;
+    if (nr > g.max_rows) nr = g.max_rows;
+    if (nr > F1 - F) nr = F1 - F;
+    c.nr = (int)nr;
+    F += nr;
+    c.oy = (p.top ? p.top[c.b] : 0) + p.off_y;
+    c.ox = (p.left ? p.left[c.b] : 0) + p.off_x;
+    c.flip = p.flip ? (p.flip[c.b] != 0) : 0;
+    c.first = 0; c.last = -1; c.s0 = 0; c.seg_len = 0;
+    const int ia = max(0, -(c.oy + c.y0)), ib = min(c.nr, p.rs_h - (c.oy + c.y0)) - 1;      // valid output rows of the chunk
+    const int x0 = c.tx * g.tc, nc = min(g.tc, p.out_w - x0);
+    int ra = c.ox + (c.flip ? p.out_w - x0 - nc : x0), rb = ra + nc - 1;                   // resized columns of the tile
+    ra = max(ra, 0); rb = min(rb, p.rs_w - 1);
+    if (ia <= ib && ra <= rb) {
+        c.first = p.by[2 * (c.oy + c.y0 + ia)];
+        c.last = p.by[2 * (c.oy + c.y0 + ib)] + NT - 1;
+        c.s0 = (p.bx[2 * ra] * 3) & ~15;
+        const int end = (p.bx[2 * rb] + p.bx[2 * rb + 1]) * 3;
+        c.seg_len = ((end + 15) & ~15) - c.s0;
+        if (c.seg_len + 16 > g.seg_pitch) asm volatile("trap;");      // the host's bound on a tile's segment is wrong
+    }
+    return true;
+}
+
+template <typename T, int NT>
+__global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring_kernel(RsParams p, RingGeom g) {
+    constexpr int C = 3;
+    constexpr int G = NT / 4;
+    constexpr int NQ = NT * C / 4;
+    constexpr int RG = kRingRG;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wpg = g.tc >> 5;
+    const int n_cons = g.ng * wpg;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + g.bar_off);        // [ng][slots][2]: full, empty
+
+    if (tid == 0) {
+        for (int i = 0; i < g.ng * g.slots; ++i) {
+            tb_mbar_init(&bars[2 * i], 1);                      // full: the producer's arrive.expect_tx
+            tb_mbar_init(&bars[2 * i + 1], (uint32_t)wpg);      // empty: one arrival per consumer warp of the group
+        }
+        tb_mbar_fence_init();
+    }
+    tb_launch_dependents();
+    tb_grid_dependency_wait();
+    {   // lane-replicated table: [c][e][lane] words
+        const T* __restrict__ glut = (const T*)p.lut;
+        uint4* t4 = reinterpret_cast<uint4*>(smem);
+        for (int i = tid; i < 3 * 256 * 8; i += blockDim.x) {
+            uint32_t v;
+            if (sizeof(T) == 4) v = __float_as_uint(((const float*)glut)[i >> 3]);
+            else v = ((const uint16_t*)glut)[i >> 3];
+            t4[i] = make_uint4(v, v, v, v);
+        }
+    }
+    __syncthreads();
+
+    const long long ngt = (long long)gridDim.x * g.ng;
+    if (warp >= n_cons) {
+        // ------------------------------------------------------------------ producer warps: one per group
+        // (one warp polling every ring topped out near 1.5 TB/s of reads: tools/micro/bulk_copy_rate.cu shows a
+        // single warp issuing four 1.5 KB copies per step saturates at ~4 TB/s even with nothing else to do)
+        const int gi = warp - n_cons;
+        if (gi >= g.ng) return;
+        const long long me = (long long)blockIdx.x * g.ng + gi;
+        long long F = me * g.total_rows / ngt;
+        const long long F1 = (me + 1) * g.total_rows / ngt;
+        int slot = 0;
+        uint32_t phase = 1;                       // a fresh barrier passes a wait on parity 1
+        RingChunk ch;
+        while (tb_ring_next<NT>(p, g, F, F1, ch)) {
+            const uint8_t* gsrc0 = p.src + (int64_t)ch.b * p.bs + ch.s0 + (int64_t)lane * p.pitch;
+            for (int r = ch.first; r <= ch.last; r += RG) {
+                uint64_t* full = &bars[2 * (gi * g.slots + slot)];
+                tb_mbar_wait(full + 1, phase);                            // every consumer warp has drained the slot
+                const int nrows = min(RG, ch.last - r + 1);
+                const int ncopy = max(0, min(nrows, p.H - r));            // rows past the source are never weighted: not fetched
+                if (lane == 0) tb_mbar_arrive_expect_tx(full, (uint32_t)(ncopy * ch.seg_len));
+                __syncwarp();
+                if (lane < ncopy) {
+                    uint8_t* sdst = smem + g.ring_off + (size_t)((gi * g.slots + slot) * RG + lane) * g.seg_pitch;
+                    tb_bulk_g2s(sdst, gsrc0 + (int64_t)r * p.pitch, (uint32_t)ch.seg_len, full);
+                }
+                if (++slot == g.slots) { slot = 0; phase ^= 1u; }
+            }
+        }
+        return;
+    }
+
+    // ---------------------------------------------------------------------- consumers
+    const int grp = warp / wpg;
+    const int gt = tid - grp * g.tc;                 // column thread within the group
+    const uint32_t s_base = tb_smem_addr(smem);
+    uint32_t (*s_kyb)[4] = reinterpret_cast<uint32_t (*)[4]>(smem + g.kyb_off) + grp * kSlideMaxTR * G;     // [row][G] x {k0, k1, k2, -}
+    int* s_ytop = reinterpret_cast<int*>(smem + g.ytop_off) + grp * kSlideMaxTR;
+    const uint32_t kyb_addr = s_base + g.kyb_off + (uint32_t)(grp * kSlideMaxTR * G * 16);
+    const uint32_t ytop_addr = s_base + g.ytop_off + (uint32_t)(grp * kSlideMaxTR * 4);
+    const uint32_t tab_addr = s_base + (uint32_t)lane * 4u;
+    const uint32_t ring_addr = s_base + g.ring_off + (uint32_t)(grp * g.slots * RG) * (uint32_t)g.seg_pitch;
+    const uint32_t slot_bytes = (uint32_t)(RG * g.seg_pitch);
+    const int64_t plane = (int64_t)p.out_h * p.out_w;
+    long long F, F1;
+    {
+        const long long me = (long long)blockIdx.x * g.ng + grp;
+        F = me * g.total_rows / ngt;
+        F1 = (me + 1) * g.total_rows / ngt;
+    }
+    int slot = 0;
+    uint32_t phase = 0;
+    RingChunk c;
+    while (tb_ring_next<NT>(p, g, F, F1, c)) {
+        tb_named_barrier(1 + grp, g.tc);             // every thread of the group is done with the previous chunk's tables
+        if (gt < c.nr) {
+            const int ry = c.oy + c.y0 + gt;
+            int top = -1;
+            if (ry >= 0 && ry < p.rs_h && c.last >= c.first) {
+                int k[NT];
+                const int xmin = p.by[2 * ry], n = p.by[2 * ry + 1];
+#pragma unroll
+                for (int j = 0; j < NT; ++j) k[j] = (j < p.ksy && j < n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+                uint32_t kb[G][3];
+                const uint32_t plain = tb_pack_taps_scaled<G, NT>(k, kb);
+#pragma unroll
+                for (int q = 0; q < G; ++q) { s_kyb[gt * G + q][0] = kb[q][0]; s_kyb[gt * G + q][1] = kb[q][1]; s_kyb[gt * G + q][2] = kb[q][2]; s_kyb[gt * G + q][3] = plain; }
+                top = xmin + NT - 1;
+            }
+            s_ytop[gt] = top;
+        }
+        const int x0 = c.tx * g.tc;
+        const int nc = min(g.tc, p.out_w - x0);
+        const bool active = gt < nc;
+        const int x = x0 + gt;
+        const int rx = c.ox + (c.flip ? p.out_w - 1 - x : x);
+        const bool colin = active && c.last >= c.first && rx >= 0 && rx < p.rs_w;
+        int kx[NT];
+#pragma unroll
+        for (int j = 0; j < NT; ++j) kx[j] = 0;
+        int woff = 0, sh1 = 0;
+        if (colin) {
+            const int xmin = p.bx[2 * rx], n = p.bx[2 * rx + 1];
+#pragma unroll
+            for (int j = 0; j < NT; ++j) kx[j] = (j < p.ksx && j < n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
+            const int off = xmin * 3 - c.s0;
+            sh1 = (off & 3) * 8;
+            woff = off & ~3;
+        }
+        // one tap encoding per warp: plain if any of its columns has a tap of exactly 1.0, else scaled (top plane
+        // only when that holds for the whole warp)
+        bool unity = false;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) unity = unity || kx[j] >= (1 << kPrecisionBits);
+        unity = __any_sync(0xffffffffu, unity);
+        uint32_t kbx[G][3];
+        {
+            int k4[NT];
+#pragma unroll
+            for (int j = 0; j < NT; ++j) k4[j] = unity ? kx[j] : kx[j] << 2;
+            tb_pack_taps<G>(k4, kbx);
+        }
+        bool lowzero = true;
+#pragma unroll
+        for (int q = 0; q < G; ++q) lowzero = lowzero && (kbx[q][0] | kbx[q][1]) == 0;
+        lowzero = __all_sync(0xffffffffu, lowzero);
+        const int hmode = unity ? 2 : (lowzero ? 0 : 1);
+        T* dbase[C];
+#pragma unroll
+        for (int ch = 0; ch < C; ++ch) dbase[ch] = (T*)p.dst + ((int64_t)c.b * C + ch) * plane + (int64_t)c.y0 * p.out_w + x;
+        uint32_t eo = 0;                             // element offset of output row yy from dbase
+        tb_named_barrier(1 + grp, g.tc);
+
+        uint32_t win[C][G];
+#pragma unroll
+        for (int ch = 0; ch < C; ++ch)
+#pragma unroll
+            for (int q = 0; q < G; ++q) win[ch][q] = 0;
+        int yy = 0;
+        const int nr = c.nr;
+        auto ytop = [&](int i) { return (int)tb_lds_at<0>(ytop_addr + 4u * (uint32_t)i); };
+        auto store_row = [&](const uint32_t (&row7)[C]) {
+            uint32_t v[C];
+            v[0] = tb_lds_at<0>(tab_addr + row7[0]);
+            v[1] = tb_lds_at<32768>(tab_addr + row7[1]);
+            v[2] = tb_lds_at<65536>(tab_addr + row7[2]);
+            if (active) {
+#pragma unroll
+                for (int ch = 0; ch < C; ++ch) tb_st_cs<T>(dbase[ch] + eo, v[ch]);
+            }
+            eo += (uint32_t)p.out_w;
+            ++yy;
+        };
+        auto emit_zero = [&]() {
+            const uint32_t row7[C] = {0u, 0u, 0u};
+            store_row(row7);
+        };
+        auto emit = [&]() {          // output row yy from the register window
+            uint32_t kb[G][3];
+            uint32_t low = 0, plain = 0;
+#pragma unroll
+            for (int q = 0; q < G; ++q) {
+                const uint4 v = tb_lds128(kyb_addr + (uint32_t)((yy * G + q) * 16));
+                kb[q][0] = v.x; kb[q][1] = v.y; kb[q][2] = v.z;
+                low |= v.x | v.y;
+                plain |= v.w;
+            }
+            uint32_t row7[C];
+            if (plain) {
+#pragma unroll
+                for (int ch = 0; ch < C; ++ch) row7[ch] = tb_row7_mode<2>(tb_dot_mode<G, 2>(win[ch], kb));
+            } else if (low == 0) {
+#pragma unroll
+                for (int ch = 0; ch < C; ++ch) row7[ch] = tb_row7_mode<0>(tb_dot_mode<G, 0>(win[ch], kb));
+            } else {
+#pragma unroll
+                for (int ch = 0; ch < C; ++ch) row7[ch] = tb_row7_mode<1>(tb_dot_mode<G, 1>(win[ch], kb));
+            }
+            store_row(row7);
+        };
+        while (yy < nr && ytop(yy) < 0) emit_zero();               // rows above the resized image (centre-crop padding)
+        if (yy < nr) {
+            int nv = nr;
+            while (ytop(nv - 1) < 0) --nv;
+            const int last = c.last;
+            int next_top = ytop(yy);
+            auto rows = [&](auto mode_c) {
+                constexpr int MODE = decltype(mode_c)::value;
+                // one ring slot: RG input rows.  FULL: all of them are rows of this chunk (no per-row test).
+                auto slot_rows = [&](int r0, auto full_c) {
+                    constexpr bool FULL = decltype(full_c)::value;
+                    uint64_t* full = &bars[2 * (grp * g.slots + slot)];
+                    tb_mbar_wait(full, phase);
+                    // every window word of the slot's RG rows first (rows past `last` hold stale bytes that are
+                    // computed on but never pushed), then RG * 3 independent dot products: the loads' latency and
+                    // the DP4A chains overlap instead of running row after row
+                    const uint32_t rowa = ring_addr + (uint32_t)slot * slot_bytes + (uint32_t)woff;
+                    uint32_t w[RG][NQ + 1];
+#pragma unroll
+                    for (int u = 0; u < RG; ++u) {
+                        const uint32_t ra = rowa + (uint32_t)(u * g.seg_pitch);
+                        w[u][0] = tb_lds_at<0>(ra);
+                        w[u][1] = tb_lds_at<4>(ra);
+                        w[u][2] = tb_lds_at<8>(ra);
+                        w[u][3] = tb_lds_at<12>(ra);
+                        if (NQ >= 6) { w[u][4] = tb_lds_at<16>(ra); w[u][5] = tb_lds_at<20>(ra); w[u][NQ] = tb_lds_at<24>(ra); }
+                    }
+                    uint32_t h[RG][C];
+#pragma unroll
+                    for (int u = 0; u < RG; ++u) {
+                        uint32_t q[NQ];
+#pragma unroll
+                        for (int i = 0; i < NQ; ++i) q[i] = __funnelshift_r(w[u][i], w[u][i + 1], sh1);
+                        uint32_t p0[G], p1[G], p2[G];
+#pragma unroll
+                        for (int t = 0; t < G; ++t) {
+                            p0[t] = __byte_perm(__byte_perm(q[3 * t], q[3 * t + 1], 0x0630), q[3 * t + 2], 0x5210);
+                            p1[t] = __byte_perm(__byte_perm(q[3 * t], q[3 * t + 1], 0x0741), q[3 * t + 2], 0x6210);
+                            p2[t] = __byte_perm(__byte_perm(q[3 * t], q[3 * t + 1], 0x0052), q[3 * t + 2], 0x7410);
+                        }
+                        h[u][0] = tb_dot_mode<G, MODE>(p0, kbx);
+                        h[u][1] = tb_dot_mode<G, MODE>(p1, kbx);
+                        h[u][2] = tb_dot_mode<G, MODE>(p2, kbx);
+                    }
+#pragma unroll
+                    for (int u = 0; u < RG; ++u) {
+                        const int r = r0 + u;
+                        if (FULL || r <= last) {
+#pragma unroll
+                            for (int ch = 0; ch < C; ++ch) {
+#pragma unroll
+                                for (int t = 0; t + 1 < G; ++t) win[ch][t] = __funnelshift_r(win[ch][t], win[ch][t + 1], 8);
+                                win[ch][G - 1] = tb_push_mode<MODE>(win[ch][G - 1], h[u][ch]);
+                            }
+                            while (next_top == r) {
+                                emit();
+                                next_top = yy < nv ? ytop(yy) : 0x7fffffff;
+                            }
+                        }
+                    }
+                    // The slot is drained by this warp (every loaded word has been consumed above): hand it back.
+                    // No proxy fence: the reads were performed before the arrive, the refill is ordered after it.
+                    __syncwarp();
+                    if (lane == 0) tb_mbar_arrive(full + 1);
+                    if (++slot == g.slots) { slot = 0; phase ^= 1u; }
+                };
+                int r0 = c.first;
+                for (; r0 + RG - 1 <= last; r0 += RG) slot_rows(r0, std::true_type{});
+                if (r0 <= last) slot_rows(r0, std::false_type{});
+            };
+            if (hmode == 0) rows(std::integral_constant<int, 0>{});
+            else if (hmode == 1) rows(std::integral_constant<int, 1>{});
+            else rows(std::integral_constant<int, 2>{});
+            while (yy < nr) emit_zero();
+        }
+    }
+}
+
+// Geometry of the ring kernel, or false when this launch does not qualify (the sliding-window kernel runs then).
+inline bool ring_geometry(const RsParams& p, int B, int nt, const TbDevice& dev, int flags, RingGeom* out, int* grid, int* threads) {
+    RingGeom g = {};
+    g.tc = p.out_w >= 256 ? 256 : ((p.out_w + 31) / 32) * 32;
+    g.tiles_x = (p.out_w + g.tc - 1) / g.tc;
+    // longest byte segment a column tile reads from one row: its resized columns span at most
+    // (tc - 1) * scale + NT + 2 source pixels; + the 16-byte alignment on both sides + one window of slack
+    const double scale = (double)p.W / (double)p.rs_w;
+    int64_t span = (int64_t)((g.tc - 1) * scale) + nt + 3;
+    if (span > p.W) span = p.W;
+    int64_t seg = ((span * 3 + 15 + 15) & ~(int64_t)15);
+    if (seg > (int64_t)p.W * 3) seg = (int64_t)p.W * 3;
+    g.seg_pitch = (int)(seg + 16);
+    const int G = nt / 4;
+    const int64_t avail = (int64_t)dev.max_smem_optin - 1024 - kRingTabBytes;
+    int ng = (flags >> 8) & 0xff;
+    auto fits = [&](int n, int slots) {
+        return (int64_t)n * ((int64_t)slots * kRingRG * g.seg_pitch + slots * 16 + kSlideMaxTR * G * 16 + kSlideMaxTR * 4) + 256 <= avail;
+    };
+    g.total_rows = (long long)g.tiles_x * B * p.out_h;
+    // three groups (24 consumer warps) once every group still owns a few dozen rows (measured on C4: batch 256 -> 90 us
+    // with three groups, 104 us with two; batch 32, 18 rows per group with three: two groups are faster)
+    if (ng == 0) ng = (fits(3, 4) && g.total_rows >= 3LL * dev.sm_count * 40) ? 3 : 2;
+    if (ng > kRingMaxGroups) ng = kRingMaxGroups;
+    int slots = 8;
+    while (slots > 3 && !fits(ng, slots)) --slots;
+    if (!fits(ng, slots)) {
+        ng = 1; slots = 8;
+        while (slots > 3 && !fits(ng, slots)) --slots;
+        if (!fits(ng, slots)) return false;
+    }
+    g.ng = ng; g.slots = slots;
+    g.total_rows = (long long)g.tiles_x * B * p.out_h;
+    g.max_rows = kSlideMaxTR < p.out_h ? kSlideMaxTR : p.out_h;
+    // every group should own a few dozen rows (the halo of a chunk is NT - 2 + 2 input rows)
+    long long ctas = (g.total_rows + 24LL * ng - 1) / (24LL * ng);
+    if (ctas > dev.sm_count) ctas = dev.sm_count;
+    if (ctas < 1) ctas = 1;
+    uint32_t off = kRingTabBytes;
+    g.ring_off = off; off += (uint32_t)(ng * slots * kRingRG * g.seg_pitch);
+    off = (off + 15u) & ~15u;
+    g.bar_off = off; off += (uint32_t)(ng * slots * 16);
+    g.kyb_off = off; off += (uint32_t)(ng * kSlideMaxTR * G * 16);
+    g.ytop_off = off; off += (uint32_t)(ng * kSlideMaxTR * 4);
+    g.dyn_bytes = off;
+    *out = g;
+    *grid = (int)ctas;
+    *threads = ng * (g.tc + 32);
+    return true;
+}
+
+template <typename T>
+int launch_ring(const RsParams& p, const RingGeom& g, int grid, int threads, int nt, bool pdl, cudaStream_t s) {
+    static int attr_set[64][2] = {};
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    auto kern = nt == 4 ? tb_resize_ring_kernel<T, 4> : tb_resize_ring_kernel<T, 8>;
+    if (dev >= 0 && dev < 64 && !__atomic_load_n(&attr_set[dev][nt == 8], __ATOMIC_ACQUIRE)) {
+        int max_optin = 0;
+        TB_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin));
+        __atomic_store_n(&attr_set[dev][nt == 8], 1, __ATOMIC_RELEASE);
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)threads);
+    cfg.dynamicSmemBytes = g.dyn_bytes;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    TB_CUDA(cudaLaunchKernelEx(&cfg, kern, p, g));
+    TB_LAUNCH_CHECK("tb_resize_ring_kernel");
+    return TB_OK;
+}
+
 template <typename T, int C>
 int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, bool fast, int nt, cudaStream_t s) {
     static bool attr_set[64] = {};
@@ -816,6 +1319,18 @@ extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(
     bool fast = !(flags & TB_FLAG_FORCE_GENERIC) && p.words_ok && rs_w != W && rs_h != H &&
                 (int64_t)W <= 4 * (int64_t)rs_w && (int64_t)H <= 4 * (int64_t)rs_h;
     const int nt = ((int64_t)W <= 2 * (int64_t)rs_w && (int64_t)H <= 2 * (int64_t)rs_h) ? 4 : 8;
+    // Ring kernel: rows staged once per column tile by bulk copies (16-byte aligned rows), persistent CTAs.
+    if (fast && !(flags & (TB_FLAG_TWO_PHASE | TB_FLAG_SLIDE)) && C == 3 && dst_dtype != TB_U8 && ((uintptr_t)src & 15) == 0 &&
+        (src_row_pitch & 15) == 0 && (src_batch_stride & 15) == 0 && (((int64_t)W * 3) & 15) == 0 && src_row_pitch < ((int64_t)1 << 31)) {
+        RingGeom g;
+        int grid = 0, threads = 0;
+        if (ring_geometry(p, B, nt, dev, flags, &g, &grid, &threads)) {
+            const bool pdl = !(flags & TB_FLAG_NO_PDL);
+            cudaStream_t s = (cudaStream_t)stream;
+            return dst_dtype == TB_F32 ? launch_ring<float>(p, g, grid, threads, nt, pdl, s)
+                                       : launch_ring<uint16_t>(p, g, grid, threads, nt, pdl, s);
+        }
+    }
     if (fast && !(flags & TB_FLAG_TWO_PHASE) && src_row_pitch < ((int64_t)1 << 32)) {
         int64_t blocks = 0;
         int threads = 0;
