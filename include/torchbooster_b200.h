@@ -320,6 +320,20 @@ TB_API int tb_metrics_update(const void* logits, int logits_dtype, int64_t N, in
 TB_API int tb_running_sum_update(const void* x, int dtype, int64_t n, double* state, tb_stream_t stream);
 
 /*
+ * int32 wire format of the packed metric state for the cross-rank all_reduce (the north star's
+ * metric reduction; the reference itself offers only gather / barrier, torchbooster/distributed.py:41-68, on the
+ * process group it creates at :174-179).  Half the bytes of the int64 state on the wire, same totals:
+ *   state : DEVICE int64 [4 + bins] = n, correct_1, correct_k, invalid_labels, confusion bins (tb_metrics_update)
+ *   wire  : DEVICE int32 [12 + bins] = every header value as three 21-bit limbs (summing over up to 1024 ranks carries
+ *           nothing from limb to limb, so unpack rebuilds the exact int64 totals), then the bins narrowed to int32.
+ * pack before the all_reduce(SUM) of `wire`, unpack after it (unpack OVERWRITES state with the totals).  Exact while
+ * every bin TOTAL stays below 2^31, i.e. while the ranks together have scored fewer than 2^31 rows since the last
+ * reset; the caller guards that (MetricState counts the rows it was fed).
+ */
+TB_API int tb_metric_state_pack_i32(const int64_t* state, int64_t bins, int32_t* wire, tb_stream_t stream);
+TB_API int tb_metric_state_unpack_i32(const int32_t* wire, int64_t bins, int64_t* state, tb_stream_t stream);
+
+/*
  * Read-only LMDB reader (host side; liblmdb 0.9 data format, memcmp key order, main DB only).
  * Replaces py-lmdb under torchbooster.lmdb.LMDBReader (torchbooster/lmdb.py:48-83:
  * lmdb.open(path, readonly=True, lock=False, readahead=False) + txn.get(key)).

@@ -176,3 +176,34 @@ def test_fuzz_rows_against_rank_rule(seed):
         assert res[f"correct_{k}"] == int(((rank < k) & valid).sum()), (seed, C, n, k, dtype)
         assert res["invalid_labels"] == int((~valid).sum())
         assert np.array_equal(res["confusion"].cpu().numpy(), MO.confusion(ref, labels, C)), (seed, C, n, dtype)
+
+
+def test_int32_wire_format_sums_exactly():
+    """The int32 transport of the exchange: three ranks' states packed, their wire buffers added as int32 (what the
+    all_reduce does), unpacked -- equal to the int64 sum, header values far beyond 32 bits included."""
+    import torch
+    from torchbooster_b200 import _native as N
+    C = 23
+    gen = torch.Generator().manual_seed(5)
+    states = []
+    for r in range(3):
+        st = M.MetricState(C, k=5, device="cuda")
+        st.buffer[4:] = torch.randint(0, 2 ** 31 // 3, (C * C,), generator=gen).cuda()
+        st.buffer[:4] = torch.tensor([2 ** 61 // 3 + r, 2 ** 40 + 12345 * r, 7 + r, 0]).cuda()
+        states.append(st)
+    want = sum(s.buffer.clone() for s in states)
+    wires = [s.pack_wire().clone() for s in states]
+    assert all(w.dtype == torch.int32 and w.numel() == 12 + C * C for w in wires)
+    total = wires[0] + wires[1] + wires[2]
+    assert int(total.min()) >= 0
+    states[0].wire().copy_(total)
+    states[0].unpack_wire()
+    assert torch.equal(states[0].buffer, want)
+    # rows counted on the host guard the exactness limit
+    st = M.MetricState(C, k=5, device="cuda")
+    st.update(torch.randn(10, C).cuda(), torch.zeros(10, dtype=torch.int64).cuda())
+    st.note_rows(5)
+    assert st.rows_fed == 15
+    st.reset()
+    assert st.rows_fed == 0
+    assert N.lib().tb_metric_state_pack_i32(None, 4, None, None) == N.TB_EINVAL

@@ -12,7 +12,7 @@ from oracle import metrics_oracle as MO
 pytestmark = pytest.mark.gpu
 
 
-def _rank_main(tmp, n_classes):
+def _rank_main(tmp, n_classes, transport="int64"):
     from torchbooster_b200 import distributed as D
     from torchbooster_b200.metrics import MetricState
     rank, world = D.get_rank(), D.get_world_size()
@@ -28,7 +28,7 @@ def _rank_main(tmp, n_classes):
         part = idx[s:s + 128]
         st.update(logits[part].to(dev), labels[part].to(dev))
     st.update_loss(torch.full((len(idx),), float(rank + 1), device=dev))
-    st.all_reduce()
+    st.all_reduce(transport=transport)
     D.synchronize()
     res = st.compute()
     torch.save({"idx": idx, "buffer": st.buffer.cpu(), "loss": st.loss.cpu(), "n": res["n"]},
@@ -36,11 +36,12 @@ def _rank_main(tmp, n_classes):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs at least 2 GPUs")
-def test_sharded_metrics_all_reduce_nccl(tmp_path):
+@pytest.mark.parametrize("transport", ["int64", "int32"])
+def test_sharded_metrics_all_reduce_nccl(tmp_path, transport):
     from torchbooster_b200 import distributed as D
     world = min(torch.cuda.device_count(), 8)
     C = 37
-    D.launch(_rank_main, world, dist_url="auto", args=(str(tmp_path), C))
+    D.launch(_rank_main, world, dist_url="auto", args=(str(tmp_path), C, transport))
     res = [torch.load(tmp_path / f"rank{r}.pt", weights_only=False) for r in range(world)]
     gen = torch.Generator().manual_seed(17)
     logits = torch.randn(1001, C, generator=gen)

@@ -50,6 +50,8 @@ SIGNATURES = {
     "tb_resize_crop_ragged_u8_to_nchw": (_i32, [_vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _i32, _vp]),
     "tb_metrics_update": (_i32, [_vp, _i32, _i64, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
     "tb_running_sum_update": (_i32, [_vp, _i32, _i64, _vp, _vp]),
+    "tb_metric_state_pack_i32": (_i32, [_vp, _i64, _vp, _vp]),
+    "tb_metric_state_unpack_i32": (_i32, [_vp, _i64, _vp, _vp]),
     "tb_lmdb_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),
     "tb_lmdb_close": (_i32, [_vp]),
     "tb_lmdb_entries": (_i64, [_vp]),

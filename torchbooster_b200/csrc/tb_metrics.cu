@@ -370,7 +370,61 @@ __global__ void __launch_bounds__(256) tb_running_sum_kernel(const void* __restr
     }
 }
 
+// ---- int32 wire format of the packed metric state (the cross-rank exchange) -------------------------------
+// state : int64 [4 + bins]  = n, correct_1, correct_k, invalid, cm...
+// wire  : int32 [12 + bins] = the four header values as three 21-bit limbs each (sums over up to 1024 ranks stay below
+//         2^31 and carry nothing from limb to limb, so the int64 totals are rebuilt exactly), then the bins as int32.
+constexpr int kWireHeader = 12;
+__global__ void __launch_bounds__(256) tb_state_pack_kernel(const long long* __restrict__ state, long long bins,
+                                                            int* __restrict__ wire) {
+    tb_grid_dependency_wait();
+    const long long i0 = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i0 < 4) {
+        const unsigned long long v = (unsigned long long)state[i0];
+        wire[3 * i0] = (int)(v & 0x1fffffu);
+        wire[3 * i0 + 1] = (int)((v >> 21) & 0x1fffffu);
+        wire[3 * i0 + 2] = (int)((v >> 42) & 0x1fffffu);
+    }
+    for (long long i = i0; i < bins; i += (long long)gridDim.x * 256) wire[kWireHeader + i] = (int)state[4 + i];
+}
+__global__ void __launch_bounds__(256) tb_state_unpack_kernel(const int* __restrict__ wire, long long bins,
+                                                              long long* __restrict__ state) {
+    tb_grid_dependency_wait();
+    const long long i0 = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i0 < 4)
+        state[i0] = (long long)wire[3 * i0] + ((long long)wire[3 * i0 + 1] << 21) + ((long long)wire[3 * i0 + 2] << 42);
+    for (long long i = i0; i < bins; i += (long long)gridDim.x * 256) state[4 + i] = (long long)wire[kWireHeader + i];
+}
+
 }  // namespace
+
+extern "C" int tb_metric_state_pack_i32(const int64_t* state, int64_t bins, int32_t* wire, tb_stream_t stream) {
+    TB_REQUIRE(bins >= 0, "tb_metric_state_pack_i32: negative bins");
+    TB_REQUIRE(state && wire, "tb_metric_state_pack_i32: NULL argument");
+    TbDevice dev;
+    int rc = tb_device(&dev);
+    if (rc) return rc;
+    int64_t blocks = (bins + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > (int64_t)dev.sm_count * 8) blocks = (int64_t)dev.sm_count * 8;
+    tb_state_pack_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const long long*)state, (long long)bins, wire);
+    TB_LAUNCH_CHECK("tb_state_pack_kernel");
+    return TB_OK;
+}
+
+extern "C" int tb_metric_state_unpack_i32(const int32_t* wire, int64_t bins, int64_t* state, tb_stream_t stream) {
+    TB_REQUIRE(bins >= 0, "tb_metric_state_unpack_i32: negative bins");
+    TB_REQUIRE(state && wire, "tb_metric_state_unpack_i32: NULL argument");
+    TbDevice dev;
+    int rc = tb_device(&dev);
+    if (rc) return rc;
+    int64_t blocks = (bins + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > (int64_t)dev.sm_count * 8) blocks = (int64_t)dev.sm_count * 8;
+    tb_state_unpack_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(wire, (long long)bins, (long long*)state);
+    TB_LAUNCH_CHECK("tb_state_unpack_kernel");
+    return TB_OK;
+}
 
 extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N, int C, int64_t row_stride,
                                  const int64_t* labels, int k, int64_t* counters, int64_t* confusion,

@@ -157,6 +157,8 @@ class MetricState:
         n = self.HEADER + (self.num_classes ** 2 if confusion else 0)
         self.buffer = torch.zeros(n, dtype=torch.int64, device=self.device)
         self.loss = torch.zeros(2, dtype=torch.float64, device=self.device)
+        self.rows_fed = 0          # host-side count of the rows scored since the last reset (bounds every bin)
+        self._wire = None          # int32 transport buffer of the exchange, allocated at its first use
 
     @property
     def counters(self) -> Tensor:
@@ -171,6 +173,12 @@ class MetricState:
     def reset(self) -> None:
         self.buffer.zero_()
         self.loss.zero_()
+        self.rows_fed = 0
+
+    def note_rows(self, rows: int) -> None:
+        """Tell the state about rows that were scored into ``buffer`` directly through the C ABI (``update`` counts
+        its own): the int32 transport of ``all_reduce`` checks this count against its exactness limit."""
+        self.rows_fed += int(rows)
 
     def update(self, logits: Tensor, labels: Tensor, dim: int = -1) -> None:
         """Accumulate one batch (enqueue only; no host sync)."""
@@ -181,6 +189,7 @@ class MetricState:
             raise ValueError(f"logits on {logits2.device}, state on {self.device}")
         cm = self.buffer[self.HEADER:] if self.with_confusion else None
         _launch_update(logits2, labels1, self.k, self.buffer, cm)
+        self.rows_fed += int(logits2.shape[0])
 
     def update_loss(self, loss: Tensor) -> None:
         """Add per-step (0-dim) or per-sample losses to the running sum (enqueue only)."""
@@ -194,10 +203,31 @@ class MetricState:
             N.check(N.lib().tb_running_sum_update(v.data_ptr(), N.dtype_code(v.dtype), v.numel(),
                                                   self.loss.data_ptr(), N.current_stream_ptr(self.device)))
 
-    def all_reduce(self, group=None) -> None:
-        """Sum the state over all ranks (``torchbooster_b200.distributed.all_reduce_metrics``)."""
+    def all_reduce(self, group=None, transport: str = "int64") -> None:
+        """Sum the state over all ranks (``torchbooster_b200.distributed.all_reduce_metrics``).  ``transport="int32"``
+        halves the bytes on the wire (same totals; needs fewer than 2**31 rows scored by all ranks together)."""
         from .distributed import all_reduce_metrics
-        all_reduce_metrics(self, group=group)
+        all_reduce_metrics(self, group=group, transport=transport)
+
+    def wire(self) -> Tensor:
+        """The int32 transport buffer ``[12 + bins]`` (see ``tb_metric_state_pack_i32``)."""
+        if self._wire is None:
+            self._wire = torch.empty(12 + self.buffer.numel() - self.HEADER, dtype=torch.int32, device=self.device)
+        return self._wire
+
+    def pack_wire(self) -> Tensor:
+        N.require_cuda(self.buffer, "MetricState")
+        w = self.wire()
+        with torch.cuda.device(self.device):
+            N.check(N.lib().tb_metric_state_pack_i32(self.buffer.data_ptr(), self.buffer.numel() - self.HEADER, w.data_ptr(),
+                                                     N.current_stream_ptr(self.device)))
+        return w
+
+    def unpack_wire(self) -> None:
+        w = self.wire()
+        with torch.cuda.device(self.device):
+            N.check(N.lib().tb_metric_state_unpack_i32(w.data_ptr(), self.buffer.numel() - self.HEADER, self.buffer.data_ptr(),
+                                                       N.current_stream_ptr(self.device)))
 
     def compute(self) -> dict:
         """Read the state back (one sync)."""
