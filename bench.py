@@ -66,6 +66,9 @@ CONFIGS = {
     "c4_b256": dict(kind="transform", B=256, H=512, W=512, alg_bytes=786432 + 786432, iters=50, kernel="tb_resize_ring_kernel",
                     spec=dict(resize=256, center_crop=256, mean=IMAGENET_MEAN, std=IMAGENET_STD), params=False,
                     desc="C4 at batch 256 (content + style batches of eight steps in one launch)"),
+    "c4_b1": dict(kind="transform", B=1, H=512, W=512, alg_bytes=786432 + 786432, iters=200, kernel="tb_resize_ring_kernel",
+                  spec=dict(resize=256, center_crop=256, mean=IMAGENET_MEAN, std=IMAGENET_STD), params=False, dev_only=True,
+                  desc="C4 at batch 1: the fixed cost of one launch (development)"),
     "c5": dict(kind="metrics", N=125_000, C=1000, dtype=torch.float32, alg_bytes=4008, iters=50, kernel="tb_metrics_kernel",
                desc="C5: one rank's share (125 000 x 1000 fp32 logits) of the 1 M rows: top-1 + top-5 + confusion in one pass"),
     "c5_bf16": dict(kind="metrics", N=125_000, C=1000, dtype=torch.bfloat16, alg_bytes=2008, iters=50, kernel="tb_metrics_kernel",
@@ -372,7 +375,7 @@ def run_configs(dev, rank, world, with_cpu, transport, only=None):
     from torchbooster_b200.transforms import BatchTransform, CropFlipParams, TransformSpec
     peak, peak_src = measured_peak()
     out, ms_list = {}, []
-    names = [n for n in CONFIGS if only is None or n in only]
+    names = [n for n in CONFIGS if (only is None and not CONFIGS[n].get("dev_only")) or (only is not None and n in only)]
     for name in names:
         cfg = CONFIGS[name]
         iters = cfg["iters"]
@@ -906,7 +909,13 @@ def main():
     ap.add_argument("--transport", default="int32", choices=["int32", "int64"],
                     help="wire format of the metric exchange (int32 is exact while every rank has scored < 2^31 / world rows)")
     ap.add_argument("--no-affinity", action="store_true", help="do not pin the rank to its GPU's local CPUs")
+    ap.add_argument("--configs-only", default="", help="development: time only these configurations (comma separated) and print them")
     args = ap.parse_args()
+    if args.configs_only:
+        torch.cuda.set_device(0)
+        res = run_configs(torch.device("cuda", 0), 0, 1, with_cpu=False, transport=args.transport, only=args.configs_only.split(","))
+        print(json.dumps(res), flush=True)
+        return
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, wl)

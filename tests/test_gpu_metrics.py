@@ -207,3 +207,25 @@ def test_int32_wire_format_sums_exactly():
     st.reset()
     assert st.rows_fed == 0
     assert N.lib().tb_metric_state_pack_i32(None, 4, None, None) == N.TB_EINVAL
+
+
+@pytest.mark.parametrize("C,n", [(10, 1_000_000), (110, 200_000), (111, 200_000), (2, 300_000), (64, 4096)])
+def test_confusion_bins_in_shared_memory_hot_bin_stress(C, n):
+    """Few classes: the bins live in shared memory per CTA (C * C * 4 <= 48 KB, i.e. C <= 110; C = 111 is the first size
+    on the global-atomic route).  A million samples over 100 bins, most of them on the diagonal, against bincount."""
+    gen = torch.Generator(device="cuda").manual_seed(C)
+    logits = torch.randn(n, C, device="cuda", generator=gen)
+    labels = torch.randint(0, C, (n,), device="cuda", generator=gen)
+    labels[::2] = logits[::2].argmax(-1)                       # half of the samples hit the diagonal
+    labels[5::97] = -1                                          # a few invalid labels are skipped
+    st = M.MetricState(C, k=min(3, C), device="cuda")
+    st.update(logits, labels)
+    st.update(logits[: n // 3], labels[: n // 3])               # accumulates across launches
+    res = st.compute()
+    L = torch.cat([logits, logits[: n // 3]]); Y = torch.cat([labels, labels[: n // 3]])
+    ok = Y >= 0
+    pred = L.argmax(-1)
+    want = torch.bincount(Y[ok] * C + pred[ok], minlength=C * C).view(C, C)
+    assert torch.equal(res["confusion"], want)
+    assert res["correct_1"] == int((pred[ok] == Y[ok]).sum()) and res["invalid_labels"] == int((~ok).sum())
+    assert res["n"] == n + n // 3

@@ -263,7 +263,12 @@ struct RowAcc {
 
 // ALIGNED: every row starts on a 16-byte boundary (base and row stride are multiples of 16
 // bytes), so the head / body / tail split is the same for all rows.
-template <int DT, bool ALIGNED>
+// SCM: the confusion bins are privatised per CTA in shared memory (uint32 [C * C], C * C * 4 <= kScmMaxBytes): a sample is
+// one shared-memory atomic, and each CTA adds its non-zero bins to the global matrix once at the end.  With few classes
+// (the reference's workloads have 10, examples/img_cls/resnet/resnet.yml) every sample of a global-atomic version
+// lands on one of C * C hot addresses.
+constexpr int kScmMaxBytes = 48 * 1024;
+template <int DT, bool ALIGNED, bool SCM>
 __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_kernel(const void* __restrict__ logits, int64_t N, int C,
                                                                 int64_t row_stride, const int64_t* __restrict__ labels,
                                                                 int k, unsigned long long* __restrict__ counters,
@@ -273,7 +278,11 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_kernel(const void* _
     constexpr int ES = 16 / VE;
     constexpr int UN = 32 / VE;      // 16-byte loads per lane per batch: 8 for fp32, 4 for 16-bit types
     __shared__ unsigned int s_cnt[3];
+    extern __shared__ unsigned int s_cm[];        // SCM only: C * C bins
     if (threadIdx.x < 3) s_cnt[threadIdx.x] = 0;
+    if (SCM) {
+        for (int i = threadIdx.x; i < C * C; i += kMxThreads) s_cm[i] = 0;
+    }
     __syncthreads();
     tb_launch_dependents();
     tb_grid_dependency_wait();      // first global access below (programmatic dependent launch)
@@ -334,7 +343,8 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_kernel(const void* _
         if (lane == 0) {
             c1 += (rank < 1) ? 1u : 0u;
             ck += (rank < k) ? 1u : 0u;
-            if (confusion) atomicAdd(&confusion[(int64_t)a.y * C + pred], 1ULL);
+            if (SCM) atomicAdd(&s_cm[a.y * C + pred], 1u);
+            else if (confusion) atomicAdd(&confusion[(int64_t)a.y * C + pred], 1ULL);
         }
     }
     if (lane == 0) {
@@ -343,6 +353,12 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_kernel(const void* _
         if (inv) atomicAdd(&s_cnt[2], inv);
     }
     __syncthreads();
+    if (SCM) {
+        for (int i = threadIdx.x; i < C * C; i += kMxThreads) {
+            const unsigned int v = s_cm[i];
+            if (v) atomicAdd(&confusion[i], (unsigned long long)v);
+        }
+    }
     if (threadIdx.x == 0) {
         if (blockIdx.x == 0) atomicAdd(&counters[0], (unsigned long long)N);
         if (s_cnt[0]) atomicAdd(&counters[1], (unsigned long long)s_cnt[0]);
@@ -455,22 +471,32 @@ extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N
     cfg.attrs = attr;
     cfg.numAttrs = 1;
 
-    const int64_t cap = (int64_t)dev.sm_count * 8;   // 8 x 256 threads = full occupancy
+    // few classes: bins in shared memory (see the kernel); more than 24 KB of them leaves room for 4 CTAs per SM
+    const size_t scm_bytes = (size_t)C * (size_t)C * 4;
+    const bool scm = confusion != nullptr && scm_bytes <= (size_t)kScmMaxBytes;
+    cfg.dynamicSmemBytes = scm ? scm_bytes : 0;
+    const int64_t cap = (int64_t)dev.sm_count * ((scm && scm_bytes > 24 * 1024) ? 4 : 8);   // 8 x 256 threads = full occupancy
     if (blocks > cap) blocks = cap;
     TB_REQUIRE(N / (blocks * kMxWarps) < ((int64_t)1 << 28), "tb_metrics_update: N too large for one launch");
     cfg.gridDim = dim3((unsigned)blocks);
     const bool aligned = ((uintptr_t)logits % 16) == 0 && ((row_stride * es) % 16) == 0;
-#define TB_MX_LAUNCH(DT)                                                                                              \
-    do {                                                                                                              \
-        if (aligned)                                                                                                  \
-            TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<DT, true>, logits, N, C, row_stride, labels, k, cnt, cm));  \
-        else                                                                                                          \
-            TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<DT, false>, logits, N, C, row_stride, labels, k, cnt, cm)); \
+#define TB_MX_LAUNCH2(DT, AL)                                                                                          \
+    do {                                                                                                               \
+        if (scm)                                                                                                       \
+            TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<DT, AL, true>, logits, N, C, row_stride, labels, k, cnt, cm));  \
+        else                                                                                                           \
+            TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<DT, AL, false>, logits, N, C, row_stride, labels, k, cnt, cm)); \
+    } while (0)
+#define TB_MX_LAUNCH(DT)                \
+    do {                                \
+        if (aligned) TB_MX_LAUNCH2(DT, true);  \
+        else TB_MX_LAUNCH2(DT, false);         \
     } while (0)
     if (logits_dtype == TB_F32) TB_MX_LAUNCH(TB_F32);
     else if (logits_dtype == TB_BF16) TB_MX_LAUNCH(TB_BF16);
     else TB_MX_LAUNCH(TB_F16);
 #undef TB_MX_LAUNCH
+#undef TB_MX_LAUNCH2
     TB_LAUNCH_CHECK("tb_metrics_kernel");
     return TB_OK;
 }

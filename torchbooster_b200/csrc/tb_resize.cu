@@ -916,19 +916,23 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
         }
         tb_mbar_fence_init();
     }
+    __syncthreads();                // the barriers exist before anyone arrives on or waits for them
     tb_launch_dependents();
     tb_grid_dependency_wait();
-    {   // lane-replicated table: [c][e][lane] words
-        const T* __restrict__ glut = (const T*)p.lut;
+    if (warp < n_cons) {
+        // lane-replicated table: [c][e][lane] words, filled by the consumer warps while the producer warps already work
+        // out their first chunk and start its copies (they never touch the table)
+        const int nthr = n_cons * 32;
         uint4* t4 = reinterpret_cast<uint4*>(smem);
-        for (int i = tid; i < 3 * 256 * 8; i += blockDim.x) {
+#pragma unroll 4
+        for (int i = tid; i < 3 * 256 * 8; i += nthr) {
             uint32_t v;
-            if (sizeof(T) == 4) v = __float_as_uint(((const float*)glut)[i >> 3]);
-            else v = ((const uint16_t*)glut)[i >> 3];
+            if (sizeof(T) == 4) v = __float_as_uint(__ldg((const float*)p.lut + (i >> 3)));
+            else v = __ldg((const uint16_t*)p.lut + (i >> 3));
             t4[i] = make_uint4(v, v, v, v);
         }
+        tb_named_barrier(15, nthr);
     }
-    __syncthreads();
 
     const long long ngt = (long long)gridDim.x * g.ng;
     if (warp >= n_cons) {
