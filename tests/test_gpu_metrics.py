@@ -229,3 +229,40 @@ def test_confusion_bins_in_shared_memory_hot_bin_stress(C, n):
     assert torch.equal(res["confusion"], want)
     assert res["correct_1"] == int((pred[ok] == Y[ok]).sum()) and res["invalid_labels"] == int((~ok).sum())
     assert res["n"] == n + n // 3
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("C", [8, 64, 96, 1000, 1024])
+def test_one_batch_rows_ties_nan_inf(C, dtype):
+    """Rows the lean kernel takes (16-byte aligned, C a multiple of the vector width, C <= 1024) and the same values
+    through the general kernel (a view whose rows start 16 bytes + one element off): heavy ties, NaN, +-inf, +-0,
+    all-(-inf) rows, NaN label logits, labels at every position of a vector."""
+    gen = torch.Generator().manual_seed(C)
+    n = 257
+    base = torch.randint(-3, 4, (n, C), generator=gen).float() / 2
+    mask = torch.rand(n, C, generator=gen)
+    base[mask < 0.01] = float("nan")
+    base[(mask >= 0.01) & (mask < 0.02)] = float("inf")
+    base[(mask >= 0.02) & (mask < 0.05)] = float("-inf")
+    base[(mask >= 0.05) & (mask < 0.08)] = -0.0
+    base[3] = float("-inf")                       # whole row -inf: argmax is index 0
+    base[4] = 0.0; base[4, ::2] = -0.0            # zeros of both signs only
+    base[5] = float("nan")                        # whole row NaN
+    labels = torch.randint(0, C, (n,), generator=gen)
+    labels[:C if C < n else n] = torch.arange(C)[:n]            # the label at every position of the first vectors
+    labels[250:] = torch.tensor([-1, C, -5, C + 3, 0, C - 1, 1])
+    x = base.to(dtype)
+    ref = x.float()
+    rank = MO.label_rank(ref, labels)
+    valid = ((labels >= 0) & (labels < C)).numpy()
+    wide = torch.zeros(n, C + 24, dtype=dtype)
+    off = 8 // x.element_size() + 1                              # 8 bytes + one element: never 16-byte aligned
+    wide[:, off:off + C] = x
+    for logits in (x.cuda(), wide.cuda()[:, off:off + C]):
+        st = M.MetricState(C, k=3, device="cuda")
+        st.update(logits, labels.cuda())
+        res = st.compute()
+        assert res["correct_1"] == int(((rank < 1) & valid).sum())
+        assert res["correct_3"] == int(((rank < 3) & valid).sum())
+        assert res["invalid_labels"] == int((~valid).sum())
+        assert np.array_equal(res["confusion"].cpu().numpy(), MO.confusion(ref, labels, C))
