@@ -110,6 +110,12 @@ struct Packed<TB_BF16> {
         asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
         return r;
     }
+    __device__ static __forceinline__ uint32_t eq2(uint32_t a, uint32_t b) {    // 0xffff per half-word that compares equal (-0 == +0)
+        uint32_t r;
+        asm("set.eq.u32.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+        return r;
+    }
+    __device__ static __forceinline__ uint32_t bits(float m) { return __float_as_uint(m) >> 16; }      // exact: m came from a bf16
     __device__ static __forceinline__ float lo(uint32_t w) { return __uint_as_float(w << 16); }
     __device__ static __forceinline__ float hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 };
@@ -128,6 +134,12 @@ struct Packed<TB_F16> {
         asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
         return r;
     }
+    __device__ static __forceinline__ uint32_t eq2(uint32_t a, uint32_t b) {
+        uint32_t r;
+        asm("set.eq.u32.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+        return r;
+    }
+    __device__ static __forceinline__ uint32_t bits(float m) { return (uint32_t)__half_as_ushort(__float2half_rn(m)); }   // exact
     __device__ static __forceinline__ float lo(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)w)); }
     __device__ static __forceinline__ float hi(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w >> 16))); }
 };
@@ -390,6 +402,14 @@ __device__ __forceinline__ uint4 tb_ldcs_or(const uint4* p, bool take, uint32_t 
     return v;
 }
 
+// volatile: the row's loads stay together at the top of the iteration, all in flight before the first use (left to the
+// scheduler they sink towards their uses and a row costs several DRAM round trips instead of one)
+__device__ __forceinline__ uint4 tb_ldcs_now(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.cs.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
 template <int DT, bool SCM>
 __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_row_kernel(const void* __restrict__ logits, int64_t N, int C,
                                                                     int64_t row_stride, const int64_t* __restrict__ labels,
@@ -415,22 +435,29 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_row_kernel(const voi
     const int64_t nwarps = (int64_t)gridDim.x * kMxWarps;
     const int nv = C / VE;
     unsigned int c1 = 0, ck = 0, inv = 0;
-    bool take[UN];
+    bool take[UN], whole[UN];       // this lane has vector i; every lane has vector i (no -inf fill needed)
 #pragma unroll
-    for (int i = 0; i < UN; ++i) take[i] = lane + 32 * i < nv;
+    for (int i = 0; i < UN; ++i) { take[i] = lane + 32 * i < nv; whole[i] = 32 * (i + 1) <= nv; }
 
     long long y64 = warp0 < N ? labels[warp0] : -1;
-    for (int64_t n = warp0; n < N; n += nwarps) {
+    const typename E::type* row = (const typename E::type*)logits + warp0 * row_stride;
+    const int64_t row_step = nwarps * row_stride;
+    for (int64_t n = warp0; n < N; n += nwarps, row += row_step) {
         const long long ycur = y64;
         if (n + nwarps < N) y64 = labels[n + nwarps];
         if (ycur < 0 || ycur >= C) { inv += 1; continue; }
         const int y = (int)ycur;
-        const typename E::type* row = (const typename E::type*)logits + n * row_stride;
         const uint4* vp = reinterpret_cast<const uint4*>(row) + lane;
         uint4 r[UN];
 #pragma unroll
-        for (int i = 0; i < UN; ++i) r[i] = tb_ldcs_or(vp + 32 * i, take[i], kFill);
+        for (int i = 0; i < UN; ++i) {
+            if (whole[i]) r[i] = tb_ldcs_now(vp + 32 * i);
+            else r[i] = tb_ldcs_or(vp + 32 * i, take[i], kFill);
+        }
         const typename E::type raw_y = row[y];
+        // the elements that share the label's 16-byte vector and lie before it, one per lane (ties among them count)
+        const int d0 = y & (VE - 1);
+        const typename E::type raw_t = row[y - d0 + min(lane, VE - 1)];
         const float ly = E::to_float(raw_y);
         if (ly != ly) {
             // rare: the label's own logit is NaN -- the key route of the general kernel, element by element
@@ -449,8 +476,10 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_row_kernel(const voi
             continue;
         }
 
-        // ---- thresholds: x > hi  <=>  x outranks the label from behind it; x > lo  <=>  x >= l_y (from before it)
-        int cnt = 0;
+        // ---- thresholds: x > hi  <=>  x outranks the label from behind it; x > lo  <=>  x >= l_y (from before it).
+        // A vector wholly before the label is counted against lo, every other one against hi; the ties before the label
+        // inside its own vector are the (lane < d0) term.
+        int cnt = (lane < d0 && E::to_float(raw_t) == ly) ? P::kScale : 0;
         float m[UN];
         const int dl = y - lane * VE;                       // label position relative to this lane's first vector
         if constexpr (P::kOn) {
@@ -463,7 +492,7 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_row_kernel(const voi
             const uint32_t hi2 = c * 0x10001u, lo2 = l * 0x10001u;
 #pragma unroll
             for (int i = 0; i < UN; ++i) {
-                const int d = dl - 32 * i * VE;                        // > 0: the label lies after this vector's first element
+                const int d = dl - 32 * i * VE;                        // >= VE: the whole vector lies before the label
                 const uint32_t thr = d >= VE ? lo2 : hi2;
                 const uint32_t t = tb_bitsel(tb_bitsel(P::gtu2(r[i].x, thr), P::gtu2(r[i].y, thr), 0x000f000fu),
                                              tb_bitsel(P::gtu2(r[i].z, thr), P::gtu2(r[i].w, thr), 0x0f000f00u), 0x00ff00ffu);
@@ -490,20 +519,6 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_row_kernel(const voi
                 m[i] = tb_max_nan(tb_max3_nan(f0, f1, f2), f3);
             }
         }
-        // the vector that straddles the label (one lane, one vector): ties among its elements BEFORE the label
-        {
-            const int i = dl >= 0 ? dl / (32 * VE) : UN;
-            const int d = dl - i * 32 * VE;
-            if (i < UN && d > 0 && d < VE) {
-                float f[VE];
-                uint4 rv = r[0];
-#pragma unroll
-                for (int q = 1; q < UN; ++q) rv = i == q ? r[q] : rv;
-                E::unpack(rv, f);
-#pragma unroll
-                for (int e = 0; e < VE - 1; ++e) cnt += (e < d && f[e] == ly) ? P::kScale : 0;
-            }
-        }
         // ---- argmax: warp maximum of the keys, then the first index among the lanes that hold it
         float M = m[0];
 #pragma unroll
@@ -512,21 +527,53 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_row_kernel(const voi
         const int mx = __reduce_max_sync(0xffffffffu, key);
         int cand = INT_MAX;
         if (key == mx) {
-            const bool nanmax = M != M;
-            int pick = 0;
+            if (M != M) {
+                // a NaN is the maximum (rare): first NaN of this lane
+                int pick = 0;
 #pragma unroll
-            for (int i = UN - 1; i >= 0; --i)
-                if (nanmax ? (m[i] != m[i]) : (m[i] >= M)) pick = i;
-            uint4 rv = r[0];
+                for (int i = UN - 1; i >= 0; --i)
+                    if (m[i] != m[i]) pick = i;
+                if (lane + 32 * pick < nv) {
+                    const uint4 rv = __ldg(vp + 32 * pick);
+                    float f[VE];
+                    E::unpack(rv, f);
+                    int e0 = 0;
 #pragma unroll
-            for (int q = 1; q < UN; ++q) rv = pick == q ? r[q] : rv;
-            float f[VE];
-            E::unpack(rv, f);
-            int e0 = 0;
+                    for (int e = VE - 1; e >= 0; --e)
+                        if (f[e] != f[e]) e0 = e;
+                    cand = (lane + 32 * pick) * VE + e0;
+                }
+            } else {
+                int pick = 0;
 #pragma unroll
-            for (int e = VE - 1; e >= 0; --e)
-                if (nanmax ? (f[e] != f[e]) : (f[e] >= M)) e0 = e;
-            cand = (lane + 32 * pick) * VE + e0;
+                for (int i = UN - 1; i >= 0; --i)
+                    if (m[i] >= M) pick = i;
+                // The winning vector is read again (one 16-byte load by one lane, an L2 hit) instead of being kept:
+                // holding all UN vectors for this moment cost the fp32 kernel its registers -- the compiler reused load
+                // registers and a row took three DRAM round trips instead of one.
+                if (lane + 32 * pick < nv) {
+                const uint4 rv = __ldg(vp + 32 * pick);
+                int e0;
+                if constexpr (P::kOn) {
+                    // packed equality against the maximum; nibble w of the low / high half <- word w's low / high element
+                    const uint32_t mp = P::bits(M) * 0x10001u;
+                    const uint32_t t = tb_bitsel(tb_bitsel(P::eq2(rv.x, mp), P::eq2(rv.y, mp), 0x000f000fu),
+                                                 tb_bitsel(P::eq2(rv.z, mp), P::eq2(rv.w, mp), 0x0f000f00u), 0x00ff00ffu);
+                    const uint32_t tl = t & 0xffffu, th = t >> 16;
+                    const int el = tl ? ((__ffs(tl) - 1) >> 2) * 2 : 99;
+                    const int eh = th ? ((__ffs(th) - 1) >> 2) * 2 + 1 : 99;
+                    e0 = min(el, eh);
+                } else {
+                    float f[VE];
+                    E::unpack(rv, f);
+                    e0 = 0;
+#pragma unroll
+                    for (int e = VE - 1; e >= 0; --e)
+                        if (f[e] >= M) e0 = e;
+                }
+                cand = (lane + 32 * pick) * VE + e0;
+                }
+            }
         }
         const int pred = __reduce_min_sync(0xffffffffu, cand);
         const int rank = __reduce_add_sync(0xffffffffu, cnt) / P::kScale;
