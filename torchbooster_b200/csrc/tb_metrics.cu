@@ -649,21 +649,6 @@ __global__ void __launch_bounds__(256) tb_state_unpack_kernel(const int* __restr
     for (long long i = i0; i < bins; i += (long long)gridDim.x * 256) state[4 + i] = (long long)wire[kWireHeader + i];
 }
 
-// The scoring kernels read with streaming loads and want no L1: they ask for the largest shared-memory carve-out, the
-// one the transform / resize kernels run with.  An SM holds CTAs of two kernels at the same time only under ONE carve-out;
-// with the default (L1-heavy) preference a scoring launch sat out every transform kernel that was running (measured:
-// 20 scoring launches of 4 us each finished after 0.83 ms, one per transform kernel boundary).
-template <typename K>
-int tb_prefer_shared(K kernel) {
-    static int done[64] = {};
-    int dev = 0;
-    TB_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || __atomic_load_n(&done[dev], __ATOMIC_ACQUIRE)) return TB_OK;
-    TB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-    __atomic_store_n(&done[dev], 1, __ATOMIC_RELEASE);
-    return TB_OK;
-}
-
 }  // namespace
 
 extern "C" int tb_metric_state_pack_i32(const int64_t* state, int64_t bins, int32_t* wire, tb_stream_t stream) {
@@ -735,10 +720,8 @@ extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N
 #define TB_MX_LAUNCH2(DT, AL)                                                                                          \
     do {                                                                                                               \
         if (scm) {                                                                                                     \
-            if ((rc = tb_prefer_shared(tb_metrics_kernel<DT, AL, true>))) return rc;                                       \
             TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<DT, AL, true>, logits, N, C, row_stride, labels, k, cnt, cm));  \
         } else {                                                                                                       \
-            if ((rc = tb_prefer_shared(tb_metrics_kernel<DT, AL, false>))) return rc;                                      \
             TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_kernel<DT, AL, false>, logits, N, C, row_stride, labels, k, cnt, cm)); \
         }                                                                                                              \
     } while (0)
@@ -754,10 +737,8 @@ extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N
 #define TB_MX_ROW(DT)                                                                                                         \
     do {                                                                                                                      \
         if (scm) {                                                                                                            \
-            if ((rc = tb_prefer_shared(tb_metrics_row_kernel<DT, true>))) return rc;                                              \
             TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_row_kernel<DT, true>, logits, N, C, row_stride, labels, k, cnt, cm));     \
         } else {                                                                                                              \
-            if ((rc = tb_prefer_shared(tb_metrics_row_kernel<DT, false>))) return rc;                                             \
             TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_row_kernel<DT, false>, logits, N, C, row_stride, labels, k, cnt, cm));    \
         }                                                                                                                     \
     } while (0)
