@@ -11,7 +11,11 @@
  *   - never throws, never synchronises the device, only enqueues on `stream`
  *     (a cudaStream_t; NULL = legacy default stream);
  *   - the caller owns every buffer and keeps it alive until the enqueued work has completed;
- *   - works on the current CUDA device of the calling thread; no library-global mutable state;
+ *   - works on the current CUDA device of the calling thread.  What the library keeps between calls, all of it
+ *     thread-safe and none of it visible in results: a launch counter (tb_launch_count), per-device caches of
+ *     device attributes and of "kernel attribute already set" flags (atomics; racing first calls write the same
+ *     values), the table of LMDB maps registered with CUDA (mutex), and the fixed device array of
+ *     tb_to_image_stretch_u8_static (shared by every call on a device: see there);
  *   - accumulating outputs (counters, confusion, running sums) are ADDED TO: the caller zeroes them.
  */
 #ifndef TORCHBOOSTER_B200_H

@@ -337,7 +337,7 @@ def main():
     c2 = dict(crop=224, flip_p=.5, mean=IMAGENET[0], std=IMAGENET[1], dtype=torch.bfloat16)
     if want("c2"):
         knob = lambda warps=0, rows=0, extra=0: extra | (warps << 16) | (rows << 24)
-        cases = [("c2_default", 0), ("c2_no_pdl", N.FLAG_NO_PDL), ("c2_w11_r8", knob(11, 8)), ("c2_w22_r4", knob(22, 4)),
+        cases = [("c2_default", 0),  ("c2_no_pdl", N.FLAG_NO_PDL), ("c2_w11_r8", knob(11, 8)), ("c2_w22_r4", knob(22, 4)),
                  ("c2_w10_r8", knob(10, 8)), ("c2_w8_r12", knob(8, 12)), ("c2_w14_r6", knob(14, 6)), ("c2_generic", 1)]
         if a.quick:
             cases = cases[:3]

@@ -62,7 +62,7 @@ def summarize_launches(csv_path, out):
         name, ns = r[4], float(r[-1])
         per.setdefault(name, []).append(ns)
         total += ns
-    lines = ["# ncu --metrics gpu__time_duration.sum --clock-control none  (python bench.py --steps 40 --warmup 3 --no-cpu --no-e2e)",
+    lines = ["# ncu --metrics gpu__time_duration.sum --clock-control none  (python bench.py --steps 20 --warmup 5 --no-cpu --no-e2e --no-configs)",
              "# per-launch times under ncu are cold-cache and serialised: compare SHARES, not absolutes", "",
              f"{'kernel':90s} {'launches':>8s} {'mean_us':>9s} {'total_us':>10s} {'share':>7s}"]
     for name, v in sorted(per.items(), key=lambda kv: -sum(kv[1])):
@@ -70,52 +70,78 @@ def summarize_launches(csv_path, out):
     out.write_text("\n".join(lines) + "\n")
 
 
+SASS_OPS = ["UBLKCP", "UTMALDG", "UTMASTG", "SYNCS", "IDP", "REDUX", "HSET2", "HMNMX2", "VHMNMX", "FMNMX3", "LDGSTS", "UTCHMMA", "HMMA", "LDTM"]
+
+
+def sass_census(out):
+    """Opcode census of the built library: which Blackwell paths the kernels really use (cuobjdump -sass)."""
+    lib = ROOT / "torchbooster_b200" / "lib" / "libtorchbooster_b200.so"
+    txt = subprocess.run(["cuobjdump", "-sass", str(lib)], capture_output=True, text=True).stdout
+    per, cur = OrderedDict(), None
+    for line in txt.splitlines():
+        line = line.strip()
+        if line.startswith("Function :"):
+            cur = line.split(":", 1)[1].strip()
+            per[cur] = OrderedDict((op, 0) for op in SASS_OPS)
+        elif cur and line.startswith("/*") and "*/" in line:
+            body = line.split("*/", 1)[1].strip()
+            toks = body.split()
+            if not toks:
+                continue
+            op = toks[1] if toks[0].startswith("@") and len(toks) > 1 else toks[0]
+            base = op.split(".")[0]
+            if base in per[cur]:
+                per[cur][base] += 1
+    lines = ["# SASS opcode census of torchbooster_b200/lib/libtorchbooster_b200.so (cuobjdump -sass, sm_100a)",
+             "# UBLKCP = cp.async.bulk (1-D bulk copy, TMA engine); UTMALDG / UTMASTG = cp.async.bulk.tensor; SYNCS = mbarrier;",
+             "# IDP = DP4A; REDUX = redux.sync; HSET2 / HMNMX2 / VHMNMX = packed 16-bit compare / max; no tensor-core opcode is",
+             "# expected (nothing on this path is a contraction).", "",
+             f"{'function':100s} " + " ".join(f"{op:>7s}" for op in SASS_OPS)]
+    tot = OrderedDict((op, 0) for op in SASS_OPS)
+    for fn, c in per.items():
+        if any(c.values()):
+            lines.append(f"{fn[:100]:100s} " + " ".join(f"{c[op]:7d}" for op in SASS_OPS))
+        for op in SASS_OPS:
+            tot[op] += c[op]
+    lines.append(f"{'TOTAL over ' + str(len(per)) + ' functions':100s} " + " ".join(f"{tot[op]:7d}" for op in SASS_OPS))
+    out.write_text("\n".join(lines) + "\n")
+
+
+CAPTURES = [
+    # report stem, output name, title, traffic key
+    ("prof_c1", "ncu_c1_crop_generic", "C1: tb_xf_generic_kernel, 256 x 32x32 reflect-pad crop / flip -> fp32", "c1"),
+    ("prof_c2", "ncu_c2_transform", "C2: tb_xf_stream_kernel, 512 x 256x256 -> crop 224, flip, bf16 (one stream, back to back)", "c2"),
+    ("prof_c3", "ncu_c3_transform", "C3: tb_xf_stream_kernel, 1024 x 64x64 flip -> fp32", "c3"),
+    ("prof_c4", "ncu_c4_resize_b32", "C4: tb_resize_ring_kernel, 32 x 512x512 -> 256x256 fp32", "c4"),
+    ("prof_c4_b256", "ncu_c4_resize_b256", "C4 at batch 256: tb_resize_ring_kernel", "c4_b256"),
+    ("prof_c5", "ncu_c5_metrics_f32", "C5: tb_metrics_row_kernel, 125 000 x 1000 fp32", "c5"),
+    ("prof_c5_bf16", "ncu_c5_metrics_bf16", "C5 bf16: tb_metrics_row_kernel, 125 000 x 1000 bf16", "c5_bf16"),
+    ("prof_rrc", "ncu_resized_crop", "resized-crop kernel, 512 x (256x256 box -> 224x224, bf16)", "rrc_c2_b512"),
+    ("prof_aug", "ncu_augment", "augment kernel, CIFAR training transform, batch 2048", "aug_cifar_b2048"),
+]
+
+
 def main():
-    tag = sys.argv[1] if len(sys.argv) > 1 else "r1"
+    tag = sys.argv[1] if len(sys.argv) > 1 else "r2"
     src = ROOT / "gpurun_out"
     OUT.mkdir(exist_ok=True)
     traffic = {}
     if (src / "launches.csv").exists():
         summarize_launches(src / "launches.csv", OUT / f"{tag}_launches.txt")
-    if (src / "prof_xf.ncu-rep").exists():
-        t = summarize_report(src / "prof_xf.ncu-rep", OUT / f"{tag}_ncu_transform.txt", "transform kernel, C2 workload")
-        for name, v in t.items():
-            if "tb_xf_stream" in name:
-                traffic["c2"] = sum(v) / len(v)
-    if (src / "prof_mx.ncu-rep").exists():
-        t = summarize_report(src / "prof_mx.ncu-rep", OUT / f"{tag}_ncu_metrics.txt", "metrics kernel, C5 workload (125 000 x 1000 fp32)")
-        for name, v in t.items():
-            traffic["c5"] = sum(v) / len(v)
-    if (src / "prof_rs.ncu-rep").exists():
-        t = summarize_report(src / "prof_rs.ncu-rep", OUT / f"{tag}_ncu_resize.txt", "resize kernel, C4 workload (batch 256)")
-        for name, v in t.items():
-            traffic["c4_b256"] = sum(v) / len(v)
-    if (src / "prof_rrc.ncu-rep").exists():
-        t = summarize_report(src / "prof_rrc.ncu-rep", OUT / f"{tag}_ncu_resized_crop.txt",
-                             "resized-crop kernel, 512 x (256x256 box -> 224x224, bf16), per-sample boxes, taps computed in-kernel")
-        for name, v in t.items():
-            traffic["rrc_c2_b512"] = sum(v) / len(v)
-    if (src / "prof_aug.ncu-rep").exists():
-        t = summarize_report(src / "prof_aug.ncu-rep", OUT / f"{tag}_ncu_augment.txt",
-                             "augment kernel, CIFAR training transform (resnet.py:96-103), batch 2048")
-        for name, v in t.items():
-            traffic["aug_cifar_b2048"] = sum(v) / len(v)
+    for stem, name, title, key in CAPTURES:
+        rep = src / f"{stem}.ncu-rep"
+        if rep.exists():
+            t = summarize_report(rep, OUT / f"{tag}_{name}.txt", title)
+            for _, v in t.items():
+                traffic[key] = sum(v) / len(v)
     if traffic:
         old = json.loads((OUT / "traffic.json").read_text()) if (OUT / "traffic.json").exists() else {}
         old.update(traffic)
         (OUT / "traffic.json").write_text(json.dumps(old, indent=1) + "\n")
-    for f in ("bench_full.json", "bench_ref.json"):
-        if (src / f).exists():
+    for f in ("bench_driver.json", "bench_ref.json"):
+        if (src / f).exists() and (src / f).stat().st_size:
             (OUT / f"{tag}_{f}").write_text((src / f).read_text())
-    if (src / "configs.jsonl").exists():        # merge by case name: a partial run must not drop the other cases
-        dst = OUT / f"{tag}_configs.jsonl"
-        rows = OrderedDict()
-        for path in (dst, src / "configs.jsonl"):
-            if path.exists():
-                for line in path.read_text().splitlines():
-                    if line.strip():
-                        rows[json.loads(line)["case"]] = line
-        dst.write_text("\n".join(rows.values()) + "\n")
+    sass_census(OUT / f"{tag}_sass_census.txt")
 
 
 if __name__ == "__main__":

@@ -1252,13 +1252,13 @@ int launch_ring(const RsParams& p, const RingGeom& g, int grid, int threads, int
 
 template <typename T, int C>
 int launch_resize(const RsParams& p, size_t smem, int64_t blocks, int max_smem, bool fast, int nt, cudaStream_t s) {
-    static bool attr_set[64] = {};
+    static int attr_set[64] = {};            // per device, atomic: racing first calls set the same attribute
     int dev = 0;
     TB_CUDA(cudaGetDevice(&dev));
-    if (smem > 40 * 1024 && !attr_set[dev]) {
+    if (smem > 40 * 1024 && dev >= 0 && dev < 64 && !__atomic_load_n(&attr_set[dev], __ATOMIC_ACQUIRE)) {
         TB_CUDA(cudaFuncSetAttribute(tb_resize_fused_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      max_smem - 8192));
-        attr_set[dev] = true;
+        __atomic_store_n(&attr_set[dev], 1, __ATOMIC_RELEASE);
     }
     if (fast && smem <= 44 * 1024) {
         if (p.box) {

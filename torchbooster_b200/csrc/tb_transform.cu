@@ -413,11 +413,11 @@ int launch_stream(const XfParams& p, const TbDevice& dev, cudaStream_t s, int fo
     g.tile_db = (int)(stride / g.tiles_per_image);
     g.tile_dt = (int)(stride % g.tiles_per_image);
     g.dyn_bytes = kXfSmemEnd;
-    static bool attr_set[64] = {};
-    if (!attr_set[dev.device]) {
+    static int attr_set[64] = {};            // per device, atomic: racing first calls set the same attribute
+    if (!__atomic_load_n(&attr_set[dev.device], __ATOMIC_ACQUIRE)) {
         TB_CUDA(cudaFuncSetAttribute(tb_xf_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      dev.max_smem_optin));
-        attr_set[dev.device] = true;
+        __atomic_store_n(&attr_set[dev.device], 1, __ATOMIC_RELEASE);
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
