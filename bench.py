@@ -180,32 +180,42 @@ def cpu_path(name: str, B: int, H: int, W: int, steps: int, workers: int, max_se
     """Reference-style CPU path: per-sample torchvision PIL transforms in DataLoader workers
     (resnet.py:94-107 pattern), default collate to fp32 NCHW, then (score = (classes, k)) accuracy (the oracle's
     restatement of torchbooster/metrics.py:27) + torch.topk + torch.bincount on all host threads.
-    The untimed warm-up consumes workers * prefetch + workers batches: everything the workers had queued before the
-    main process started reading is gone by then, so the timed batches arrive at the steady-state rate (a 20-batch
-    window straight after start-up reads 2x high: the prefetched batches land in a burst).
+
+    Steady state by construction: the workers of a DataLoader run in lockstep (they all start together and every
+    batch costs the same), so whole batches of B arrive in bursts of `workers` and a window of K batches reads up to
+    2x high or low depending on where it falls.  Here every worker collates B / workers images at a time and a STEP
+    is one such piece from every worker (B images in all, concatenated): each step is exactly one burst, so K steps
+    take K burst periods whatever K is.  The untimed warm-up drains everything that was queued at start-up.
     Returns (images_per_second, steps_done, seconds)."""
     from oracle import metrics_oracle as MO
     rng = np.random.default_rng(1234)
     pool = rng.integers(0, 256, (min(2048, max(B * 2, 256)), H, W, 3), dtype=np.uint8)
-    warmup = workers * prefetch + workers if workers else 2
-    total = (steps + warmup) * B
+    piece = -(-B // workers) if workers else B                 # images a worker collates at a time
+    per_step = -(-B // piece)                                   # pieces per step
+    step_images = per_step * piece
+    warmup = (2 * prefetch + 1) if workers else 1               # steps (bursts) consumed before the clock starts
+    total = (steps + warmup) * step_images
     ds = _SyntheticImages(pool, _cpu_compose(name))
     sampler = torch.utils.data.RandomSampler(ds, replacement=True, num_samples=total)
-    loader = torch.utils.data.DataLoader(ds, batch_size=B, sampler=sampler, num_workers=workers, pin_memory=False,
+    loader = torch.utils.data.DataLoader(ds, batch_size=piece, sampler=sampler, num_workers=workers, pin_memory=False,
                                          drop_last=True, persistent_workers=False,
                                          prefetch_factor=prefetch if workers else None)
     if score:
         classes, k = score
         gen = torch.Generator().manual_seed(1234)
-        logits = torch.randn(B, classes, generator=gen)
+        logits = torch.randn(step_images, classes, generator=gen)
         cm = torch.zeros(classes ** 2, dtype=torch.int64)
     done, t0, n1, nk = 0, None, 0, 0
-    for i, (x, y) in enumerate(loader):
+    it = iter(loader)
+    for i in range(steps + warmup):
         if i == warmup:
             t0 = time.perf_counter()
+        parts = [next(it) for _ in range(per_step)]
+        x = torch.cat([p[0] for p in parts])
+        y = torch.cat([p[1] for p in parts])
         x = x.to(out_dtype) if out_dtype != torch.float32 else x
         if score:
-            n1 += int(MO.accuracy(logits, y) * B)
+            n1 += int(MO.accuracy(logits, y) * step_images)
             nk += int((logits.topk(k, -1).indices == y[:, None]).any(-1).sum())
             cm += torch.bincount(y * classes + logits.argmax(-1), minlength=classes ** 2)
         if i >= warmup:
@@ -213,8 +223,8 @@ def cpu_path(name: str, B: int, H: int, W: int, steps: int, workers: int, max_se
             if time.perf_counter() - t0 > max_seconds:
                 break
     dt = time.perf_counter() - t0
-    del loader
-    return done * B / dt, done, dt
+    del it, loader
+    return done * step_images / dt, done, dt
 
 
 def cpu_metrics_path(n: int, classes: int, dtype, k: int = 5, max_seconds: float = 4.0):
@@ -279,9 +289,10 @@ def run_reference(args, wl):
         "config": {"workload": wl["desc"],
                    "per_step": f"one batch of {B} images on the host CPU" +
                                ("" if B == full_b else f" (bounded sample of the {full_b}-image batch)"),
-                   "untimed_warmup_batches": workers * 3},
+                   "timing": "every DataLoader worker collates B / workers images at a time and a step is one such piece from every "
+                             "worker, so each timed step is one full burst of the lockstepped workers (steady state for any K)"},
         "cpu_baseline": {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
-                         "sample": f"{done} batches of {B} images after {workers * 3} untimed batches (steady state); torchvision "
+                         "sample": f"{done} steps of {B} images (one piece of {-(-B // workers)} from each worker) after 5 untimed steps; torchvision "
                                    f"{__import__('torchvision').__version__} PIL transforms in {workers} DataLoader workers + "
                                    f"accuracy/topk/bincount; {cpu_model()}"},
         "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -769,7 +780,7 @@ def run_ours(args, wl):
                                  out_dtype=wl["dtype"])
         import torchvision
         cpu = {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
-               "sample": f"{done} batches of {B} images in {dt:.1f} s after {workers * 3} untimed batches; torchvision "
+               "sample": f"{done} steps of {B} images in {dt:.1f} s (one piece of {-(-B // workers)} images from each worker per step); torchvision "
                          f"{torchvision.__version__} PIL transforms in {workers} DataLoader workers + accuracy/topk/bincount on the host; {cpu_model()}"}
 
     if rank == 0:
