@@ -812,26 +812,29 @@ def run_ours(args, wl):
         dist.destroy_process_group()
 
 
-def h2d_probe(dev, world, nbytes, iters=8):
-    """What this box can move host -> device: every rank copies `nbytes` of pinned memory to its GPU `iters` times at the
-    same moment (plain cudaMemcpyAsync through torch, the copy engine).  Returns aggregate GB/s over all ranks."""
+def h2d_probe(dev, world, host, nbytes, iters=10, repeats=3):
+    """What this box can move host -> device: every rank copies `nbytes` of (already pinned, already touched) host
+    memory to its GPU `iters` times at the same moment (plain cudaMemcpyAsync through torch, the copy engine); best of
+    `repeats` rounds.  Returns aggregate GB/s over all ranks."""
     import torch.distributed as dist
-    host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    src = host.view(-1)[:nbytes]
     dst = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-    for _ in range(2):
-        dst.copy_(host, non_blocking=True)
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for _ in range(iters):
-        dst.copy_(host, non_blocking=True)
-    torch.cuda.synchronize(dev)
-    dt = time.perf_counter() - t0
-    t = torch.tensor([dt], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return world * nbytes * iters / float(t.item()) / 1e9
+    best = None
+    for _ in range(repeats + 1):            # the first round is a warm-up
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(iters):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        best = dt if best is None else min(best, dt)
+    return world * nbytes * iters / best / 1e9
 
 
 def run_e2e(args, wl, dev, world, bt, spec, rank):
@@ -902,12 +905,11 @@ def run_e2e(args, wl, dev, world, bt, spec, rank):
     window = B * crop * (((crop * 3 + 15 + 15) // 16) * 16)       # bytes the bulk copies pull over PCIe per step
     h2d = window + B * classes * 4 + B * 8 + 9 * B
     # what the box can move: N ranks copying the same number of bytes host -> device at once (untimed probe)
-    del host_imgs
-    roof = h2d_probe(dev, world, h2d)
+    roof = h2d_probe(dev, world, host_imgs[0], h2d)
     moved = world * h2d * K / dt / 1e9
     return {"value": world * B * K / dt, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32,
             "ms_per_step": dt / K * 1e3, "h2d_gbs": moved, "h2d_roofline_gbs": roof, "frac_of_h2d_roofline": moved / roof,
-            "h2d_roofline_method": f"{world} rank(s) x 8 plain pinned->device copies of {h2d} bytes at the same moment, wall clock, max over ranks",
+            "h2d_roofline_method": f"{world} rank(s) x 10 plain pinned->device copies of {h2d} bytes at the same moment, wall clock, max over ranks, best of 3 rounds",
             "api": "CropFlipParams.draw + BatchTransform.__call__(pinned uint8 batch, params): the kernel reads the pinned batch in "
                    "place (zero-copy, crop rows only, 8 CTAs) + H2D of logits/labels + MetricState.update + counters read "
                    "back every step; two streams, one step of lookahead"}
