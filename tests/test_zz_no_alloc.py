@@ -50,7 +50,7 @@ def test_grey_and_limits():
     rc = _static(five, np.zeros(5, np.float32), np.ones(5, np.float32), torch.empty((1, 4, 4, 5), dtype=torch.uint8, device="cuda"))
     assert rc == N.TB_EINVAL and "beyond" in N.last_error()
     empty = torch.zeros((0, 3, 4, 4), device="cuda")
-    assert _static(empty, ti.mean, ti.std, torch.empty((0, 4, 4, 3), dtype=torch.uint8, device="cuda")) == N.TB_OK
+    assert _static(empty, np.zeros(3, np.float32), np.ones(3, np.float32), torch.empty((0, 4, 4, 3), dtype=torch.uint8, device="cuda")) == N.TB_OK
 
 
 def test_negative_zero_extrema_through_the_fixed_array():

@@ -133,12 +133,12 @@ static int check_to_image_args(const char* fn, const float* src, int64_t images,
     TB_REQUIRE(C == 1 || C == 3 || C == 4, "%s: C=%d is not a PIL mode (1, 3 or 4 channels)", fn, C);
     TB_REQUIRE(mode >= TB_IMAGE_PLAIN && mode <= TB_IMAGE_STRETCH, "%s: unknown mode %d", fn, mode);
     TB_REQUIRE((mean == nullptr) == (std == nullptr), "%s: mean and std come together", fn);
+    if (images == 0) return TB_OK;          // an empty batch is a no-op: nothing below is read
     for (int c = 0; c < C && mean; ++c) {
         // torchvision raises for a zero std (_functional_tensor.py:923-924); the stretch relies on std > 0
         TB_REQUIRE(std[c] != 0.0f, "%s: std evaluated to zero, leading to division by zero", fn);
         TB_REQUIRE(mode != TB_IMAGE_STRETCH || std[c] > 0.0f, "%s: the stretch needs std > 0", fn);
     }
-    if (images == 0) return TB_OK;
     TB_REQUIRE(src && dst, "%s: NULL src/dst", fn);
     TB_REQUIRE(mode != TB_IMAGE_STRETCH || minmax_given, "%s: the stretch needs the per-channel extrema (tb_channel_minmax)", fn);
     return TB_OK;
