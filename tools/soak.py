@@ -74,6 +74,9 @@ def case_transform(rng):
 def case_resize(rng):
     C = int(rng.choice([1, 3, 3]))
     H, W, B = int(rng.integers(2, 200)), int(rng.integers(2, 200)), int(rng.integers(1, 5))
+    if rng.integers(0, 2):
+        W = 16 * int(rng.integers(1, 40))            # 16-byte aligned rows: the ring kernel's territory (C == 3)
+        B = int(rng.integers(1, 40))
     rs = (int(rng.integers(1, 150)), int(rng.integers(1, 150))) if rng.integers(0, 2) else int(rng.integers(2, 150))
     cc = None if rng.integers(0, 3) == 0 else (int(rng.integers(1, 120)), int(rng.integers(1, 120)))
     dtype = DTYPES[int(rng.integers(0, 3))]
@@ -81,7 +84,7 @@ def case_resize(rng):
     m, s = mean_std(C)
     spec = TransformSpec(resize=rs, center_crop=cc, mean=m, std=s, dtype=dtype)
     bt = BatchTransform(spec, device="cuda")
-    bt.flags = int(rng.choice([0, 1, 16]))
+    bt.flags = int(rng.choice([0, 0, 1, 16, 32, 1 << 8, 2 << 8, 3 << 8, 4]))      # default, generic, two-phase, slide, ring groups, no PDL
     got = bt(torch.from_numpy(batch).cuda())
     want = TO.transform_batch(batch, resize=rs, center_crop=cc, mean=m, std=s, dtype=dtype)
     return same(got, want), dict(kind="resize", C=C, H=H, W=W, B=B, rs=rs, cc=cc, dtype=str(dtype), flags=bt.flags)
@@ -173,6 +176,8 @@ def case_augment(rng):
 
 def case_metrics(rng):
     N, C, k = int(rng.integers(1, 600)), int(rng.integers(1, 1300)), int(rng.integers(1, 8))
+    if rng.integers(0, 2):
+        C = 8 * int(rng.integers(1, 129))            # whole vectors, at most 1024 classes: the one-batch row kernel
     dtype = DTYPES[int(rng.integers(0, 3))]
     g = torch.Generator().manual_seed(int(rng.integers(0, 2 ** 31)))
     logits = torch.randn(N, C, generator=g)
@@ -187,6 +192,8 @@ def case_metrics(rng):
         logits = torch.zeros(N, C) * torch.where(torch.rand(N, C, generator=g) < 0.5, -1.0, 1.0)     # +0 / -0
     logits = logits.to(dtype)
     labels = torch.randint(0, C, (N,), generator=g)
+    if kind == 1:
+        labels[::2] = logits[::2].float().argmax(-1)           # labels on (tied) maxima
     st = MetricState(C, k=k, device="cuda")
     st.update(logits.cuda(), labels.cuda())
     res = st.compute()
