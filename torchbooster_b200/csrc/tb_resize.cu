@@ -760,12 +760,13 @@ inline void slide_geometry(RsParams& p, int B, int sm_count, int flags, int64_t*
 //     per byte value and channel, 96 KiB): lane l reads word l of its row, so the lookups never collide
 //     on a bank whatever the 32 byte values are (the plain [c][256] table cost 35 % extra wavefronts);
 //   * the flattened (column tile, image, output row) space is split EVENLY over the groups of the grid
-//     (a group = tc column threads), in chunks of at most kSlideMaxTR rows that never straddle an image:
+//     (a group = tc column threads), in chunks of at most kRingMaxRows rows that never straddle an image:
 //     no wave quantisation (2048 strips over 592 resident CTAs ran 4 waves for 3.46 waves of work);
 //   * tap byte planes that are zero for a whole warp (horizontal) or output row (vertical) are skipped:
 //     an exact 2x / 4x reduction has taps k * 2^-3 / 2^-4, i.e. only the top byte plane, and its dot
 //     product is one DP4A instead of three.  Same integers either way.
 // ----------------------------------------------------------------------------------------------
+constexpr int kRingMaxRows = 256;     // output rows per chunk (their vertical taps sit in shared memory); at most tc
 constexpr int kRingRG = 4;            // input rows per ring slot (one full / empty barrier pair per slot)
 constexpr int kRingMaxGroups = 3;
 constexpr uint32_t kRingTabBytes = 3u * 256u * 32u * 4u;
@@ -970,10 +971,10 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
     const int grp = warp / wpg;
     const int gt = tid - grp * g.tc;                 // column thread within the group
     const uint32_t s_base = tb_smem_addr(smem);
-    uint32_t (*s_kyb)[4] = reinterpret_cast<uint32_t (*)[4]>(smem + g.kyb_off) + grp * kSlideMaxTR * G;     // [row][G] x {k0, k1, k2, -}
-    int* s_ytop = reinterpret_cast<int*>(smem + g.ytop_off) + grp * kSlideMaxTR;
-    const uint32_t kyb_addr = s_base + g.kyb_off + (uint32_t)(grp * kSlideMaxTR * G * 16);
-    const uint32_t ytop_addr = s_base + g.ytop_off + (uint32_t)(grp * kSlideMaxTR * 4);
+    uint32_t (*s_kyb)[4] = reinterpret_cast<uint32_t (*)[4]>(smem + g.kyb_off) + grp * kRingMaxRows * G;     // [row][G] x {k0, k1, k2, -}
+    int* s_ytop = reinterpret_cast<int*>(smem + g.ytop_off) + grp * kRingMaxRows;
+    const uint32_t kyb_addr = s_base + g.kyb_off + (uint32_t)(grp * kRingMaxRows * G * 16);
+    const uint32_t ytop_addr = s_base + g.ytop_off + (uint32_t)(grp * kRingMaxRows * 4);
     const uint32_t tab_addr = s_base + (uint32_t)lane * 4u;
     const uint32_t ring_addr = s_base + g.ring_off + (uint32_t)(grp * g.slots * RG) * (uint32_t)g.seg_pitch;
     const uint32_t slot_bytes = (uint32_t)(RG * g.seg_pitch);
@@ -1189,7 +1190,7 @@ inline bool ring_geometry(const RsParams& p, int B, int nt, const TbDevice& dev,
     const int64_t avail = (int64_t)dev.max_smem_optin - 1024 - kRingTabBytes;
     int ng = (flags >> 8) & 0xff;
     auto fits = [&](int n, int slots) {
-        return (int64_t)n * ((int64_t)slots * kRingRG * g.seg_pitch + slots * 16 + kSlideMaxTR * G * 16 + kSlideMaxTR * 4) + 256 <= avail;
+        return (int64_t)n * ((int64_t)slots * kRingRG * g.seg_pitch + slots * 16 + kRingMaxRows * G * 16 + kRingMaxRows * 4) + 256 <= avail;
     };
     g.total_rows = (long long)g.tiles_x * B * p.out_h;
     // three groups (24 consumer warps) once every group still owns a few dozen rows (measured on C4: batch 256 -> 90 us
@@ -1205,7 +1206,8 @@ inline bool ring_geometry(const RsParams& p, int B, int nt, const TbDevice& dev,
     }
     g.ng = ng; g.slots = slots;
     g.total_rows = (long long)g.tiles_x * B * p.out_h;
-    g.max_rows = kSlideMaxTR < p.out_h ? kSlideMaxTR : p.out_h;
+    g.max_rows = kRingMaxRows < p.out_h ? kRingMaxRows : p.out_h;
+    if (g.max_rows > g.tc) g.max_rows = g.tc;          // one thread of the group sets up one row of a chunk
     // every group should own a few dozen rows (the halo of a chunk is NT - 2 + 2 input rows)
     long long ctas = (g.total_rows + 24LL * ng - 1) / (24LL * ng);
     if (ctas > dev.sm_count) ctas = dev.sm_count;
@@ -1214,8 +1216,8 @@ inline bool ring_geometry(const RsParams& p, int B, int nt, const TbDevice& dev,
     g.ring_off = off; off += (uint32_t)(ng * slots * kRingRG * g.seg_pitch);
     off = (off + 15u) & ~15u;
     g.bar_off = off; off += (uint32_t)(ng * slots * 16);
-    g.kyb_off = off; off += (uint32_t)(ng * kSlideMaxTR * G * 16);
-    g.ytop_off = off; off += (uint32_t)(ng * kSlideMaxTR * 4);
+    g.kyb_off = off; off += (uint32_t)(ng * kRingMaxRows * G * 16);
+    g.ytop_off = off; off += (uint32_t)(ng * kRingMaxRows * 4);
     g.dyn_bytes = off;
     *out = g;
     *grid = (int)ctas;
