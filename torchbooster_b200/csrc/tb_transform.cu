@@ -220,17 +220,24 @@ __global__ void __launch_bounds__(768, 1) tb_xf_stream_kernel(XfParams p, XfGeom
         ti += g.tile_dt;
         if (ti >= g.tiles_per_image) { ti -= g.tiles_per_image; ++b; }
     };
-    auto issue = [&](int stage) {
-        // bulk copies of tile (bp, tip) into `stage`; nothing is armed for tiles that leave the image
-        if (tp < g.total_tiles) {
-            const int y0 = tip * g.rows;
+    // Crop parameters of the tile a stage holds, read ONCE (when its copies are issued) and kept for the compute side:
+    // a tile costs one round trip for (top, left, flip) instead of two, and none on the path that waits for its data.
+    int top_s0 = 0, left_s0 = 0, top_s1 = 0, left_s1 = 0;
+    bool flip_s0 = false, flip_s1 = false;
+    auto load_params = [&](int b, int& top, int& left, bool& flip) {
+        top = (p.top ? p.top[b] : 0) - p.pad_y;
+        left = (p.left ? p.left[b] : 0) - p.pad_x;
+        flip = p.flip ? (p.flip[b] != 0) : false;
+    };
+    auto issue_tile = [&](int stage, int t, int b, int ti, int top, int left) {
+        // bulk copies of tile (b, ti) into `stage`; nothing is armed for tiles that leave the image
+        if (t < g.total_tiles) {
+            const int y0 = ti * g.rows;
             const int nrows = min(g.rows, p.out_h - y0);
-            const int top = (p.top ? p.top[bp] : 0) - p.pad_y;
-            const int left = (p.left ? p.left[bp] : 0) - p.pad_x;
             const bool inside = top >= 0 && top + p.out_h <= p.H && left >= 0 && left + p.out_w <= p.W;
             if (inside) {
                 const int boff = left * 3;
-                const uint8_t* gsrc = tb_image(p, bp) + (int64_t)(top + y0) * p.pitch + (boff & ~15);
+                const uint8_t* gsrc = tb_image(p, b) + (int64_t)(top + y0) * p.pitch + (boff & ~15);
                 uint8_t* sdst = my_ring_ptr + stage * g.stage_bytes;
                 if (g.contiguous) {
                     if (lane == 0) {
@@ -248,13 +255,41 @@ __global__ void __launch_bounds__(768, 1) tb_xf_stream_kernel(XfParams p, XfGeom
                 }
             }
         }
+    };
+    auto issue = [&](int stage) {
+        int top = 0, left = 0;
+        bool flip = false;
+        if (tp < g.total_tiles) load_params(bp, top, left, flip);
+        issue_tile(stage, tp, bp, tip, top, left);
+        if (stage) { top_s1 = top; left_s1 = left; flip_s1 = flip; }
+        else { top_s0 = top; left_s0 = left; flip_s0 = flip; }
         advance(tp, bp, tip);
     };
-    // first two tiles are in flight while the table is built
-    issue(0);
-    issue(1);
-
-    for (int i = tid; i < 768; i += blockDim.x) plain[i] = X::widen(((const T*)p.lut)[i]);
+    // Start-up: everything the CTA needs from global memory is asked for at once -- the table values (at most four per
+    // thread, into registers) and the parameters of the first TWO tiles -- so the launch pays one round trip, not the
+    // four in a row it used to (top, left of tile 0; of tile 1; then the table: 5 us before the first tile was touched).
+    T lutv[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int i = tid + q * (int)blockDim.x;
+        lutv[q] = i < 768 ? ((const T*)p.lut)[i] : T(0);
+    }
+    {
+        const int tA = tp, bA = bp, tiA = tip;
+        advance(tp, bp, tip);
+        const int tB = tp, bB = bp, tiB = tip;
+        advance(tp, bp, tip);
+        if (tA < g.total_tiles) load_params(bA, top_s0, left_s0, flip_s0);
+        if (tB < g.total_tiles) load_params(bB, top_s1, left_s1, flip_s1);
+        issue_tile(0, tA, bA, tiA, top_s0, left_s0);
+        issue_tile(1, tB, bB, tiB, top_s1, left_s1);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int i = tid + q * (int)blockDim.x;
+        if (i < 768) plain[i] = X::widen(lutv[q]);
+    }
+    for (int i = tid + 4 * (int)blockDim.x; i < 768; i += blockDim.x) plain[i] = X::widen(((const T*)p.lut)[i]);   // (fewer than 192 threads)
     __syncthreads();
     X::fill(tab, plain, tid, blockDim.x);
     __syncthreads();
@@ -269,9 +304,9 @@ __global__ void __launch_bounds__(768, 1) tb_xf_stream_kernel(XfParams p, XfGeom
         const int stage = it & 1;
         const int y0 = tic * g.rows;
         const int nrows = min(g.rows, p.out_h - y0);
-        const int top = (p.top ? p.top[bc] : 0) - p.pad_y;
-        const int left = (p.left ? p.left[bc] : 0) - p.pad_x;
-        const bool flip = p.flip ? (p.flip[bc] != 0) : false;
+        const int top = stage ? top_s1 : top_s0;
+        const int left = stage ? left_s1 : left_s0;
+        const bool flip = stage ? flip_s1 : flip_s0;
         const bool inside = top >= 0 && top + p.out_h <= p.H && left >= 0 && left + p.out_w <= p.W;
         T* __restrict__ dimg = (T*)p.dst + (int64_t)bc * 3 * plane;
 
