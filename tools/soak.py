@@ -78,6 +78,9 @@ def case_resize(rng):
         W = 16 * int(rng.integers(1, 40))            # 16-byte aligned rows: the ring kernel's territory (C == 3)
         B = int(rng.integers(1, 40))
     rs = (int(rng.integers(1, 150)), int(rng.integers(1, 150))) if rng.integers(0, 2) else int(rng.integers(2, 150))
+    if rng.integers(0, 4) == 0 and H % 4 == 0 and W % 4 == 0:
+        f = int(rng.choice([2, 4]))
+        rs = (H // f, W // f)                        # exact 2x / 4x: taps with a single byte plane (their own code path)
     cc = None if rng.integers(0, 3) == 0 else (int(rng.integers(1, 120)), int(rng.integers(1, 120)))
     dtype = DTYPES[int(rng.integers(0, 3))]
     batch = images(rng, B, H, W, C)
@@ -361,13 +364,15 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seconds", type=float, default=60)
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--only", default="", help="comma separated case names (resize, metrics, ...)")
     a = ap.parse_args()
+    cases = [c for c in CASES if not a.only or c.__name__[5:] in a.only.split(",")]
     rng = np.random.default_rng(a.seed)
     t0 = time.time()
     done, fails, classes = {}, 0, {}
     i = 0
     while time.time() - t0 < a.seconds:
-        fn = CASES[i % len(CASES)]
+        fn = cases[i % len(cases)]
         sub = int(rng.integers(0, 2 ** 31))
         i += 1
         try:

@@ -998,10 +998,23 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
                 const int xmin = p.by[2 * ry], n = p.by[2 * ry + 1];
 #pragma unroll
                 for (int j = 0; j < NT; ++j) k[j] = (j < p.ksy && j < n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+                // vertical taps: mode word 1 = plain 22-bit taps (one of them is 1.0); 2 = taps scaled by TWO with only their
+                // top byte plane non-zero (k a multiple of 2^15: exact 2x / 4x) -- the rounded row lands in bits 7..14 of
+                // the accumulator, so the byte offset of its table row is one AND; 0 = taps scaled by four, three planes
                 uint32_t kb[G][3];
-                const uint32_t plain = tb_pack_taps_scaled<G, NT>(k, kb);
+                uint32_t vmode = tb_pack_taps_scaled<G, NT>(k, kb);
+                bool top_only = vmode == 0;
 #pragma unroll
-                for (int q = 0; q < G; ++q) { s_kyb[gt * G + q][0] = kb[q][0]; s_kyb[gt * G + q][1] = kb[q][1]; s_kyb[gt * G + q][2] = kb[q][2]; s_kyb[gt * G + q][3] = plain; }
+                for (int j = 0; j < NT; ++j) top_only = top_only && (k[j] & 0x7fff) == 0;
+                if (top_only) {
+                    int k2[NT];
+#pragma unroll
+                    for (int j = 0; j < NT; ++j) k2[j] = k[j] << 1;
+                    tb_pack_taps<G>(k2, kb);
+                    vmode = 2;
+                }
+#pragma unroll
+                for (int q = 0; q < G; ++q) { s_kyb[gt * G + q][0] = kb[q][0]; s_kyb[gt * G + q][1] = kb[q][1]; s_kyb[gt * G + q][2] = kb[q][2]; s_kyb[gt * G + q][3] = vmode; }
                 top = xmin + NT - 1;
             }
             s_ytop[gt] = top;
@@ -1074,21 +1087,25 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
         };
         auto emit = [&]() {          // output row yy from the register window
             uint32_t kb[G][3];
-            uint32_t low = 0, plain = 0;
+            uint32_t vmode = 0;
 #pragma unroll
             for (int q = 0; q < G; ++q) {
                 const uint4 v = tb_lds128(kyb_addr + (uint32_t)((yy * G + q) * 16));
                 kb[q][0] = v.x; kb[q][1] = v.y; kb[q][2] = v.z;
-                low |= v.x | v.y;
-                plain |= v.w;
+                vmode = v.w;
             }
             uint32_t row7[C];
-            if (plain) {
+            if (vmode == 2) {
+#pragma unroll
+                for (int ch = 0; ch < C; ++ch) {
+                    uint32_t a = 64u;                       // 2^21 at the scale of these taps (2 k >> 16)
+#pragma unroll
+                    for (int q = 0; q < G; ++q) a = __dp4a(win[ch][q], kb[q][2], a);
+                    row7[ch] = a & 0x7f80u;                 // ((a >> 7) & 255) << 7
+                }
+            } else if (vmode == 1) {
 #pragma unroll
                 for (int ch = 0; ch < C; ++ch) row7[ch] = tb_row7_mode<2>(tb_dot_mode<G, 2>(win[ch], kb));
-            } else if (low == 0) {
-#pragma unroll
-                for (int ch = 0; ch < C; ++ch) row7[ch] = tb_row7_mode<0>(tb_dot_mode<G, 0>(win[ch], kb));
             } else {
 #pragma unroll
                 for (int ch = 0; ch < C; ++ch) row7[ch] = tb_row7_mode<1>(tb_dot_mode<G, 1>(win[ch], kb));
