@@ -798,6 +798,14 @@ __device__ __forceinline__ uint4 tb_lds128(uint32_t addr) {
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
     return v;
 }
+// base + idx as ONE 32 x 32 + 64-bit multiply-add (IMAD.WIDE, the FMA pipe): left to itself the compiler builds the
+// 64-bit address from three or four integer-ALU instructions per store, and that pipe is what bounds the ring kernel
+template <typename T>
+__device__ __forceinline__ T* tb_elem_ptr(T* base, uint32_t idx) {
+    uint64_t a;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(a) : "r"(idx), "r"((uint32_t)sizeof(T)), "l"(base));
+    return reinterpret_cast<T*>(a);
+}
 template <typename T>
 __device__ __forceinline__ void tb_st_cs(T* p, uint32_t bits);
 template <>
@@ -1076,7 +1084,7 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
             v[2] = tb_lds_at<65536>(tab_addr + row7[2]);
             if (active) {
 #pragma unroll
-                for (int ch = 0; ch < C; ++ch) tb_st_cs<T>(dbase[ch] + eo, v[ch]);
+                for (int ch = 0; ch < C; ++ch) tb_st_cs<T>(tb_elem_ptr<T>(dbase[ch], eo), v[ch]);
             }
             eo += (uint32_t)p.out_w;
             ++yy;
