@@ -944,8 +944,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--side-priority", type=int, default=1, help="1: the scoring / exchange stream has high priority")
     ap.add_argument("--no-configs", action="store_true", help="skip the per-configuration block (C1 .. C5)")
-    ap.add_argument("--transport", default="int32", choices=["int32", "int64"],
-                    help="wire format of the metric exchange (int32 is exact while every rank has scored < 2^31 / world rows)")
+    ap.add_argument("--transport", default="int64", choices=["int32", "int64"],
+                    help="wire format of the metric exchange (int32: half the bytes, exact while the ranks together have scored "
+                         "< 2^31 rows; measured no faster than int64 at 2-8 ranks: the exchange is latency-bound)")
     ap.add_argument("--no-affinity", action="store_true", help="do not pin the rank to its GPU's local CPUs")
     ap.add_argument("--configs-only", default="", help="development: time only these configurations (comma separated) and print them")
     args = ap.parse_args()
