@@ -247,3 +247,19 @@ def test_resized_crop_replay_over_images_of_different_sizes():
     b2, f2 = rp.draw_ragged(hs[120:], ws[120:], 0.5)
     assert np.array_equal(np.concatenate([b1, b2]), np.array(want, np.int32))
     assert np.concatenate([f1, f2]).tolist() == flips
+
+
+def test_bench_cpu_arm_staggers_the_workers():
+    """bench.py's CPU arm: the first batch of every DataLoader worker is shorter, (w + 1) / workers of a batch, so that
+    the lockstepped workers end up evenly out of phase; every later batch is a full one; CONFIGS name every BASELINE
+    configuration with its algorithmic bytes."""
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+    import bench
+    sizes = [len(b) for b in bench._StaggeredBatches(pool=100, B=64, workers=4, batches=7)]
+    assert sizes == [16, 32, 48, 64, 64, 64, 64]
+    assert all(0 <= i < 100 for b in bench._StaggeredBatches(100, 64, 4, 3) for i in b)
+    assert {"c1", "c2", "c3", "c4", "c5", "c5_bf16"} <= set(bench.CONFIGS)
+    assert bench.CONFIGS["c2"]["alg_bytes"] == 451584 and bench.CONFIGS["c4"]["alg_bytes"] == 1572864
+    assert bench.CONFIGS["c5"]["alg_bytes"] == 4008 and bench.CONFIGS["c1"]["alg_bytes"] == 15360
