@@ -213,8 +213,9 @@ def test_larger_images_and_limits():
             torch.zeros((1, 8, 8, 4), dtype=torch.uint8, device="cuda"), params=(None, None, None, [[("Invert", 0.0)]]))
     with pytest.raises(ValueError, match="seed"):
         BatchTransform(spec, device="cuda")(torch.zeros((1, 8, 8, 3), dtype=torch.uint8, device="cuda"))
-    with pytest.raises(NotImplementedError):
-        TransformSpec(resize=64, rand_augment=True)
+    assert TransformSpec(resize=64, rand_augment=True).two_stage        # resize hands a uint8 image to the augment kernel
+    with pytest.raises(NotImplementedError, match="ragged"):
+        BatchTransform(TransformSpec(resize=(8, 8), rand_augment=True), device="cuda").ragged([torch.zeros((9, 9, 3), dtype=torch.uint8)])
     # an empty batch and an empty operation list are fine
     empty = BatchTransform(spec, device="cuda")(torch.zeros((0, 8, 8, 3), dtype=torch.uint8, device="cuda"), params=(None, None, None, []))
     assert tuple(empty.shape) == (0, 3, 8, 8)
@@ -265,3 +266,65 @@ def test_resized_crop_chain_on_frames_beyond_4x():
         spec = TransformSpec(random_resized_crop=size, pre_rotation=pre, flip_p=0.5, rand_augment=ra, mean=IMAGENET[0], std=IMAGENET[1])
         got = BatchTransform(spec, device="cuda", seed=77)(torch.from_numpy(batch).cuda())
         assert same(got, want), (H, W, size, pre, ra)
+
+
+def _resize_chain_cases():
+    import torchvision.transforms as T
+    return [
+        # Resize -> CenterCrop -> RandomCrop(reflect padding): the padding mirrors the centre crop, not the resized image
+        ((96, 128), dict(resize=64, center_crop=56, crop=56, padding=4, padding_mode="reflect", flip_p=0.5),
+         lambda: [T.Resize(64), T.CenterCrop(56), T.RandomCrop(56, padding=4, padding_mode="reflect"), T.RandomHorizontalFlip()]),
+        # Resize -> RandomCrop(symmetric padding), no centre crop
+        ((90, 70), dict(resize=(64, 60), crop=48, padding=6, padding_mode="symmetric", flip_p=0.5),
+         lambda: [T.Resize((64, 60)), T.RandomCrop(48, padding=6, padding_mode="symmetric"), T.RandomHorizontalFlip()]),
+        # CenterCrop -> RandomCrop(zero padding), no resize: the padding must not show what the centre crop cut away
+        ((60, 60), dict(center_crop=40, crop=40, padding=4, flip_p=None),
+         lambda: [T.CenterCrop(40), T.RandomCrop(40, padding=4)]),
+        # CenterCrop LARGER than the image (zero fill) then edge padding: the edge is the zero fill
+        ((30, 44), dict(center_crop=(40, 50), crop=(36, 50), padding=3, padding_mode="edge", flip_p=0.5),
+         lambda: [T.CenterCrop((40, 50)), T.RandomCrop((36, 50), padding=3, padding_mode="edge"), T.RandomHorizontalFlip()]),
+        # the ImageNet evaluation resize followed by the training augmentations
+        ((300, 400), dict(resize=256, center_crop=224, flip_p=0.5, rand_augment=True),
+         lambda: [T.Resize(256), T.CenterCrop(224), T.RandomHorizontalFlip(), T.RandAugment()]),
+        ((150, 130), dict(resize=72, center_crop=64, crop=64, padding=4, padding_mode="edge", flip_p=0.5, rotation=15, rand_augment=True),
+         lambda: [T.Resize(72), T.CenterCrop(64), T.RandomCrop(64, padding=4, padding_mode="edge"), T.RandomHorizontalFlip(),
+                  T.RandomRotation(15), T.RandAugment()]),
+    ]
+
+
+@pytest.mark.parametrize("case", range(6))
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_resize_then_padding_or_augment_vs_the_compose(case, dtype):
+    """Resize / CenterCrop pipelines whose tail needs the resized image as a whole (padding that mirrors it, padding after a
+    centre crop, rotation / RandAugment): two launches with a planar uint8 hand-off, against the literal Compose under
+    torch.manual_seed with the draws replayed from the same seed."""
+    import torchvision.transforms as T
+    from PIL import Image
+    (H, W), kw, stages = _resize_chain_cases()[case]
+    rng = np.random.default_rng(40 + case)
+    B = 6
+    batch = rng.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+    compose = T.Compose(stages() + [T.ToTensor(), T.Normalize(IMAGENET[0], IMAGENET[1])])
+    spec = TransformSpec(mean=IMAGENET[0], std=IMAGENET[1], dtype=dtype, **kw)
+    assert spec.two_stage
+    bt = BatchTransform(spec, device="cuda", seed=31 + case)
+    torch.manual_seed(31 + case)
+    for step in range(2):           # two consecutive batches from one generator
+        want = torch.stack([compose(Image.fromarray(batch[b])) for b in range(B)]).to(dtype)
+        got = bt(torch.from_numpy(batch).cuda())
+        assert same(got, want), (case, step)
+    # explicit parameters and the oracle's own chain
+    g = bt.geometry(H, W)
+    th, tw = g["out"]
+    ph, pw = g["cur"][0] + 2 * g["pad"][1], g["cur"][1] + 2 * g["pad"][0]
+    top = rng.integers(0, ph - th + 1, B).astype(np.int32)
+    left = rng.integers(0, pw - tw + 1, B).astype(np.int32)
+    flip = rng.integers(0, 2, B).astype(np.uint8)
+    ops = [[("Rotate", 21.0), ("Posterize", 5.0)] if b % 2 else [] for b in range(B)] if spec.augments else None
+    params = (top, left, flip, ops) if spec.augments else (top, left, flip)
+    got = BatchTransform(spec, device="cuda")(torch.from_numpy(batch).cuda(), params=params)
+    pad = kw.get("padding", 0)
+    want = TO.transform_batch(batch, resize=kw.get("resize"), center_crop=kw.get("center_crop"), padding=pad,
+                              padding_mode=kw.get("padding_mode", "constant"), crop_top=top, crop_left=left, out_size=(th, tw),
+                              flip=flip, ops=ops, mean=IMAGENET[0], std=IMAGENET[1], dtype=dtype)
+    assert same(got, want), case

@@ -57,8 +57,8 @@ class TransformSpec:
     rotation      ``T.RandomRotation`` degrees (number or (min, max)); nearest, no expand, fill 0.
     rand_augment  ``T.RandAugment`` as ``(num_ops, magnitude, num_magnitude_bins)``, ``True`` = its defaults
                   ``(2, 9, 31)`` (``resnet.py:99-100``).  Both apply to crop / flip pipelines (one launch) and
-                  after a random_resized_crop (the crop hands a uint8 image to the augment kernel); the
-                  per-sample operations come from ``params`` or the replayed generator.
+                  after a random_resized_crop or a Resize / CenterCrop (the resize hands a uint8 image to the
+                  augment kernel); the per-sample operations come from ``params`` or the replayed generator.
     mean, std     ``T.Normalize``; ``None`` = ToTensor only.
     one_minus     the ``1.0 - X`` of ``examples/img_gen/gan/gan.py:99``.
     dtype         output dtype: float32 (the reference), bfloat16 or float16 (RNE of the fp32 value).
@@ -86,20 +86,24 @@ class TransformSpec:
             raise ValueError("Padding mode should be either constant, edge, reflect or symmetric")
         if (self.mean is None) != (self.std is None):
             raise ValueError("mean and std must be given together")
-        if self.resize is not None and _pair(self.padding) != (0, 0) and self.padding_mode != "constant":
-            raise NotImplementedError("resize combined with non-constant padding is not supported")
-        if self.center_crop is not None and _pair(self.padding) != (0, 0):
-            raise NotImplementedError("center_crop combined with padding is not supported")
         if self.random_resized_crop is not None and (self.resize is not None or self.center_crop is not None or
                                                      self.crop is not None or _pair(self.padding) != (0, 0)):
             raise ValueError("random_resized_crop excludes resize, center_crop, crop and padding")
-        if self.augments and (self.resize is not None or self.center_crop is not None):
-            raise NotImplementedError("rotation / rand_augment are built for crop / flip and random_resized_crop pipelines")
         if self.pre_rotation is not None and self.random_resized_crop is None:
             raise NotImplementedError("pre_rotation is the head of a random_resized_crop pipeline (use rotation otherwise)")
         if self.rand_augment not in (None, True, False) and len(tuple(self.rand_augment)) != 3:
             raise ValueError("rand_augment is True or (num_ops, magnitude, num_magnitude_bins)")
         N.dtype_code(self.dtype)
+
+    @property
+    def two_stage(self) -> bool:
+        """Resize / CenterCrop pipelines whose tail reads the resized image as a whole: RandomCrop padding that mirrors it
+        (or pads a centre crop: the padding must not show the pixels the centre crop cut away) and rotation / RandAugment.
+        The resize kernel hands a planar uint8 image to the augment kernel (two launches)."""
+        if self.resize is None and self.center_crop is None:
+            return False
+        padded = _pair(self.padding) != (0, 0)
+        return self.augments or (padded and (self.padding_mode != "constant" or self.center_crop is not None))
 
     @property
     def augments(self) -> bool:
@@ -534,6 +538,53 @@ class BatchTransform:
                 lut.data_ptr(), N.FLAG_SRC_PLANAR, stream))
         return out
 
+    def _resize_chain(self, batch: torch.Tensor, g, params, out: Optional[torch.Tensor]) -> torch.Tensor:
+        """Resize [-> CenterCrop] -> RandomCrop(padding, any mode) -> flip [-> rotation / RandAugment] -> table
+        (``TransformSpec.two_stage``): the resize kernel writes the resized (and centre-cropped) image as planar uint8,
+        the augment kernel pads / crops / flips it, runs the operations and applies the table."""
+        sp = self.spec
+        B, H, W, Cn = batch.shape
+        out_h, out_w = g["out"]
+        cur_h, cur_w = g["cur"]
+        if sp.augments:
+            if params is None or len(params) != 4:
+                raise ValueError("rotation / rand_augment need params=(top, left, flip, ops) or a seed")
+            ops = params[3]
+            params = params[:3]
+        else:
+            ops = None
+        if out is None:
+            out = torch.empty((B, Cn, out_h, out_w), dtype=sp.dtype, device=self.device)
+        elif tuple(out.shape) != (B, Cn, out_h, out_w) or out.dtype != sp.dtype or not out.is_contiguous() or out.device != self.device:
+            raise ValueError(f"out must be a contiguous tensor of shape {(B, Cn, out_h, out_w)}, dtype {sp.dtype} on {self.device}")
+        if B == 0:
+            return out
+        top = left = flip = None
+        if params is not None:
+            top, left, flip = self._params_to_device(params, B)
+        rec = None if ops is None else self._ops_to_device(ops, B, out_h, out_w, Cn)
+        lut = self.lut(Cn)
+        px, py = g["pad"]
+        ptr = lambda t: None if t is None else t.data_ptr()
+        L = N.lib()
+        with torch.cuda.device(self.device):
+            stream = N.current_stream_ptr(self.device)
+            rs_h, rs_w = g["rs"]
+            ksx, bx, kx = self._resize_taps(W, rs_w) if rs_w != W else (0, None, None)
+            ksy, by, ky = self._resize_taps(H, rs_h) if rs_h != H else (0, None, None)
+            off_y, off_x = g["off"]
+            mid = torch.empty((B, Cn, cur_h, cur_w), dtype=torch.uint8, device=self.device)
+            N.check(L.tb_resize_bilinear_u8_nhwc_to_nchw(
+                batch.data_ptr(), B, H, W, Cn, batch.stride(0), batch.stride(1), rs_h, rs_w,
+                ptr(bx), ptr(kx), ksx, ptr(by), ptr(ky), ksy, mid.data_ptr(), N.TB_U8, cur_h, cur_w,
+                None, None, None, off_y, off_x, self._identity_bytes(Cn).data_ptr(), self.flags, stream))
+            mode = N.PAD_MODES[sp.padding_mode] if (px or py) else N.PAD_MODES["none"]
+            N.check(L.tb_augment_u8_nhwc_to_nchw(
+                mid.data_ptr(), B, cur_h, cur_w, Cn, Cn * cur_h * cur_w, cur_w, out.data_ptr(), N.dtype_code(sp.dtype),
+                out_h, out_w, ptr(top), ptr(left), ptr(flip), py, px, mode, ptr(rec), 0 if rec is None else int(rec.shape[1]),
+                lut.data_ptr(), N.FLAG_SRC_PLANAR, stream))
+        return out
+
     # -- ragged batches --------------------------------------------------------------------
     def _ragged_geometry(self, sizes: np.ndarray, params):
         """Per-sample records ``[top, left, h, w, resized h, resized w, y, x, image h, image w]`` for images of the
@@ -720,6 +771,8 @@ class BatchTransform:
             if params is None:
                 raise ValueError("random_resized_crop needs params=(box[B,4], flip) or a seed")
             box, flip = self._boxes_to_device(params, B)
+        elif sp.two_stage:
+            return self._resize_chain(batch, g, params, out)
         elif sp.augments:
             if params is None or len(params) != 4:
                 raise ValueError("rotation / rand_augment need params=(top, left, flip, ops) or a seed")
