@@ -18,7 +18,7 @@ outs = [torch.empty((B, 3, 256, 256), device=dev) for _ in range(8)]
 for i in range(20):
     bt(x[i % 8], out=outs[i % 8])
 torch.cuda.synchronize()
-names = ["entry", "dep wait done", "table filled", "first copy issued", "first slot full", "first store", "grp0 done", "grpN done", "producer0 done"]
+names = ["entry", "dep wait done", "table filled", "first copy issued", "first slot full", "first store", "grp0 done", "grpN done", "producer0 done", "chunk set up", "waiting for slot"]
 for mode in ("alone", "back-to-back"):
     lib.tb_trace_read(None, 1)
     torch.cuda.synchronize()
@@ -26,7 +26,7 @@ for mode in ("alone", "back-to-back"):
         bt(x[0], out=outs[0])
     else:
         for i in range(6):
-            bt(x[i % 8], out=outs[i % 8])       # the trace holds the last launch (first-copy / first-full / first-store slots: the first)
+            bt(x[i % 8], out=outs[i % 8])       # the trace holds the last launch
     torch.cuda.synchronize()
     buf = np.zeros(256 * 16, dtype=np.uint64)
     lib.tb_trace_read(buf.ctypes.data, 0)

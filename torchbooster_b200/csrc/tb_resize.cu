@@ -778,10 +778,13 @@ struct RingGeom {
     int seg_pitch;          // bytes per staged row (multiple of 16, >= longest segment + 16)
     int tiles_x;
     int max_rows;           // output rows per chunk
-    long long total_rows;   // tiles_x * B * out_h
+    int total_rows;         // tiles_x * B * out_h (< 2^31: the kernel's row arithmetic is 32-bit, 64-bit divisions cost ~0.3 us each)
+    int gpu;                // > 0: groups per (image, column tile) unit -- no group straddles two units; 0: even split of all rows
+    int rows_q, rows_r;     // even split: total_rows = rows_q * groups + rows_r
     uint32_t ring_off, bar_off, kyb_off, ytop_off, dyn_bytes;
 };
 
+__device__ __forceinline__ void tb_prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void tb_named_barrier(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -875,18 +878,32 @@ struct RingChunk {
     int first, last;        // last < first: nothing to fetch (all rows / columns outside the resized image)
     int s0, seg_len;
 };
+// Output rows [F, F1) of group `me` of `ngt`.  Even split of all rows, or -- when the host found that every unit (one
+// image x one column tile, out_h rows) can be given g.gpu whole groups at little loss -- an even split of each unit
+// among its own groups: a group that straddles two units pays a second chunk set-up and window warm-up.
+__device__ __forceinline__ void tb_ring_range(const RingGeom& g, int out_h, int me, int& F, int& F1) {
+    if (g.gpu > 0) {
+        const int unit = (int)((unsigned)me / (unsigned)g.gpu);
+        const int j = me - unit * g.gpu;
+        F = F1 = 0;
+        if ((long long)unit * out_h >= g.total_rows) return;
+        F = unit * out_h + (int)((unsigned)(j * out_h) / (unsigned)g.gpu);
+        F1 = unit * out_h + (int)((unsigned)((j + 1) * out_h) / (unsigned)g.gpu);
+        return;
+    }
+    F = me * g.rows_q + min(me, g.rows_r);
+    F1 = F + g.rows_q + (me < g.rows_r ? 1 : 0);
+}
+
 template <int NT>
-__device__ __forceinline__ bool tb_ring_next(const RsParams& p, const RingGeom& g, long long& F, long long F1, RingChunk& c) {
+__device__ __forceinline__ bool tb_ring_next(const RsParams& p, const RingGeom& g, int& F, int F1, RingChunk& c) {
     if (F >= F1) return false;
-    const long long unit = F / p.out_h;
-    c.y0 = (int)(F - unit * p.out_h);
-    c.b = (int)(unit / g.tiles_x);
-    c.tx = (int)(unit - (long long)c.b * g.tiles_x);
-    long long nr = p.out_h - c.y0;
-    if (nr > g.max_rows) nr = g.max_rows;
-    if (nr > F1 - F) nr = F1 - F;
-    c.nr = (int)nr;
-    F += nr;
+    const int unit = (int)((unsigned)F / (unsigned)p.out_h);
+    c.y0 = F - unit * p.out_h;
+    c.b = (int)((unsigned)unit / (unsigned)g.tiles_x);
+    c.tx = unit - c.b * g.tiles_x;
+    c.nr = min(min(p.out_h - c.y0, g.max_rows), F1 - F);
+    F += c.nr;
     c.oy = (p.top ? p.top[c.b] : 0) + p.off_y;
     c.ox = (p.left ? p.left[c.b] : 0) + p.off_x;
     c.flip = p.flip ? (p.flip[c.b] != 0) : 0;
@@ -927,32 +944,51 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
     }
     __syncthreads();                // the barriers exist before anyone arrives on or waits for them
     tb_launch_dependents();
+    // the group's share of the rows: arithmetic only, done while the previous launch drains
+    int F, F1;
+    tb_ring_range(g, p.out_h, (int)blockIdx.x * g.ng + (warp >= n_cons ? warp - n_cons : warp / wpg), F, F1);
     tb_grid_dependency_wait();
     if (warp < n_cons) {
+        // the head of the four tap tables into L1 (one 128-byte line per thread and table): the chunk set-up below then
+        // reads them at L1 latency instead of paying two more dependent trips to L2 / DRAM after the table fill
+        {
+            const size_t line = (size_t)tid * 128;
+            if (line < (size_t)p.rs_h * 8) tb_prefetch_l1((const char*)p.by + line);
+            if (line < (size_t)p.rs_h * p.ksy * 4) tb_prefetch_l1((const char*)p.ky + line);
+            if (line < (size_t)p.rs_w * 8) tb_prefetch_l1((const char*)p.bx + line);
+            if (line < (size_t)p.rs_w * p.ksx * 4) tb_prefetch_l1((const char*)p.kx + line);
+        }
         // lane-replicated table: [c][e][lane] words, filled by the consumer warps while the producer warps already work
-        // out their first chunk and start its copies (they never touch the table)
+        // out their first chunk and start its copies (they never touch the table).  A dozen values of the thread's share
+        // at a time: one round trip to L2 for all of them at the usual 512 / 768 consumer threads.
         const int nthr = n_cons * 32;
         uint4* t4 = reinterpret_cast<uint4*>(smem);
-#pragma unroll 4
-        for (int i = tid; i < 3 * 256 * 8; i += nthr) {
-            uint32_t v;
-            if (sizeof(T) == 4) v = __float_as_uint(__ldg((const float*)p.lut + (i >> 3)));
-            else v = __ldg((const uint16_t*)p.lut + (i >> 3));
-            t4[i] = make_uint4(v, v, v, v);
+        constexpr int kPer = 12;
+        for (int i0 = tid; i0 < 3 * 256 * 8; i0 += kPer * nthr) {
+            uint32_t tv[kPer];
+#pragma unroll
+            for (int k = 0; k < kPer; ++k) {
+                const int i = i0 + k * nthr;
+                tv[k] = 0;
+                if (i < 3 * 256 * 8) {
+                    if (sizeof(T) == 4) tv[k] = __float_as_uint(__ldg((const float*)p.lut + (i >> 3)));
+                    else tv[k] = __ldg((const uint16_t*)p.lut + (i >> 3));
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < kPer; ++k) {
+                const int i = i0 + k * nthr;
+                if (i < 3 * 256 * 8) t4[i] = make_uint4(tv[k], tv[k], tv[k], tv[k]);
+            }
         }
         tb_named_barrier(15, nthr);
     }
 
-    const long long ngt = (long long)gridDim.x * g.ng;
     if (warp >= n_cons) {
         // ------------------------------------------------------------------ producer warps: one per group
         // (one warp polling every ring topped out near 1.5 TB/s of reads: tools/micro/bulk_copy_rate.cu shows a
         // single warp issuing four 1.5 KB copies per step saturates at ~4 TB/s even with nothing else to do)
         const int gi = warp - n_cons;
-        if (gi >= g.ng) return;
-        const long long me = (long long)blockIdx.x * g.ng + gi;
-        long long F = me * g.total_rows / ngt;
-        const long long F1 = (me + 1) * g.total_rows / ngt;
         int slot = 0;
         uint32_t phase = 1;                       // a fresh barrier passes a wait on parity 1
         RingChunk ch;
@@ -987,12 +1023,6 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
     const uint32_t ring_addr = s_base + g.ring_off + (uint32_t)(grp * g.slots * RG) * (uint32_t)g.seg_pitch;
     const uint32_t slot_bytes = (uint32_t)(RG * g.seg_pitch);
     const int64_t plane = (int64_t)p.out_h * p.out_w;
-    long long F, F1;
-    {
-        const long long me = (long long)blockIdx.x * g.ng + grp;
-        F = me * g.total_rows / ngt;
-        F1 = (me + 1) * g.total_rows / ngt;
-    }
     int slot = 0;
     uint32_t phase = 0;
     RingChunk c;
@@ -1217,7 +1247,9 @@ inline bool ring_geometry(const RsParams& p, int B, int nt, const TbDevice& dev,
     auto fits = [&](int n, int slots) {
         return (int64_t)n * ((int64_t)slots * kRingRG * g.seg_pitch + slots * 16 + kRingMaxRows * G * 16 + kRingMaxRows * 4) + 256 <= avail;
     };
-    g.total_rows = (long long)g.tiles_x * B * p.out_h;
+    const long long total64 = (long long)g.tiles_x * B * p.out_h;
+    if (total64 >= ((long long)1 << 30)) return false;      // 32-bit row arithmetic in the kernel
+    g.total_rows = (int)total64;
     // three groups (24 consumer warps) once every group still owns a few dozen rows (measured on C4: batch 256 -> 90 us
     // with three groups, 104 us with two; batch 32, 18 rows per group with three: two groups are faster)
     if (ng == 0) ng = (fits(3, 4) && g.total_rows >= 3LL * dev.sm_count * 40) ? 3 : 2;
@@ -1230,13 +1262,25 @@ inline bool ring_geometry(const RsParams& p, int B, int nt, const TbDevice& dev,
         if (!fits(ng, slots)) return false;
     }
     g.ng = ng; g.slots = slots;
-    g.total_rows = (long long)g.tiles_x * B * p.out_h;
     g.max_rows = kRingMaxRows < p.out_h ? kRingMaxRows : p.out_h;
     if (g.max_rows > g.tc) g.max_rows = g.tc;          // one thread of the group sets up one row of a chunk
     // every group should own a few dozen rows (the halo of a chunk is NT - 2 + 2 input rows)
     long long ctas = (g.total_rows + 24LL * ng - 1) / (24LL * ng);
     if (ctas > dev.sm_count) ctas = dev.sm_count;
     if (ctas < 1) ctas = 1;
+    // whole groups per unit when that costs little: the longest group then has ceil(out_h / gpu) rows against the even
+    // split's total / groups, but none pays for a second chunk (measured on C4 at batch 32: see DESIGN.md 4.3)
+    g.gpu = 0;
+    {
+        const long long groups = ctas * ng, units = g.total_rows / p.out_h;
+        const long long per = units > 0 ? groups / units : 0;
+        if (per >= 2 && per <= 64 && !((flags >> 16) & 1)) {
+            const long long longest = (p.out_h + per - 1) / per;
+            if (longest >= 8 && (double)g.total_rows / ((double)groups * (double)longest) >= 0.92) g.gpu = (int)per;
+        }
+    }
+    g.rows_q = (int)(g.total_rows / (ctas * ng));
+    g.rows_r = (int)(g.total_rows % (ctas * ng));
     uint32_t off = kRingTabBytes;
     g.ring_off = off; off += (uint32_t)(ng * slots * kRingRG * g.seg_pitch);
     off = (off + 15u) & ~15u;
