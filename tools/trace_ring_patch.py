@@ -1,4 +1,5 @@
-# development: patch tb_resize.cu with %globaltimer trace points (ring kernel), build to build_ab/libT.so, restore
+# development: patch tb_resize.cu with %globaltimer trace points (ring kernel), build to build_ab/libT.so, restore the source
+# and the library (the patch is a list of exact-text replacements: it has to follow edits of the kernel)
 import subprocess, shutil
 p='/root/repo/torchbooster_b200/csrc/tb_resize.cu'
 orig=open(p).read()
@@ -16,16 +17,17 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
 rep("    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + g.bar_off);        // [ng][slots][2]: full, empty\n",
     "    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + g.bar_off);        // [ng][slots][2]: full, empty\n    if (tid == 0) TR(0);\n    bool tr_first = true, tr_first2 = true;\n")
 rep("    tb_grid_dependency_wait();\n    if (warp < n_cons) {", "    tb_grid_dependency_wait();\n    if (tid == 0) TR(1);\n    if (warp < n_cons) {")
-rep("            tb_named_barrier(15, (int)blockDim.x);\n            before_table = -1;", "            tb_named_barrier(15, (int)blockDim.x);\n            before_table = -1;\n            if (gi == 0 && lane == 0) TR(2);")
+rep("        tb_named_barrier(15, nthr);\n    }", "        tb_named_barrier(15, nthr);\n        if (tid == 0) TR(2);\n    }")
 rep("                    tb_bulk_g2s(sdst, gsrc0 + (int64_t)r * p.pitch, (uint32_t)ch.seg_len, full);\n                }",
     "                    tb_bulk_g2s(sdst, gsrc0 + (int64_t)r * p.pitch, (uint32_t)ch.seg_len, full);\n                }\n                if (gi == 0 && lane == 0 && tr_first) { TR(3); tr_first = false; }")
-rep("        if (before_table >= 0) fill_table();\n        return;", "        if (before_table >= 0) fill_table();\n        if (gi == 0 && lane == 0) TR(8);\n        return;")
+rep("            }\n        }\n        return;\n    }\n\n    // ---------------------------------------------------------------------- consumers",
+    "            }\n        }\n        if (gi == 0 && lane == 0) TR(8);\n        return;\n    }\n\n    // ---------------------------------------------------------------------- consumers")
 rep("        uint32_t eo = 0;                             // element offset of output row yy from dbase\n        tb_named_barrier(1 + grp, g.tc);\n",
     "        uint32_t eo = 0;                             // element offset of output row yy from dbase\n        tb_named_barrier(1 + grp, g.tc);\n        if (tid == 32 && tr_first) TR(9);\n")
 rep("                    tb_mbar_wait(full, phase);\n", "                    if (tid == 32 && tr_first) TR(10);\n                    tb_mbar_wait(full, phase);\n                    if (tid == 32 && tr_first) { TR(4); tr_first = false; }\n")
 rep("            if (active) {\n#pragma unroll\n                for (int ch = 0; ch < C; ++ch) tb_st_cs<T>",
     "            if (tid == 32 && tr_first2) { TR(5); tr_first2 = false; }\n            if (active) {\n#pragma unroll\n                for (int ch = 0; ch < C; ++ch) tb_st_cs<T>")
-rep("    if (table_pending) tb_named_barrier(15, (int)blockDim.x);", "    if (table_pending) tb_named_barrier(15, (int)blockDim.x);\n    if (gt == 32) TR(6 + (grp ? 1 : 0));")
+rep("            while (yy < nr) emit_zero();\n        }\n    }\n}", "            while (yy < nr) emit_zero();\n        }\n    }\n    if (gt == 32) TR(6 + (grp ? 1 : 0));\n}")
 rep('extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(', '''extern "C" __attribute__((visibility("default"))) int tb_trace_read(unsigned long long* host, int reset) {
     if (reset) { static unsigned long long z[256 * 16]; return (int)cudaMemcpyToSymbol(tb_trace, z, sizeof(z)); }
     return (int)cudaMemcpyFromSymbol(host, tb_trace, sizeof(unsigned long long) * 256 * 16);
