@@ -177,6 +177,63 @@ def case_augment(rng):
     return same(got, want), info
 
 
+def case_twostage(rng):
+    """Resize / CenterCrop, then RandomCrop with any padding mode, flip and (half of the time) operations: the resize kernel
+    hands planar bytes to the augment kernel (TransformSpec.two_stage)."""
+    from torchbooster_b200.transforms import resized_output_size
+    C = int(rng.choice([1, 3, 3]))
+    H, W, B = int(rng.integers(8, 160)), int(rng.integers(8, 160)), int(rng.integers(1, 8))
+    rs = None if rng.integers(0, 4) == 0 else ((int(rng.integers(6, 120)), int(rng.integers(6, 120))) if rng.integers(0, 2) else int(rng.integers(6, 120)))
+    cur_h, cur_w = resized_output_size(H, W, rs) if rs is not None else (H, W)
+    cc = None
+    if rs is None or rng.integers(0, 2):
+        cc = (int(rng.integers(4, cur_h + 12)), int(rng.integers(4, cur_w + 12)))
+        cur_h, cur_w = cc
+    with_ops = bool(rng.integers(0, 2))
+    pad = int(rng.integers(0 if with_ops else 1, 6))
+    mode = MODES[int(rng.integers(0, 4))]
+    if mode == "reflect":
+        pad = min(pad, cur_h - 1, cur_w - 1)
+    if mode == "symmetric":
+        pad = min(pad, cur_h, cur_w)
+    if not with_ops and pad == 0:
+        return True, dict(kind="twostage", skipped=True)
+    if not with_ops and mode == "constant" and cc is None:
+        mode = "edge"                                 # (constant padding after a bare resize is the one-launch route)
+    th, tw = int(rng.integers(1, cur_h + 2 * pad + 1)), int(rng.integers(1, cur_w + 2 * pad + 1))
+    dtype = DTYPES[int(rng.integers(0, 3))]
+    batch = images(rng, B, H, W, C)
+    top = rng.integers(0, cur_h + 2 * pad - th + 1, B).astype(np.int32)
+    left = rng.integers(0, cur_w + 2 * pad - tw + 1, B).astype(np.int32)
+    flip = rng.integers(0, 2, B).astype(np.uint8)
+    ops = None
+    if with_ops:
+        ops = []
+        for b in range(B):
+            mags = A.rand_augment_magnitudes(th, tw, int(rng.integers(0, 31)))
+            mine = []
+            for _ in range(int(rng.integers(0, 4))):
+                name = NAMES[int(rng.integers(0, len(NAMES)))]
+                mag = float(np.float32(rng.uniform(-360, 360))) if name == "RandomRotation" else mags.get(name, 0.0)
+                if name not in ("Posterize", "Solarize", "RandomRotation") and rng.integers(0, 2):
+                    mag = -mag
+                mine.append((name, mag))
+            ops.append(mine)
+    m, s = mean_std(C)
+    spec = TransformSpec(resize=rs, center_crop=cc, crop=(th, tw), padding=pad, padding_mode=mode, flip_p=.5,
+                         rotation=10 if with_ops else None, rand_augment=True if with_ops else None, mean=m, std=s, dtype=dtype)
+    info = dict(kind="twostage", C=C, H=H, W=W, B=B, rs=rs, cc=cc, pad=pad, mode=mode, th=th, tw=tw, dtype=str(dtype), ops=ops)
+    if not spec.two_stage:
+        return False, dict(info, error="not two_stage")
+    try:
+        got = BatchTransform(spec, device="cuda")(torch.from_numpy(batch).cuda(), params=(top, left, flip, ops) if with_ops else (top, left, flip))
+    except Exception as e:
+        return False, dict(info, ops=None, error=repr(e))
+    want = TO.transform_batch(batch, resize=rs, center_crop=cc, crop_top=top, crop_left=left, out_size=(th, tw), flip=flip, ops=ops,
+                              padding=pad, padding_mode=mode, mean=m, std=s, dtype=dtype)
+    return same(got, want), info
+
+
 def case_metrics(rng):
     N, C, k = int(rng.integers(1, 600)), int(rng.integers(1, 1300)), int(rng.integers(1, 8))
     if rng.integers(0, 2):
@@ -357,7 +414,7 @@ def case_loader(rng):
     return ok, info
 
 
-CASES = [case_transform, case_resize, case_rrc, case_ragged, case_augment, case_metrics, case_image, case_stream, case_chain, case_loader]
+CASES = [case_transform, case_resize, case_rrc, case_ragged, case_augment, case_twostage, case_metrics, case_image, case_stream, case_chain, case_loader]
 
 
 def main():
