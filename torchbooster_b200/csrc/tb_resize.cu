@@ -1250,9 +1250,9 @@ inline bool ring_geometry(const RsParams& p, int B, int nt, const TbDevice& dev,
     const long long total64 = (long long)g.tiles_x * B * p.out_h;
     if (total64 >= ((long long)1 << 30)) return false;      // 32-bit row arithmetic in the kernel
     g.total_rows = (int)total64;
-    // three groups (24 consumer warps) once every group still owns a few dozen rows (measured on C4: batch 256 -> 90 us
-    // with three groups, 104 us with two; batch 32, 18 rows per group with three: two groups are faster)
-    if (ng == 0) ng = (fits(3, 4) && g.total_rows >= 3LL * dev.sm_count * 40) ? 3 : 2;
+    // three groups (24 consumer warps) once every group of a full grid owns 16 rows or more (measured on C4: batch 256 ->
+    // 90 us with three groups, 104 us with two; batch 64 25.8 / 28.1 us; batch 32, 18-20 rows per group, 15.3 / 15.7 us)
+    if (ng == 0) ng = (fits(3, 4) && g.total_rows >= 3LL * dev.sm_count * 16) ? 3 : 2;
     if (ng > kRingMaxGroups) ng = kRingMaxGroups;
     int slots = 8;
     while (slots > 3 && !fits(ng, slots)) --slots;
@@ -1264,8 +1264,13 @@ inline bool ring_geometry(const RsParams& p, int B, int nt, const TbDevice& dev,
     g.ng = ng; g.slots = slots;
     g.max_rows = kRingMaxRows < p.out_h ? kRingMaxRows : p.out_h;
     if (g.max_rows > g.tc) g.max_rows = g.tc;          // one thread of the group sets up one row of a chunk
-    // every group should own a few dozen rows (the halo of a chunk is NT - 2 + 2 input rows)
-    long long ctas = (g.total_rows + 24LL * ng - 1) / (24LL * ng);
+    // Small batches are latency, not throughput: rather more SMs with few rows each than few SMs with many, down to
+    // 8 rows per group (4 while that still leaves most SMs empty), although a chunk's halo is NT input rows.  Measured on
+    // C4 (512^2 -> 256^2), us per launch with 24 / 8 / 4 rows at least: batch 1 12.1 / 7.2 / 5.9, batch 2 - / 7.3 / 6.1,
+    // batch 8 14.7 / 7.9 / 8.6.
+    long long min_rows = (g.total_rows <= 2LL * ng * dev.sm_count) ? 4 : 8;
+    if ((flags >> 17) & 0x7f) min_rows = (flags >> 17) & 0x7f;      // (development knob)
+    long long ctas = (g.total_rows + min_rows * ng - 1) / (min_rows * ng);
     if (ctas > dev.sm_count) ctas = dev.sm_count;
     if (ctas < 1) ctas = 1;
     // whole groups per unit when that costs little: the longest group then has ceil(out_h / gpu) rows against the even
