@@ -18,7 +18,7 @@ outs = [torch.empty((B, 3, 256, 256), device=dev) for _ in range(8)]
 for i in range(20):
     bt(x[i % 8], out=outs[i % 8])
 torch.cuda.synchronize()
-names = ["entry", "dep wait done", "table filled", "first copy issued", "first slot full", "first store", "grp0 done", "grpN done", "producer0 done", "chunk set up", "waiting for slot"]
+names = ["entry", "dep wait done", "table filled", "first copy issued", "first slot full", "first store", "grp0 done", "grpN done", "producer0 done", "chunk set up", "waiting for slot", "chunk bounds read", "group barrier passed", "row taps stored", "column taps read"]
 for mode in ("alone", "back-to-back"):
     lib.tb_trace_read(None, 1)
     torch.cuda.synchronize()

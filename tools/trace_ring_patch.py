@@ -28,6 +28,10 @@ rep("                    tb_mbar_wait(full, phase);\n", "                    if 
 rep("            if (active) {\n#pragma unroll\n                for (int ch = 0; ch < C; ++ch) tb_st_cs<T>",
     "            if (tid == 32 && tr_first2) { TR(5); tr_first2 = false; }\n            if (active) {\n#pragma unroll\n                for (int ch = 0; ch < C; ++ch) tb_st_cs<T>")
 rep("            while (yy < nr) emit_zero();\n        }\n    }\n}", "            while (yy < nr) emit_zero();\n        }\n    }\n    if (gt == 32) TR(6 + (grp ? 1 : 0));\n}")
+rep("    while (tb_ring_next<NT>(p, g, F, F1, c)) {\n        tb_named_barrier(1 + grp, g.tc);             // every thread of the group is done with the previous chunk's tables\n",
+    "    while (tb_ring_next<NT>(p, g, F, F1, c)) {\n        if (tid == 32 && tr_first) TR(11);\n        tb_named_barrier(1 + grp, g.tc);\n        if (tid == 32 && tr_first) TR(12);\n")
+rep("            s_ytop[gt] = top;\n        }\n", "            s_ytop[gt] = top;\n        }\n        if (tid == 32 && tr_first) TR(13);\n")
+rep("        // one tap encoding per warp: plain if any of its columns has a tap of exactly 1.0, else scaled (top plane\n", "        if (tid == 32 && tr_first) TR(14);\n        // one tap encoding per warp: plain if any of its columns has a tap of exactly 1.0, else scaled (top plane\n")
 rep('extern "C" int tb_resize_bilinear_u8_nhwc_to_nchw(', '''extern "C" __attribute__((visibility("default"))) int tb_trace_read(unsigned long long* host, int reset) {
     if (reset) { static unsigned long long z[256 * 16]; return (int)cudaMemcpyToSymbol(tb_trace, z, sizeof(z)); }
     return (int)cudaMemcpyFromSymbol(host, tb_trace, sizeof(unsigned long long) * 256 * 16);

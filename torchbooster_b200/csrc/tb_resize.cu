@@ -1027,15 +1027,43 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
     uint32_t phase = 0;
     RingChunk c;
     while (tb_ring_next<NT>(p, g, F, F1, c)) {
+        // Every global load of the set-up first, none waiting for another: the chunk's bounds (in tb_ring_next), this
+        // thread's row taps and its column taps -- one trip to L2 / DRAM instead of three in a row (a trace showed 0.9 us
+        // for the bounds and 0.9 us for the column taps).  Taps are read whole and masked by their count afterwards.
+        const int ry = c.oy + c.y0 + gt;
+        const bool rowok = gt < c.nr && ry >= 0 && ry < p.rs_h;
+        int kyr[NT], ymin = 0, yn = 0;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) kyr[j] = 0;
+        if (rowok) {
+            ymin = p.by[2 * ry]; yn = p.by[2 * ry + 1];
+#pragma unroll
+            for (int j = 0; j < NT; ++j)
+                if (j < p.ksy) kyr[j] = p.ky[(size_t)ry * p.ksy + j];
+        }
+        const int x0 = c.tx * g.tc;
+        const int nc = min(g.tc, p.out_w - x0);
+        const bool active = gt < nc;
+        const int x = x0 + gt;
+        const int rx = c.ox + (c.flip ? p.out_w - 1 - x : x);
+        const bool colok = active && rx >= 0 && rx < p.rs_w;
+        int kx[NT], xmin_c = 0, xn = 0;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) kx[j] = 0;
+        if (colok) {
+            xmin_c = p.bx[2 * rx]; xn = p.bx[2 * rx + 1];
+#pragma unroll
+            for (int j = 0; j < NT; ++j)
+                if (j < p.ksx) kx[j] = __ldg(p.kx + (size_t)rx * p.ksx + j);
+        }
         tb_named_barrier(1 + grp, g.tc);             // every thread of the group is done with the previous chunk's tables
         if (gt < c.nr) {
-            const int ry = c.oy + c.y0 + gt;
             int top = -1;
-            if (ry >= 0 && ry < p.rs_h && c.last >= c.first) {
+            if (rowok && c.last >= c.first) {
                 int k[NT];
-                const int xmin = p.by[2 * ry], n = p.by[2 * ry + 1];
+                const int xmin = ymin, n = yn;
 #pragma unroll
-                for (int j = 0; j < NT; ++j) k[j] = (j < p.ksy && j < n) ? p.ky[(size_t)ry * p.ksy + j] : 0;
+                for (int j = 0; j < NT; ++j) k[j] = j < n ? kyr[j] : 0;
                 // vertical taps: mode word 1 = plain 22-bit taps (one of them is 1.0); 2 = taps scaled by TWO with only their
                 // top byte plane non-zero (k a multiple of 2^15: exact 2x / 4x) -- the rounded row lands in bits 7..14 of
                 // the accumulator, so the byte offset of its table row is one AND; 0 = taps scaled by four, three planes
@@ -1057,21 +1085,12 @@ __global__ void __launch_bounds__(kRingMaxGroups * (256 + 32), 1) tb_resize_ring
             }
             s_ytop[gt] = top;
         }
-        const int x0 = c.tx * g.tc;
-        const int nc = min(g.tc, p.out_w - x0);
-        const bool active = gt < nc;
-        const int x = x0 + gt;
-        const int rx = c.ox + (c.flip ? p.out_w - 1 - x : x);
-        const bool colin = active && c.last >= c.first && rx >= 0 && rx < p.rs_w;
-        int kx[NT];
-#pragma unroll
-        for (int j = 0; j < NT; ++j) kx[j] = 0;
+        const bool colin = colok && c.last >= c.first;
         int woff = 0, sh1 = 0;
-        if (colin) {
-            const int xmin = p.bx[2 * rx], n = p.bx[2 * rx + 1];
 #pragma unroll
-            for (int j = 0; j < NT; ++j) kx[j] = (j < p.ksx && j < n) ? __ldg(p.kx + (size_t)rx * p.ksx + j) : 0;
-            const int off = xmin * 3 - c.s0;
+        for (int j = 0; j < NT; ++j) kx[j] = (colin && j < xn) ? kx[j] : 0;
+        if (colin) {
+            const int off = xmin_c * 3 - c.s0;
             sh1 = (off & 3) * 8;
             woff = off & ~3;
         }
