@@ -259,6 +259,8 @@ TB_API int64_t tb_augment_params_walk(
  *   mean, std : HOST float[C], the T.Normalize arguments as float32 (NULL, NULL = no Normalize)
  *   minmax    : DEVICE float[C][2], per-channel (min, max) of src, for TB_IMAGE_STRETCH only.
  *               tb_channel_minmax ACCUMULATES into it (the caller initialises it to +inf, -inf).
+ *               -0.0 and +0.0 order as torch.min / max order them; NaNs are skipped (torch would
+ *               propagate them and stretch every pixel to NaN: undefined bytes either way).
  */
 TB_API int tb_channel_minmax(const float* src, int64_t images, int C, int64_t plane, float* minmax, tb_stream_t stream);
 TB_API int tb_to_image_u8(const float* src, int64_t images, int C, int H, int W, const float* mean, const float* std,
