@@ -80,6 +80,8 @@ extern "C" {
 #define TB_FLAG_TWO_PHASE    16  /* tests: the two-phase (shared-memory intermediate) resize kernel instead of the sliding-window one */
 #define TB_FLAG_SLIDE        32  /* tests: the sliding-window resize kernel where the ring (bulk-copy staged) kernel would run */
 #define TB_FLAG_SRC_PLANAR    8  /* tb_augment: the source is uint8 [B][C][H][W] (src_row_pitch = bytes per row of one plane) */
+/* Bits 8 and up of `flags` are development knobs of single kernels (group / cluster / thread counts, row split); they
+   change how a launch is cut, never its result.  Callers pass 0 there. */
 
 typedef struct CUstream_st* tb_stream_t;   /* == cudaStream_t */
 
