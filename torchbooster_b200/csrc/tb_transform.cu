@@ -60,8 +60,9 @@ __device__ __forceinline__ int tb_fold(int i, int n, int mode, bool& inside) {
 // generic: one thread per output pixel, all channels
 // ------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(256) tb_xf_generic_kernel(XfParams p, int blocks_per_image) {
+__global__ void __launch_bounds__(1024) tb_xf_generic_kernel(XfParams p, int blocks_per_image) {
     __shared__ T s_lut[4 * 256];
+    tb_launch_dependents();
     tb_grid_dependency_wait();
     const T* __restrict__ glut = (const T*)p.lut;
     for (int i = threadIdx.x; i < p.C * 256; i += blockDim.x) s_lut[i] = glut[i];
@@ -385,12 +386,24 @@ __global__ void __launch_bounds__(768, 1) tb_xf_stream_kernel(XfParams p, XfGeom
 }
 
 template <typename T>
-int launch_generic(const XfParams& p, cudaStream_t s) {
-    const int threads = 256;
-    const int64_t bpi = ((int64_t)p.out_h * p.out_w + threads - 1) / threads;
+int launch_generic(const XfParams& p, cudaStream_t s, bool pdl) {
+    // a block copies the table into shared memory before its pixels: large blocks (a whole 32 x 32 image each) keep
+    // that fixed cost per pixel low; small outputs keep small blocks
+    const int64_t pixels = (int64_t)p.out_h * p.out_w;
+    const int threads = pixels >= 1024 ? 1024 : (pixels >= 512 ? 512 : 256);
+    const int64_t bpi = (pixels + threads - 1) / threads;
     const int64_t blocks = bpi * p.B;
     TB_REQUIRE(blocks < (int64_t)1 << 31, "tb_transform: grid too large");
-    tb_xf_generic_kernel<T><<<(unsigned)blocks, threads, 0, s>>>(p, (int)bpi);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3((unsigned)threads);
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    TB_CUDA(cudaLaunchKernelEx(&cfg, tb_xf_generic_kernel<T>, p, (int)bpi));
     TB_LAUNCH_CHECK("tb_xf_generic_kernel");
     return TB_OK;
 }
@@ -544,8 +557,9 @@ static int tb_transform_impl(const uint8_t* src, const int64_t* offsets, int B, 
         if (rc) return rc;
         if (taken) return TB_OK;
     }
-    if (dst_dtype == TB_F32) return launch_generic<float>(p, s);
-    return launch_generic<uint16_t>(p, s);
+    const bool pdl_generic = !(flags & TB_FLAG_NO_PDL);
+    if (dst_dtype == TB_F32) return launch_generic<float>(p, s, pdl_generic);
+    return launch_generic<uint16_t>(p, s, pdl_generic);
 }
 
 extern "C" int tb_transform_u8_nhwc_to_nchw(const uint8_t* src, int B, int H, int W, int C, int64_t src_batch_stride,
