@@ -140,6 +140,22 @@ def test_spec_validation():
             BatchTransform(TransformSpec(), device="cpu")
 
 
+def test_two_stage_pipelines_are_recognised():
+    """Which Resize / CenterCrop pipelines need the uint8 hand-off to the augment kernel (two launches) and which stay one
+    launch: constant padding after a bare resize reads as zeros outside the resized image in the resize kernel itself."""
+    one = [TransformSpec(resize=64), TransformSpec(resize=64, center_crop=56), TransformSpec(resize=64, crop=48, padding=4),
+           TransformSpec(crop=32, padding=4, padding_mode="reflect"), TransformSpec(crop=32, rand_augment=True),
+           TransformSpec(random_resized_crop=32, rand_augment=True)]
+    two = [TransformSpec(resize=64, crop=48, padding=4, padding_mode="reflect"),        # the padding mirrors the resized image
+           TransformSpec(center_crop=40, crop=40, padding=4),                          # must not show what the centre crop cut
+           TransformSpec(resize=64, center_crop=56, crop=56, padding=2, padding_mode="edge"),
+           TransformSpec(resize=256, center_crop=224, flip_p=.5, rand_augment=True), TransformSpec(resize=64, rotation=10)]
+    assert not any(sp.two_stage for sp in one)
+    assert all(sp.two_stage for sp in two)
+    with pytest.raises(ValueError, match="excludes"):
+        TransformSpec(random_resized_crop=32, resize=64)
+
+
 def test_cpu_inputs_are_rejected_not_emulated():
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         M.accuracy(torch.randn(4, 3), torch.zeros(4, dtype=torch.int64))
