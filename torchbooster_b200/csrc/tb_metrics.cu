@@ -604,6 +604,222 @@ __global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_row_kernel(const voi
     }
 }
 
+// Reductions over the 16 lanes of a half-warp (xor butterflies stay inside the half; `m` = the half's lanes).
+__device__ __forceinline__ int tb_half_max(unsigned m, int v) {
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) v = max(v, __shfl_xor_sync(m, v, o));
+    return v;
+}
+__device__ __forceinline__ int tb_half_min(unsigned m, int v) {
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) v = min(v, __shfl_xor_sync(m, v, o));
+    return v;
+}
+__device__ __forceinline__ int tb_half_add(unsigned m, int v) {
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) v += __shfl_xor_sync(m, v, o);
+    return v;
+}
+
+// 16-bit logits: TWO rows per warp, one per half-warp.  A 2 KB row is only four vectors per lane of a full warp, and the
+// work that does not depend on the row's length (label, thresholds, three reductions, the argmax search, the counters)
+// was three quarters of a row's 273 instructions; a half-warp per row does that work for two rows at once.
+template <int DT, bool SCM>
+__global__ void __launch_bounds__(kMxThreads, 4) tb_metrics_row2_kernel(const void* __restrict__ logits, int64_t N, int C,
+                                                                    int64_t row_stride, const int64_t* __restrict__ labels,
+                                                                    int k, unsigned long long* __restrict__ counters,
+                                                                    unsigned long long* __restrict__ confusion) {
+    using E = Elem<DT>;
+    using P = Packed<DT>;
+    constexpr int VE = E::VE;
+    constexpr int UN = 64 / VE;      // vectors per lane of a half-warp: 8 for 16-bit types (1024 elements per row at most)
+    constexpr uint32_t kFill = DT == TB_F32 ? 0xff800000u : (DT == TB_BF16 ? 0xff80ff80u : 0xfc00fc00u);     // -inf
+    __shared__ unsigned int s_cnt[3];
+    extern __shared__ unsigned int s_cm[];        // SCM only: C * C bins
+    if (threadIdx.x < 3) s_cnt[threadIdx.x] = 0;
+    if (SCM) {
+        for (int i = threadIdx.x; i < C * C; i += kMxThreads) s_cm[i] = 0;
+    }
+    __syncthreads();
+    tb_launch_dependents();
+    tb_grid_dependency_wait();
+
+    // `lane` is the lane within the HALF-warp, `warp0` / `nwarps` the first row and the row stride of this half-warp
+    const int lane = threadIdx.x & 15;
+    const unsigned hmask = 0xffffu << (threadIdx.x & 16);
+    const int64_t warp0 = ((int64_t)blockIdx.x * kMxWarps + (threadIdx.x >> 5)) * 2 + ((threadIdx.x >> 4) & 1);
+    const int64_t nwarps = (int64_t)gridDim.x * kMxWarps * 2;
+    const int nv = C / VE;
+    unsigned int c1 = 0, ck = 0, inv = 0;
+    bool take[UN], whole[UN];       // this lane has vector i; every lane has vector i (no -inf fill needed)
+#pragma unroll
+    for (int i = 0; i < UN; ++i) { take[i] = lane + 16 * i < nv; whole[i] = 16 * (i + 1) <= nv; }
+
+    long long y64 = warp0 < N ? labels[warp0] : -1;
+    const typename E::type* row = (const typename E::type*)logits + warp0 * row_stride;
+    const int64_t row_step = nwarps * row_stride;
+    for (int64_t n = warp0; n < N; n += nwarps, row += row_step) {
+        const long long ycur = y64;
+        if (n + nwarps < N) y64 = labels[n + nwarps];
+        if (ycur < 0 || ycur >= C) { inv += 1; continue; }
+        const int y = (int)ycur;
+        const uint4* vp = reinterpret_cast<const uint4*>(row) + lane;
+        uint4 r[UN];
+#pragma unroll
+        for (int i = 0; i < UN; ++i) {
+            if (whole[i]) r[i] = tb_ldcs_now(vp + 16 * i);
+            else r[i] = tb_ldcs_or(vp + 16 * i, take[i], kFill);
+        }
+        const typename E::type raw_y = row[y];
+        // the elements that share the label's 16-byte vector and lie before it, one per lane (ties among them count)
+        const int d0 = y & (VE - 1);
+        const typename E::type raw_t = row[y - d0 + min(lane, VE - 1)];
+        const float ly = E::to_float(raw_y);
+        if (ly != ly) {
+            // rare: the label's own logit is NaN -- the key route of the general kernel, element by element
+            RowAcc<DT> a;
+            a.init(raw_y, y);
+            for (int j = lane; j < C; j += 16) a.one(E::get(row, j), j);
+            const int mx = tb_half_max(hmask, a.bestk);
+            const int pred = tb_half_min(hmask, a.bestk == mx ? a.bj0 : INT_MAX);
+            const int rank = tb_half_add(hmask, a.cnt) / P::kScale;
+            if (lane == 0) {
+                c1 += (rank < 1) ? 1u : 0u;
+                ck += (rank < k) ? 1u : 0u;
+                if (SCM) atomicAdd(&s_cm[y * C + pred], 1u);
+                else if (confusion) atomicAdd(&confusion[(int64_t)y * C + pred], 1ULL);
+            }
+            continue;
+        }
+
+        // ---- thresholds: x > hi  <=>  x outranks the label from behind it; x > lo  <=>  x >= l_y (from before it).
+        // A vector wholly before the label is counted against lo, every other one against hi; the ties before the label
+        // inside its own vector are the (lane < d0) term.
+        int cnt = (lane < d0 && E::to_float(raw_t) == ly) ? P::kScale : 0;
+        float m[UN];
+        const int dl = y - lane * VE;                       // label position relative to this lane's first vector
+        if constexpr (P::kOn) {
+            uint32_t c = (uint32_t)raw_y;
+            if (c == 0x8000u) c = 0;                                   // -0 == +0
+            uint32_t l;
+            if (c == P::kNegInf) l = 0x7fffu;                          // >= -inf: everything counts (NaN threshold: unordered)
+            else if (c == 0u) l = 0x8001u;                             // just below zero
+            else l = (c & 0x8000u) ? c + 1u : c - 1u;
+            const uint32_t hi2 = c * 0x10001u, lo2 = l * 0x10001u;
+#pragma unroll
+            for (int i = 0; i < UN; ++i) {
+                const int d = dl - 16 * i * VE;                        // >= VE: the whole vector lies before the label
+                const uint32_t thr = d >= VE ? lo2 : hi2;
+                const uint32_t t = tb_bitsel(tb_bitsel(P::gtu2(r[i].x, thr), P::gtu2(r[i].y, thr), 0x000f000fu),
+                                             tb_bitsel(P::gtu2(r[i].z, thr), P::gtu2(r[i].w, thr), 0x0f000f00u), 0x00ff00ffu);
+                cnt += __popc(t);
+                const uint32_t mm = P::max2(P::max2(r[i].x, r[i].y), P::max2(r[i].z, r[i].w));
+                m[i] = tb_max_nan(P::lo(mm), P::hi(mm));
+            }
+        } else {
+            const float cc = ly + 0.0f;
+            const uint32_t b = __float_as_uint(cc);
+            const float hi = cc;
+            float lo;
+            if (b == 0xff800000u) lo = __uint_as_float(0x7fffffffu);
+            else if (b == 0u) lo = __uint_as_float(0x80000001u);
+            else lo = __uint_as_float((b & 0x80000000u) ? b + 1u : b - 1u);
+#pragma unroll
+            for (int i = 0; i < UN; ++i) {
+                const int d = dl - 16 * i * VE;
+                const float thr = d >= VE ? lo : hi;
+                const float f0 = __uint_as_float(r[i].x), f1 = __uint_as_float(r[i].y), f2 = __uint_as_float(r[i].z),
+                            f3 = __uint_as_float(r[i].w);
+                cnt = cnt - tb_gtu(f0, thr) - tb_gtu(f1, thr);
+                cnt = cnt - tb_gtu(f2, thr) - tb_gtu(f3, thr);
+                m[i] = tb_max_nan(tb_max3_nan(f0, f1, f2), f3);
+            }
+        }
+        // ---- argmax: warp maximum of the keys, then the first index among the lanes that hold it
+        float M = m[0];
+#pragma unroll
+        for (int i = 1; i < UN; ++i) M = tb_max_nan(M, m[i]);
+        const int key = tb_key(M);
+        const int mx = tb_half_max(hmask, key);
+        int cand = INT_MAX;
+        if (key == mx) {
+            if (M != M) {
+                // a NaN is the maximum (rare): first NaN of this lane
+                int pick = 0;
+#pragma unroll
+                for (int i = UN - 1; i >= 0; --i)
+                    if (m[i] != m[i]) pick = i;
+                if (lane + 16 * pick < nv) {
+                    const uint4 rv = __ldg(vp + 16 * pick);
+                    float f[VE];
+                    E::unpack(rv, f);
+                    int e0 = 0;
+#pragma unroll
+                    for (int e = VE - 1; e >= 0; --e)
+                        if (f[e] != f[e]) e0 = e;
+                    cand = (lane + 16 * pick) * VE + e0;
+                }
+            } else {
+                int pick = 0;
+#pragma unroll
+                for (int i = UN - 1; i >= 0; --i)
+                    if (m[i] >= M) pick = i;
+                // The winning vector is read again (one 16-byte load by one lane, an L2 hit) instead of being kept:
+                // holding all UN vectors for this moment cost the fp32 kernel its registers -- the compiler reused load
+                // registers and a row took three DRAM round trips instead of one.
+                if (lane + 16 * pick < nv) {
+                const uint4 rv = __ldg(vp + 16 * pick);
+                int e0;
+                if constexpr (P::kOn) {
+                    // packed equality against the maximum; nibble w of the low / high half <- word w's low / high element
+                    const uint32_t mp = P::bits(M) * 0x10001u;
+                    const uint32_t t = tb_bitsel(tb_bitsel(P::eq2(rv.x, mp), P::eq2(rv.y, mp), 0x000f000fu),
+                                                 tb_bitsel(P::eq2(rv.z, mp), P::eq2(rv.w, mp), 0x0f000f00u), 0x00ff00ffu);
+                    const uint32_t tl = t & 0xffffu, th = t >> 16;
+                    const int el = tl ? ((__ffs(tl) - 1) >> 2) * 2 : 99;
+                    const int eh = th ? ((__ffs(th) - 1) >> 2) * 2 + 1 : 99;
+                    e0 = min(el, eh);
+                } else {
+                    float f[VE];
+                    E::unpack(rv, f);
+                    e0 = 0;
+#pragma unroll
+                    for (int e = VE - 1; e >= 0; --e)
+                        if (f[e] >= M) e0 = e;
+                }
+                cand = (lane + 16 * pick) * VE + e0;
+                }
+            }
+        }
+        const int pred = tb_half_min(hmask, cand);
+        const int rank = tb_half_add(hmask, cnt) / P::kScale;
+        if (lane == 0) {
+            c1 += (rank < 1) ? 1u : 0u;
+            ck += (rank < k) ? 1u : 0u;
+            if (SCM) atomicAdd(&s_cm[y * C + pred], 1u);
+            else if (confusion) atomicAdd(&confusion[(int64_t)y * C + pred], 1ULL);
+        }
+    }
+    if (lane == 0) {
+        if (c1) atomicAdd(&s_cnt[0], c1);
+        if (ck) atomicAdd(&s_cnt[1], ck);
+        if (inv) atomicAdd(&s_cnt[2], inv);
+    }
+    __syncthreads();
+    if (SCM) {
+        for (int i = threadIdx.x; i < C * C; i += kMxThreads) {
+            const unsigned int v = s_cm[i];
+            if (v) atomicAdd(&confusion[i], (unsigned long long)v);
+        }
+    }
+    if (threadIdx.x == 0) {
+        if (blockIdx.x == 0) atomicAdd(&counters[0], (unsigned long long)N);
+        if (s_cnt[0]) atomicAdd(&counters[1], (unsigned long long)s_cnt[0]);
+        if (s_cnt[1]) atomicAdd(&counters[2], (unsigned long long)s_cnt[1]);
+        if (s_cnt[2]) atomicAdd(&counters[3], (unsigned long long)s_cnt[2]);
+    }
+}
+
 // Deterministic float64 sum of a short vector (per-step losses) into a device-resident state.
 template <int DT>
 __global__ void __launch_bounds__(256) tb_running_sum_kernel(const void* __restrict__ x, int64_t n,
@@ -712,7 +928,11 @@ extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N
     const size_t scm_bytes = (size_t)C * (size_t)C * 4;
     const bool scm = confusion != nullptr && scm_bytes <= (size_t)kScmMaxBytes;
     cfg.dynamicSmemBytes = scm ? scm_bytes : 0;
-    const int64_t cap = (int64_t)dev.sm_count * ((scm && scm_bytes > 24 * 1024) ? 4 : 8);   // 8 x 256 threads = full occupancy
+    // 16-bit rows of one batch: the two-rows-per-warp kernel (two resident CTAs per SM, 16 rows per CTA round)
+    const int ve0 = 16 / es;
+    const bool row2 = es == 2 && ((uintptr_t)logits % 16) == 0 && ((row_stride * es) % 16) == 0 && (C % ve0) == 0 && C / ve0 <= 128;
+    if (row2) blocks = (N + 2 * kMxWarps - 1) / (2 * kMxWarps);
+    const int64_t cap = (int64_t)dev.sm_count * (row2 ? 8 : ((scm && scm_bytes > 24 * 1024) ? 4 : 8));   // two rounds of the resident CTAs
     if (blocks > cap) blocks = cap;
     TB_REQUIRE(N / (blocks * kMxWarps) < ((int64_t)1 << 28), "tb_metrics_update: N too large for one launch");
     cfg.gridDim = dim3((unsigned)blocks);
@@ -742,13 +962,22 @@ extern "C" int tb_metrics_update(const void* logits, int logits_dtype, int64_t N
             TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_row_kernel<DT, false>, logits, N, C, row_stride, labels, k, cnt, cm));    \
         }                                                                                                                     \
     } while (0)
+#define TB_MX_ROW2(DT)                                                                                                        \
+    do {                                                                                                                      \
+        if (scm) {                                                                                                            \
+            TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_row2_kernel<DT, true>, logits, N, C, row_stride, labels, k, cnt, cm));    \
+        } else {                                                                                                              \
+            TB_CUDA(cudaLaunchKernelEx(&cfg, tb_metrics_row2_kernel<DT, false>, logits, N, C, row_stride, labels, k, cnt, cm));   \
+        }                                                                                                                     \
+    } while (0)
     if (one_batch) {
         if (logits_dtype == TB_F32) TB_MX_ROW(TB_F32);
-        else if (logits_dtype == TB_BF16) TB_MX_ROW(TB_BF16);
-        else TB_MX_ROW(TB_F16);
+        else if (logits_dtype == TB_BF16) TB_MX_ROW2(TB_BF16);
+        else TB_MX_ROW2(TB_F16);
         TB_LAUNCH_CHECK("tb_metrics_row_kernel");
         return TB_OK;
     }
+#undef TB_MX_ROW2
 #undef TB_MX_ROW
     if (logits_dtype == TB_F32) TB_MX_LAUNCH(TB_F32);
     else if (logits_dtype == TB_BF16) TB_MX_LAUNCH(TB_BF16);
